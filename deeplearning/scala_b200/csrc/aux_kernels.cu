@@ -1,0 +1,201 @@
+// aux_kernels.cu -- the remaining hand-written sm_100a kernels:
+//   N3  sum_kernel / sum_axis_*   full and single-axis reductions (warp shuffles + block tree, one launch)
+//   N5  random_kernel / random_normal_kernel   counter-based RNG, bit-compatible with Tensors:98-117, :398-443
+//   N6  sgd_kernel                fused in-place `data - lr * delta` (TW:63-72 without the buffer swap)
+#include "common.h"
+#include "reduce.cuh"
+
+namespace dls {
+
+// ---- N3: full sum (replaces reduce(PlusPrograms), Tensors:673-766) ---------------------------------------------------
+__global__ void __launch_bounds__(kBlock) sum_kernel(const float *__restrict__ in, size_t n, ReduceArgs R) {
+  const size_t n4 = n / 4;
+  const float4 *in4 = reinterpret_cast<const float4 *>(in);
+  const size_t stride = (size_t)gridDim.x * kBlock;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x;
+  // four independent 128-bit loads in flight per lane
+  for (; i + 3 * stride < n4; i += 4 * stride) {
+    float4 v0 = __ldcs(in4 + i), v1 = __ldcs(in4 + i + stride), v2 = __ldcs(in4 + i + 2 * stride),
+           v3 = __ldcs(in4 + i + 3 * stride);
+    a0 += (v0.x + v0.y) + (v0.z + v0.w);
+    a1 += (v1.x + v1.y) + (v1.z + v1.w);
+    a2 += (v2.x + v2.y) + (v2.z + v2.w);
+    a3 += (v3.x + v3.y) + (v3.z + v3.w);
+  }
+  for (; i < n4; i += stride) {
+    float4 v = __ldcs(in4 + i);
+    a0 += (v.x + v.y) + (v.z + v.w);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) a1 += in[n4 * 4 + threadIdx.x];
+  grid_sum_finish((a0 + a1) + (a2 + a3), R);
+}
+
+int launch_sum(dls_ctx *ctx, int stream, const float *in, size_t n, float *out) {
+  cudaStream_t st = ctx->streams[stream];
+  if (n == 0) {
+    DLS_CUDA(cudaMemsetAsync(out, 0, sizeof(float), st));
+    return DLS_OK;
+  }
+  ReduceArgs R{ctx->red_partials[stream], ctx->red_counter[stream], out};
+  size_t want = (n / 4 + (size_t)kBlock * 4 - 1) / ((size_t)kBlock * 4);
+  size_t cap = (size_t)ctx->sm_count * 8;
+  if (cap > (size_t)kReduceMaxBlocks) cap = kReduceMaxBlocks;
+  int grid = (int)std::max<size_t>(1, std::min(want, cap));
+  sum_kernel<<<grid, kBlock, 0, st>>>(in, n, R);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+// ---- N3: one-axis sum over a row-major [outer, k, inner] view ---------------------------------------------------------
+// inner > 1: one lane per (outer, inner) column, lanes coalesced along `inner`, k summed in ascending order -- the same
+// left fold ((t0 + t1) + t2) + ... the reference builds on the host (TL:124-162), so results are bit-identical to it.
+__global__ void __launch_bounds__(kBlock) sum_axis_cols_kernel(const float *__restrict__ in, float *__restrict__ out,
+                                                               size_t outer, size_t k, size_t inner) {
+  const size_t total = outer * inner;
+  for (size_t c = (size_t)blockIdx.x * kBlock + threadIdx.x; c < total; c += (size_t)gridDim.x * kBlock) {
+    const size_t o = c / inner, i = c - o * inner;
+    const float *p = in + o * k * inner + i;
+    float acc = __ldg(p);
+    size_t j = 1;
+    for (; j + 4 <= k; j += 4) {
+      float v0 = __ldg(p + j * inner), v1 = __ldg(p + (j + 1) * inner), v2 = __ldg(p + (j + 2) * inner),
+            v3 = __ldg(p + (j + 3) * inner);
+      acc = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v0), v1), v2), v3);
+    }
+    for (; j < k; ++j) acc = __fadd_rn(acc, __ldg(p + j * inner));
+    out[c] = acc;
+  }
+}
+
+// inner == 1: one warp per row, lanes strided along k, shuffle tree (order differs from the host fold: <= 1e-5 rel).
+__global__ void __launch_bounds__(kBlock) sum_axis_rows_kernel(const float *__restrict__ in, float *__restrict__ out,
+                                                               size_t rows, size_t k) {
+  const size_t warps = (size_t)gridDim.x * (kBlock / 32);
+  const int lane = threadIdx.x & 31;
+  for (size_t r = (size_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5); r < rows; r += warps) {
+    const float *p = in + r * k;
+    float acc = 0.f;
+    for (size_t j = lane; j < k; j += 32) acc += __ldg(p + j);
+    acc = warp_sum(acc);
+    if (lane == 0) out[r] = acc;
+  }
+}
+
+int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, size_t k, size_t inner, float *out) {
+  cudaStream_t st = ctx->streams[stream];
+  if (outer * inner == 0) return DLS_OK;
+  if (k == 0) {
+    DLS_CUDA(cudaMemsetAsync(out, 0, outer * inner * sizeof(float), st));
+    return DLS_OK;
+  }
+  size_t cap = (size_t)ctx->sm_count * 8;
+  if (inner == 1 && k >= 64) {
+    size_t want = (outer + kBlock / 32 - 1) / (kBlock / 32);
+    sum_axis_rows_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, out, outer, k);
+  } else {
+    size_t want = (outer * inner + kBlock - 1) / kBlock;
+    sum_axis_cols_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, out, outer, k, inner);
+  }
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+// ---- N5: RNG --------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t wang_hash(uint32_t v) {  // Tensors:107-116
+  v = (v ^ 61u) ^ (v >> 16);
+  v *= 9u;
+  v ^= v << 4;
+  v *= 0x27d4eb2du;
+  v ^= v >> 15;
+  return v;
+}
+__device__ __forceinline__ uint32_t lcg_hash(uint32_t v) { return 1103515245u * v + 12345u; }  // Tensors:99-103
+__device__ __forceinline__ uint32_t xorshift(uint32_t s) {                                      // Tensors:403-407
+  uint32_t t1 = s ^ (s << 13);
+  uint32_t t2 = t1 ^ (t1 >> 17);
+  return t2 ^ (t2 << 5);
+}
+__device__ __forceinline__ float u01(uint32_t h) { return __fdiv_rn(__uint2float_rn(h), 4294967296.0f); }
+
+template <int HASH>
+__global__ void __launch_bounds__(kBlock) random_kernel(float *__restrict__ out, size_t n, uint32_t seed) {
+  // Tensors:436-439: buffer[i] = hash(i ^ seed) / 4294967296.0f
+  for (size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += (size_t)gridDim.x * kBlock) {
+    uint32_t x = (uint32_t)i ^ seed;
+    out[i] = u01(HASH == DLS_HASH_WANG ? wang_hash(x) : lcg_hash(x));
+  }
+}
+
+template <int HASH>
+__global__ void __launch_bounds__(kBlock) random_normal_kernel(float2 *__restrict__ out, size_t n_pairs, uint32_t seed) {
+  // Tensors:409-425: Box-Muller, work-item i writes elements 2i and 2i+1
+  for (size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x; i < n_pairs; i += (size_t)gridDim.x * kBlock) {
+    uint32_t x = (uint32_t)i ^ seed;
+    uint32_t r1 = HASH == DLS_HASH_WANG ? wang_hash(x) : lcg_hash(x);
+    uint32_t r2 = xorshift(r1);
+    float u1 = u01(r1), u2 = u01(r2);
+    float r = __fsqrt_rn(__fmul_rn(-2.0f, logf(u1)));
+    float theta = __fmul_rn(6.28318530717958647692f, u2);
+    out[i] = make_float2(__fmul_rn(r, cosf(theta)), __fmul_rn(r, sinf(theta)));
+  }
+}
+
+static int grid_for(dls_ctx *ctx, size_t work) {
+  size_t want = (work + kBlock - 1) / kBlock;
+  size_t cap = (size_t)ctx->sm_count * 8;
+  return (int)std::max<size_t>(1, std::min(want, cap));
+}
+
+int launch_random(dls_ctx *ctx, int stream, float *out, size_t n, uint32_t seed, int hash_kind) {
+  if (n == 0) return DLS_OK;
+  cudaStream_t st = ctx->streams[stream];
+  if (hash_kind == DLS_HASH_LCG) random_kernel<DLS_HASH_LCG><<<grid_for(ctx, n), kBlock, 0, st>>>(out, n, seed);
+  else random_kernel<DLS_HASH_WANG><<<grid_for(ctx, n), kBlock, 0, st>>>(out, n, seed);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+int launch_random_normal(dls_ctx *ctx, int stream, float *out, size_t n_padded, uint32_t seed, int hash_kind) {
+  if (n_padded == 0) return DLS_OK;
+  cudaStream_t st = ctx->streams[stream];
+  size_t pairs = n_padded / 2;
+  float2 *o2 = reinterpret_cast<float2 *>(out);
+  if (hash_kind == DLS_HASH_LCG) random_normal_kernel<DLS_HASH_LCG><<<grid_for(ctx, pairs), kBlock, 0, st>>>(o2, pairs, seed);
+  else random_normal_kernel<DLS_HASH_WANG><<<grid_for(ctx, pairs), kBlock, 0, st>>>(o2, pairs, seed);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+// ---- N6: fused SGD step ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) sgd_kernel(float *__restrict__ w, const float *__restrict__ d, size_t n, float lr) {
+  const size_t n4 = n / 4;
+  float4 *w4 = reinterpret_cast<float4 *>(w);
+  const float4 *d4 = reinterpret_cast<const float4 *>(d);
+  for (size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x; i < n4; i += (size_t)gridDim.x * kBlock) {
+    float4 a = w4[i], g = __ldcs(d4 + i);
+    a.x = __fsub_rn(a.x, __fmul_rn(lr, g.x));
+    a.y = __fsub_rn(a.y, __fmul_rn(lr, g.y));
+    a.z = __fsub_rn(a.z, __fmul_rn(lr, g.z));
+    a.w = __fsub_rn(a.w, __fmul_rn(lr, g.w));
+    w4[i] = a;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    size_t i = n4 * 4 + threadIdx.x;
+    w[i] = __fsub_rn(w[i], __fmul_rn(lr, d[i]));
+  }
+}
+
+int launch_sgd(dls_ctx *ctx, int stream, float *w, const float *d, size_t n, float lr) {
+  if (n == 0) return DLS_OK;
+  sgd_kernel<<<grid_for(ctx, (n + 3) / 4), kBlock, 0, ctx->streams[stream]>>>(w, d, n, lr);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+}  // namespace dls

@@ -1,0 +1,119 @@
+// common.h -- internal runtime structures behind the opaque handles of include/dls_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/dls_b200.h"
+#include "plan.h"
+
+namespace dls {
+
+void set_error(const std::string &msg);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+
+#define DLS_CUDA(expr)                                                       \
+  do {                                                                       \
+    cudaError_t e__ = (expr);                                                \
+    if (e__ != cudaSuccess) return ::dls::cuda_fail(e__, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define DLS_CHECK(cond, code, msg) \
+  do {                             \
+    if (!(cond)) {                 \
+      ::dls::set_error(msg);       \
+      return (code);               \
+    }                              \
+  } while (0)
+
+constexpr int kMaxStreams = 32;
+constexpr int kReduceMaxBlocks = 4096;   // partial sums per stream-private scratch
+
+struct Block {
+  void *ptr = nullptr;
+  size_t bytes = 0;
+  uint32_t stream_mask = 0;                 // pool streams that touched the block before it was freed
+  cudaEvent_t free_events[kMaxStreams] = {};  // only for streams in stream_mask when more than one stream exists
+};
+
+struct CachedPlan {
+  std::vector<uint8_t> blob;
+  Plan plan;
+};
+
+}  // namespace dls
+
+struct dls_event {
+  std::atomic<int> rc{1};
+  dls_ctx *ctx = nullptr;
+  cudaEvent_t ev = nullptr;
+};
+
+struct dls_buf {
+  std::atomic<int> rc{1};
+  dls_ctx *ctx = nullptr;
+  float *ptr = nullptr;
+  size_t n = 0;            // floats
+  dls::Block block;
+  int last_stream = 0;     // stream of the most recent writer
+  cudaEvent_t ready = nullptr;  // recorded after the most recent writer (multi-stream contexts only)
+};
+
+struct dls_ctx {
+  int device = 0;
+  int sm_count = 148;
+  int n_streams = 1;
+  dls_ctx_opts opts{};
+  std::vector<cudaStream_t> streams;
+  uint32_t rr = 0;
+  std::recursive_mutex mu;
+
+  // caching allocator
+  std::multimap<size_t, dls::Block> free_blocks;
+  dls_stats stats{};
+
+  // plan cache (replaces Tensors.kernelCache)
+  std::unordered_multimap<uint64_t, std::shared_ptr<dls::CachedPlan>> plans;
+
+  // per-stream reduction scratch: kReduceMaxBlocks partial sums + one arrival counter
+  std::vector<float *> red_partials;
+  std::vector<unsigned int *> red_counter;
+
+  // occupancy-derived grid sizes, filled at create time
+  int vec_blocks_per_sm = 4;
+  int gather_blocks_per_sm = 4;
+
+  void *nccl_comm = nullptr;
+  int comm_rank = 0, comm_world = 1;
+};
+
+namespace dls {
+
+// runtime.cu
+int pick_stream(dls_ctx *ctx);
+int alloc_block(dls_ctx *ctx, size_t bytes, int stream, Block *out);
+void free_block(dls_ctx *ctx, Block &blk);
+int new_buf(dls_ctx *ctx, size_t n_floats, int stream, dls_buf **out);
+int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_event *const *deps, int n_deps);
+int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_written, dls_buf *const *read, int n_read,
+                  dls_event **done);
+
+// ew_kernels.cu
+int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params, dls_buf *out, bool reduce_sum);
+int query_ew_occupancy(dls_ctx *ctx);
+
+// aux_kernels.cu
+int launch_sum(dls_ctx *ctx, int stream, const float *in, size_t n, float *out);
+int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, size_t k, size_t inner, float *out);
+int launch_random(dls_ctx *ctx, int stream, float *out, size_t n, uint32_t seed, int hash_kind);
+int launch_random_normal(dls_ctx *ctx, int stream, float *out, size_t n_padded, uint32_t seed, int hash_kind);
+int launch_sgd(dls_ctx *ctx, int stream, float *w, const float *d, size_t n, float lr);
+
+}  // namespace dls

@@ -1,0 +1,272 @@
+"""Host mirror of the DeepLearning.scala tensor autodiff plugins on top of `deeplearning.scala_b200.tensors`.
+
+  TL   = plugins-TensorLayers/src/main/scala/com/thoughtworks/deeplearning/plugins/TensorLayers.scala
+  TW   = plugins-TensorWeights/src/main/scala/com/thoughtworks/deeplearning/plugins/TensorWeights.scala
+  CTL  = plugins-CumulativeTensorLayers/src/main/scala/com/thoughtworks/deeplearning/plugins/CumulativeTensorLayers.scala
+  TLit = plugins-TensorLiterals/src/main/scala/com/thoughtworks/deeplearning/plugins/TensorLiterals.scala
+
+`Plugins(cumulative=..., optimizer_delta=...)` is one mixin stack (`Factory[TensorLayers with TensorWeights with
+[Cumulative]TensorLayers ...].newInstance()`), exposing the same operations under the same names: `+`, `*`, `translate`,
+`split`, `join`, `TensorLayer(forward)`, `train`, `predict`, `TensorWeight.allocate` (here `weight`).  All tensor work
+stays lazy; the only device launches are the ones the reference performs -- `doCache` of each weight's
+`data - delta` tree (TW:64), i.e. forward recompute + backward + SGD step fused into a single kernel per weight.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional
+
+from . import tensors as T
+from .do import Do, sequence
+
+
+class Tape:
+    """DeepLearning.scala:18 -- Tape(data, backward)."""
+    __slots__ = ("data", "backward")
+
+    def __init__(self, data, backward):
+        self.data, self.backward = data, backward
+
+
+def sum_as(tensor, shape):
+    """TL:124-162: reduce `tensor` to `shape` by summing away trailing dims with host-unrolled `split(j).reduce(_ + _)`
+    (a left fold).  The `shape(i) == 1` branch reproduces the reference's defect (its permute is discarded, TL:139-148)."""
+    shape = list(shape)
+    if len(shape) > len(tensor.shape):
+        raise ValueError("Cannot sum %r to %r" % (tensor.shape, shape))
+
+    def fold(parts):
+        acc = parts[0]
+        for p in parts[1:]:
+            acc = acc + p
+        return acc
+
+    def loop(t, i, j):
+        if j >= len(t.shape):
+            return t
+        if i >= len(shape):
+            return fold([loop(s, i + 1, j) for s in t.split(j)])
+        if t.shape[i] != 1 and shape[i] == 1:
+            return fold([loop(s, i + 1, j + 1) for s in t.split(j)])
+        if t.shape[j] == shape[i]:
+            return loop(t, i + 1, j + 1)
+        raise ValueError("Cannot sum %r to %r" % (tensor.shape, shape))
+
+    out = loop(tensor, 0, 0)
+    if list(out.shape) != shape:
+        raise AssertionError("sumAs produced %r, expected %r (TL:159-161)" % (out.shape, shape))
+    return out
+
+
+def broadcast_then_sum(tensor, shape):
+    """TL:110-121: pad the delta's shape on the right up to the target rank, then sumAs."""
+    shape = list(shape)
+    have = list(tensor.shape)
+    if len(have) < len(shape):
+        tensor = tensor.broadcast(have + shape[len(have):])
+    return sum_as(tensor, shape)
+
+
+class Differentiable:
+    plugins: "Plugins"
+
+    def forward(self) -> Do:
+        raise NotImplementedError
+
+    def __add__(self, other): return self.plugins.plus(self, other)
+    def __radd__(self, other): return self.plugins.plus(other, self)
+    def __mul__(self, other): return self.plugins.times(self, other)
+    def __rmul__(self, other): return self.plugins.times(other, self)
+
+
+class TensorLiteral(Differentiable):
+    """TLit:13-27: a raw Tensor in the graph; backward is a no-op."""
+
+    def __init__(self, plugins, tensor):
+        self.plugins, self.tensor = plugins, tensor
+
+    def forward(self) -> Do:
+        return Do.now(Tape(self.tensor, lambda do_delta: None))
+
+
+class TensorLayer(Differentiable):
+    """TensorLayerApi (TL:57-82); with `plugins.cumulative` also CumulativeTensorLayers.TensorLayerApi (CTL:30-83)."""
+
+    def __init__(self, plugins: "Plugins", raw_forward: Do):
+        self.plugins, self.raw_forward = plugins, raw_forward
+        self._accumulated: Optional[Do] = None
+
+    def forward(self) -> Do:
+        if not self.plugins.cumulative:
+            return self.raw_forward                                          # TL:66-68
+        if self._accumulated is None:                                        # CTL:55-63
+            self._accumulated = self.raw_forward.flat_map(self._accumulator).shared()
+        return self._accumulated.map(self._cumulative_tape)
+
+    @staticmethod
+    def _accumulator(tape: Tape) -> Do:
+        def acquire():
+            zero = Do.now(T.scalar(0.0))
+            state = {"delta": zero, "zero": zero}
+
+            def flush():                                                     # Accumulator.release, CTL:39-52
+                delta, state["delta"] = state["delta"], None
+                if delta is not state["zero"]:
+                    tape.backward(delta)
+            return (tape, state), flush
+        return Do(acquire)
+
+    @staticmethod
+    def _cumulative_tape(pair) -> Tape:
+        tape, state = pair
+
+        def backward(do_delta: Do):                                          # CTL:67-79
+            current = state["delta"]
+            if current is None:
+                raise RuntimeError("Cannot perform Tape.backward after the Tape is released")
+            # CTL:72 compares a Do with a Tensor, so the `zero` case never matches: every delta is `0.0f + delta`
+            state["delta"] = sequence([current, do_delta]).map(lambda pair: pair[0] + pair[1])
+        return Tape(tape.data, backward)
+
+    def train(self) -> Do:
+        """TL:70-76: forward, backward with the scalar delta 1.0f (TL:55), yield the forward data."""
+        def step(tape):
+            tape.backward(Do.now(T.scalar(1.0)))
+            return Do.now(tape.data)
+        return self.forward().flat_map(step)
+
+    def predict(self) -> Do:
+        """TL:78-80."""
+        return self.forward().map(lambda tape: tape.data)
+
+
+class TensorWeight(Differentiable):
+    """TensorWeightApi (TW:27-74) + allocate (TW:139-153)."""
+
+    def __init__(self, plugins: "Plugins", data):
+        self.plugins, self.data = plugins, data
+
+    def forward(self) -> Do:
+        def acquire():
+            data = self.data                                                 # TW:31 data.doCache (already pinned)
+
+            def backward(do_delta: Do):
+                try:
+                    self.backward(do_delta)
+                except Exception as exc:                                     # TW:36-39 -> handleException
+                    self.plugins.handle_exception(exc)
+            return Tape(data, backward), (lambda: None)
+        return Do(acquire)
+
+    def backward(self, original_delta: Do):
+        """TW:50-74: delta = optimizer.delta; newData = (data - delta).doCache; release the old buffer; swap."""
+        delta = original_delta.map(lambda d: self.plugins.optimizer_delta(self, d)).run()
+        # The old buffer is released when the last tape that pinned it goes away (TW:31 retains it per forward);
+        # here that is the DeviceBuffer reference count.
+        self.data = (self.data - delta).do_cache()
+
+
+class Plugins:
+    def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None):
+        self.cumulative = cumulative
+        self.optimizer_delta = optimizer_delta or (lambda weight, delta: delta)   # Weights.scala:46-51 default
+        self.handled_exceptions: List[BaseException] = []
+
+    def handle_exception(self, exc):                                         # Differentiables.scala:10-14
+        self.handled_exceptions.append(exc)
+
+    # -- Do helpers used by hand-written layers --------------------------------------------------------------------
+    @staticmethod
+    def do_now(value) -> Do:
+        return Do.now(value)
+
+    @staticmethod
+    def do(acquire) -> Do:
+        return Do(acquire)
+
+    # -- constructors ----------------------------------------------------------------------------------------------
+    def lift(self, x) -> Differentiable:
+        return x if isinstance(x, Differentiable) else TensorLiteral(self, T.as_tensor(x))
+
+    def layer(self, raw_forward: Do) -> TensorLayer:
+        """TensorLayer.apply (TL:98-108): the extension point for custom differentiable operations."""
+        return TensorLayer(self, raw_forward)
+
+    def weight(self, initial) -> TensorWeight:
+        """TensorWeight.allocate (TW:139-143)."""
+        return TensorWeight(self, initial.do_cache())
+
+    # -- differentiable operators ----------------------------------------------------------------------------------
+    def _binary(self, a, b, data_of, deltas_of) -> TensorLayer:
+        a, b = self.lift(a), self.lift(b)
+
+        def build(tapes):
+            t0, t1 = tapes
+            d0, d1 = t0.data, t1.data
+            s0, s1 = list(d0.shape), list(d1.shape)
+
+            def backward(do_delta: Do):
+                t0.backward(do_delta.map(lambda d: broadcast_then_sum(deltas_of(d, d0, d1)[0], s0)))
+                t1.backward(do_delta.map(lambda d: broadcast_then_sum(deltas_of(d, d0, d1)[1], s1)))
+            return Tape(data_of(d0, d1), backward)
+        return self.layer(sequence([a.forward(), b.forward()]).map(build))
+
+    def plus(self, a, b) -> TensorLayer:
+        """`Tensor+Tensor` (TL:291-314)."""
+        return self._binary(a, b, lambda x, y: x + y, lambda d, x, y: (d, d))
+
+    def times(self, a, b) -> TensorLayer:
+        """`Tensor*Tensor` (TL:316-340)."""
+        return self._binary(a, b, lambda x, y: x * y, lambda d, x, y: (d * y, d * x))
+
+    def translate(self, a, offset) -> TensorLayer:
+        """TL:225-238: backward translates the (broadcast) delta back by -offset."""
+        a = self.lift(a)
+        offset = [float(o) for o in offset]
+
+        def build(tape):
+            shape0 = list(tape.data.shape)
+
+            def backward(do_delta: Do):
+                tape.backward(do_delta.map(lambda d: d.broadcast(shape0).translate([-o for o in offset])))
+            return Tape(tape.data.translate(offset), backward)
+        return self.layer(a.forward().map(build))
+
+    def join(self, operands, dimension=None) -> TensorLayer:
+        """TL:164-215: operand i receives `delta.broadcast(outShape).split(dim)(i)`."""
+        operands = [self.lift(o) for o in operands]
+
+        def build(tapes):
+            out = T.join([t.data for t in tapes], dimension)
+            out_shape = list(out.shape)
+            dim = len(out_shape) - 1 if dimension is None else dimension
+
+            def backward(do_delta: Do):
+                for i, tape in enumerate(tapes):
+                    tape.backward(do_delta.map(lambda d, i=i: d.broadcast(out_shape).split(dim)[i]))
+            return Tape(out, backward)
+        return self.layer(sequence([o.forward() for o in operands]).map(build))
+
+    def split(self, a, dimension) -> Do:
+        """TL:240-287: Do[Seq[TensorLayer]]; slice deltas accumulate per slot and are re-joined and sent upstream once,
+        when the shared Do is released."""
+        a = self.lift(a)
+
+        def bind(tape):
+            def acquire():
+                slices = tape.data.split(dimension)
+                zero = Do.now(T.scalar(0.0))
+                slots: List[Do] = [zero] * len(slices)
+
+                def flush():
+                    pending = list(slots)
+                    for i in range(len(slots)):
+                        slots[i] = zero
+                    tape.backward(sequence(pending).map(lambda ts: T.join(ts, dimension)))
+
+                def slice_layer(i):
+                    def backward(do_delta: Do):
+                        slots[i] = sequence([slots[i], do_delta]).map(lambda pair: pair[0] + pair[1])
+                    return self.layer(Do.now(Tape(slices[i], backward)))
+                return [slice_layer(i) for i in range(len(slices))], flush
+            return Do(acquire).shared()
+        return a.forward().flat_map(bind)

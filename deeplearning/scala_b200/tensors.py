@@ -1,0 +1,550 @@
+"""The lazy `Tensor` algebra of Compute.scala's `Tensors` trait on top of libdlsb200 (CUDA, sm_100a).
+
+Host-side mirror of `trait Tensors` (Tensors = Compute.scala/Tensors/src/main/scala/com/thoughtworks/compute/Tensors.scala):
+same public surface, same laziness, same class-dependent view semantics (the checkpoint rule, Tensors:978-1003), but
+every slow action goes through the C ABI (`dls_launch_tree`, `dls_sum`, `dls_random*`, ...) instead of generating and
+compiling OpenCL C.  `Backend` is one `Factory[... with Tensors].newInstance(...)`; the module-level functions are the
+`gpu` singleton (gpu.scala:15-27).  There is no CPU path in this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+import weakref
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+from . import ndat
+from ._format import format_tensor
+from .trees import Binary, Ident, Literal, Unary, Xform, serialize
+
+F32 = np.float32
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# device handles
+# ----------------------------------------------------------------------------------------------------------------------
+
+
+class DeviceBuffer:
+    """Owns one reference to a `dls_buf` (OpenCL.DeviceBuffer, OpenCL.scala:633-717)."""
+    __slots__ = ("backend", "handle", "length", "__weakref__")
+
+    def __init__(self, backend, handle, length):
+        self.backend, self.handle, self.length = backend, handle, length
+
+    def __del__(self):
+        h, self.handle = self.handle, None
+        if h and N is not None and self.backend._ctx:
+            N.lib.dls_buf_release(h)
+
+    @property
+    def device_ptr(self) -> int:
+        return N.lib.dls_buf_device_ptr(self.handle)
+
+
+class Event:
+    """Owns one reference to a `dls_event` (OpenCL.Event, OpenCL.scala:565-612)."""
+    __slots__ = ("handle",)
+
+    def __init__(self, handle):
+        self.handle = handle
+
+    def wait(self):
+        N.check(N.lib.dls_event_wait(self.handle))
+
+    def __del__(self):
+        h, self.handle = self.handle, None
+        if h and N is not None:
+            N.lib.dls_event_release(h)
+
+
+def elapsed_ms(start: Event, end: Event) -> float:
+    ms = C.c_float()
+    N.check(N.lib.dls_event_elapsed_ms(start.handle, end.handle, C.byref(ms)))
+    return ms.value
+
+
+class Backend:
+    """One instance of the `Tensors` trait: context, stream pool, allocator, plan cache (Tensors:199, OpenCL:1139)."""
+
+    def __init__(self, device: int = 0, streams_per_device: int = 1, rng_hash: str = "wang", gemm_mode: str = "fp32",
+                 allocator_cap_bytes: int = 0, fuse_reductions: bool = True):
+        self._opts = N.CtxOpts(device=device, streams_per_device=streams_per_device,
+                               rng_hash={"wang": N.DLS_HASH_WANG, "lcg": N.DLS_HASH_LCG}[rng_hash],
+                               gemm_mode={"fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}[gemm_mode],
+                               allocator_cap_bytes=allocator_cap_bytes, plan_cache_capacity=0, reserved=0)
+        self.fuse_reductions = fuse_reductions
+        self._ctx = None
+        self._lock = threading.Lock()
+
+    # -- lifetime (lazy like OpenCL.context, OpenCL:1376-1393; close == monadicClose, OpenCL:1335) ---------------------
+    @property
+    def ctx(self):
+        if self._ctx is None:
+            with self._lock:
+                if self._ctx is None:
+                    h = C.c_void_p()
+                    N.check(N.lib.dls_ctx_create(C.byref(self._opts), C.byref(h)))
+                    self._ctx = h
+        return self._ctx
+
+    def close(self):
+        ctx, self._ctx = self._ctx, None
+        if ctx:
+            N.lib.dls_ctx_destroy(ctx)
+
+    def synchronize(self):
+        N.check(N.lib.dls_ctx_sync(self.ctx))
+
+    def stats(self) -> dict:
+        s = N.Stats()
+        N.check(N.lib.dls_ctx_stats(self.ctx, C.byref(s)))
+        return {k: int(getattr(s, k)) for k, _ in N.Stats._fields_}
+
+    def record_event(self, stream: int = 0) -> Event:
+        h = C.c_void_p()
+        N.check(N.lib.dls_event_record(self.ctx, stream, C.byref(h)))
+        return Event(h)
+
+    def stream_handle(self, index: int = 0) -> int:
+        return N.lib.dls_ctx_stream(self.ctx, index)
+
+    # -- raw device operations ---------------------------------------------------------------------------------------
+    def upload(self, flat: np.ndarray) -> DeviceBuffer:
+        flat = np.ascontiguousarray(flat, dtype=F32).reshape(-1)
+        h = C.c_void_p()
+        N.check(N.lib.dls_buf_from_host(self.ctx, flat.ctypes.data_as(C.c_void_p), flat.size, C.byref(h), None))
+        # the source array may be freed by the caller: the copy above is enqueued from pageable memory, which the CUDA
+        # runtime stages synchronously, so no extra wait is needed here
+        return DeviceBuffer(self, h, flat.size)
+
+    def download(self, buf: DeviceBuffer, n: Optional[int] = None, offset: int = 0) -> np.ndarray:
+        n = buf.length - offset if n is None else n
+        out = np.empty(n, dtype=F32)
+        N.check(N.lib.dls_buf_read(self.ctx, buf.handle, offset, out.ctypes.data_as(C.c_void_p), n, None, 0, None))
+        return out
+
+    def launch(self, roots, out_shape, reduce_sum: bool = False) -> DeviceBuffer:
+        """enqueueClosure (Tensors:1163-1264): serialise, materialise every parameter tensor, launch."""
+        blob, params = serialize(roots, out_shape)
+        bufs = [p._buffer() for p in params]                         # Tensors:1208-1212
+        arr = (C.c_void_p * max(1, len(bufs)))(*[b.handle for b in bufs])
+        out = C.c_void_p()
+        flags = N.DLS_LAUNCH_REDUCE_SUM if reduce_sum else N.DLS_LAUNCH_DEFAULT
+        N.check(N.lib.dls_launch_tree(self.ctx, blob, len(blob), arr, len(bufs), None, 0, flags, C.byref(out), None))
+        n = 1 if reduce_sum else int(np.prod(out_shape, dtype=np.int64)) * len(roots)
+        return DeviceBuffer(self, out, n)
+
+    def describe_plan(self, roots, out_shape) -> str:
+        blob, _ = serialize(roots, out_shape)
+        text = C.create_string_buffer(4096)
+        N.check(N.lib.dls_plan_describe(None, blob, len(blob), text, len(text)))
+        return text.value.decode()
+
+    def plan_cache_contains(self, tensor: "Tensor") -> bool:
+        """`kernelCache.getIfPresent(tensor.getClosure)` (TensorsSpec:48-52)."""
+        blob, _ = serialize([tensor.closure()], tensor.shape)
+        found = C.c_int()
+        N.check(N.lib.dls_plan_cache_contains(self.ctx, blob, len(blob), C.byref(found)))
+        return bool(found.value)
+
+    # -- object Tensor (Tensors:395-600) -------------------------------------------------------------------------------
+    def tensor(self, elements, padding: float = 0.0) -> "NonInlineTensor":
+        """Tensor.apply (Tensors:445-463); ragged input raises ValueError (TensorBuilder.shape, Tensors:78-91)."""
+        if isinstance(elements, np.ndarray):
+            data = np.ascontiguousarray(elements, dtype=F32)
+            shape = list(data.shape)
+        else:
+            shape = _nested_shape(elements)
+            flat: List[float] = []
+            _nested_flatten(elements, flat)
+            data = np.array(flat, dtype=F32)
+        return UploadTensor(self, data.reshape(-1), shape, padding)
+
+    def scalar(self, value, padding: float = 0.0) -> "FillTensor":
+        return FillTensor(self, value, [], padding)
+
+    def fill(self, value, shape, padding: float = 0.0) -> "FillTensor":
+        return FillTensor(self, value, list(shape), padding)
+
+    def random(self, shape, seed: int, padding: float = 0.0) -> "NonInlineTensor":
+        """Tensor.random (Tensors:479-497)."""
+        shape = [int(s) for s in shape]
+        n = int(np.prod(shape, dtype=np.int64))
+
+        def produce():
+            h = C.c_void_p()
+            N.check(N.lib.dls_random(self.ctx, n, seed & 0xFFFFFFFF, C.byref(h), None))
+            return DeviceBuffer(self, h, n)
+        return ProducedTensor(self, produce, shape, padding)
+
+    def random_normal(self, shape, seed: int, padding: float = 0.0) -> "NonInlineTensor":
+        """Tensor.randomNormal (Tensors:500-524)."""
+        shape = [int(s) for s in shape]
+        n = int(np.prod(shape, dtype=np.int64))
+
+        def produce():
+            h = C.c_void_p()
+            N.check(N.lib.dls_random_normal(self.ctx, n, seed & 0xFFFFFFFF, C.byref(h), None))
+            return DeviceBuffer(self, h, n)
+        return ProducedTensor(self, produce, shape, padding)
+
+    def join(self, tensors: Sequence["Tensor"], dimension: Optional[int] = None) -> "Tensor":
+        """Tensor.join (Tensors:560-598): every element is evaluated at the HEAD tensor's shape and written as the new
+        last dimension (Concatenate, KB:632-652); a `dimension` other than the last is a permute of that (Tensors:560-575)."""
+        tensors = list(tensors)
+        head = tensors[0]
+        shape = list(head.shape) + [len(tensors)]
+        roots = [t.closure() for t in tensors]
+        joined = ProducedTensor(self, lambda: self.launch(roots, head.shape), shape, head.padding)
+        if dimension is None or dimension == len(shape) - 1:
+            return joined
+        n = len(shape)
+        perm = [i if i < dimension else (n - 1 if i == dimension else i - 1) for i in range(n)]
+        return joined.permute(perm)
+
+    def abs(self, t): return t._derived(Unary("abs", t.closure()))
+    def sqrt(self, t): return t._derived(Unary("sqrt", t.closure()))
+    def tanh(self, t): return t._derived(Unary("tanh", t.closure()))
+    def exp(self, t): return t._derived(Unary("exp", t.closure()))
+    def log(self, t): return t._derived(Unary("log", t.closure()))
+    def min(self, a, b): return a._binary("min", b)
+    def max(self, a, b): return a._binary("max", b)
+
+
+def _is_seq(a):
+    return isinstance(a, (list, tuple)) or (isinstance(a, np.ndarray) and a.ndim > 0)
+
+
+def _nested_shape(a):
+    if _is_seq(a):
+        if len(a) == 0:
+            return [0]
+        subs = [_nested_shape(x) for x in a]
+        for s in subs[1:]:
+            if s != subs[0]:
+                raise ValueError("ragged nested sequence: %r vs %r" % (subs[0], s))
+        return [len(a)] + subs[0]
+    return []
+
+
+def _nested_flatten(a, out):
+    if _is_seq(a):
+        for x in a:
+            _nested_flatten(x, out)
+    else:
+        out.append(float(a))
+
+
+def auto_broadcast_shape(s1, s2):
+    """Tensors:208-222 -- dims are aligned from the LEFT (unlike numpy)."""
+    out = []
+    for i in range(max(len(s1), len(s2))):
+        if i >= len(s1) or s1[i] == 1:
+            out.append(s2[i])
+        elif i >= len(s2) or s2[i] == 1:
+            out.append(s1[i])
+        elif s1[i] == s2[i]:
+            out.append(s1[i])
+        else:
+            raise ValueError("Failed to automatically broadcast between shape %r and %r" % (list(s1), list(s2)))
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# sealed trait Tensor (Tensors:636-1133) and its five classes (Tensors:602, :1266-1312)
+# ----------------------------------------------------------------------------------------------------------------------
+
+
+class Tensor:
+    backend: Backend
+    shape: List[int]
+    padding: float
+
+    # -- closure / buffer ------------------------------------------------------------------------------------------
+    def closure(self):
+        raise NotImplementedError
+
+    def _buffer(self) -> DeviceBuffer:
+        """doBuffer: the row-major device buffer of this tensor."""
+        raise NotImplementedError
+
+    @property
+    def size(self) -> int:
+        return int(np.prod(self.shape, dtype=np.int64))
+
+    # -- slow actions ----------------------------------------------------------------------------------------------
+    def flat_array(self) -> np.ndarray:
+        """flatArray (Tensors:1099-1118): materialise, then a blocking read-back."""
+        return self.backend.download(self._buffer(), self.size)
+
+    def to_string(self) -> str:
+        """toString (Tensors:776-811)."""
+        return format_tensor(self.shape, self.flat_array())
+
+    __str__ = to_string
+
+    def do_cache(self) -> "CachedTensor":
+        """doCache (Tensors:642-666): pin the materialised buffer."""
+        return CachedTensor(self.backend, self._buffer(), list(self.shape), self.padding)
+
+    def non_inline(self) -> "NonInlineTensor":
+        """nonInline (Tensors:671, :1277-1282)."""
+        return ProducedTensor(self.backend, self._buffer, list(self.shape), self.padding)
+
+    def sum(self) -> "NonInlineTensor":
+        """sum (Tensors:771) = reduce(PlusPrograms) (Tensors:673-766).  The reference always materialises the receiver
+        first (Tensors:678); with `fuse_reductions` an inline receiver is reduced inside the interpreter kernel instead
+        (8 B/element instead of 16 for tanh(a*b+c).sum)."""
+        be = self.backend
+
+        def produce():
+            if be.fuse_reductions and isinstance(self, InlineTensor) and self._live() is None:
+                return be.launch([self.closure()], self.shape, reduce_sum=True)
+            buf = self._buffer()
+            h = C.c_void_p()
+            N.check(N.lib.dls_sum(be.ctx, buf.handle, self.size, None, 0, C.byref(h), None))
+            return DeviceBuffer(be, h, 1)
+        return ProducedTensor(be, produce, [], self.padding)
+
+    # -- views (Tensors:816-1074) ----------------------------------------------------------------------------------
+    def _transform(self, new_shape, matrix1) -> "TransformedTensor":
+        """Tensors:978-1003, the checkpoint rule: a view of a view composes against the ORIGINAL checkpoint; a view of
+        anything else makes the receiver the checkpoint (it is materialised when the consumer runs)."""
+        matrix1 = np.asarray(matrix1, dtype=np.float64)
+        if isinstance(self, TransformedTensor):
+            m = ndat.pre_concatenate(matrix1, self.matrix)
+            return TransformedTensor(self.backend, self.checkpoint, m, list(new_shape), self.padding)
+        return TransformedTensor(self.backend, self, matrix1, list(new_shape), self.padding)
+
+    def broadcast(self, new_shape) -> "Tensor":
+        """Tensors:816-855 (left aligned; a FillTensor stays a FillTensor)."""
+        new_shape = [int(s) for s in new_shape]
+        if new_shape == list(self.shape):
+            return self
+        if isinstance(self, FillTensor):
+            return FillTensor(self.backend, self.value, new_shape, self.padding)
+        n, n_new = len(self.shape), len(new_shape)
+        if n_new < n:
+            raise ValueError("Cannot broadcast %r to %r" % (self.shape, new_shape))
+        m = np.zeros((n, n_new + 1), dtype=np.float64)
+        for i in range(n):
+            if self.shape[i] == new_shape[i]:
+                m[i, i] = 1.0
+            elif self.shape[i] != 1:
+                raise ValueError("Cannot broadcast %r to %r" % (self.shape, new_shape))
+        return self._transform(new_shape, m)
+
+    def reshape(self, new_shape) -> "NonInlineTensor":
+        """Tensors:879-888: same buffer, row-major reinterpretation; materialises the receiver."""
+        new_shape = [int(s) for s in new_shape]
+        if int(np.prod(new_shape, dtype=np.int64)) != self.size:
+            raise ValueError("Cannot reshape %r to %r" % (self.shape, new_shape))
+        return ProducedTensor(self.backend, self._buffer, new_shape, self.padding)
+
+    def scale(self, new_shape) -> "TransformedTensor":
+        """Tensors:950-965: nearest-neighbour resample, coefficient shape_i / newShape_i."""
+        new_shape = [int(s) for s in new_shape]
+        n = len(self.shape)
+        if len(new_shape) != n:
+            raise ValueError("scale: rank mismatch")
+        m = np.zeros((n, n + 1), dtype=np.float64)
+        for i in range(n):
+            m[i, i] = float(self.shape[i]) / float(new_shape[i])
+        return self._transform(new_shape, m)
+
+    def translate(self, offset, new_shape=None) -> "TransformedTensor":
+        """Tensors:970-976: out[g] = in[g - offset], out-of-range reads give the checkpoint's padding."""
+        if len(offset) != len(self.shape):
+            raise ValueError("translate: offset rank mismatch")
+        new_shape = self.shape if new_shape is None else new_shape
+        return self._transform(new_shape, ndat.translate([-float(o) for o in offset]))
+
+    def permute(self, dimensions) -> "TransformedTensor":
+        """Tensors:1008-1025."""
+        n = len(self.shape)
+        if len(dimensions) != n:
+            raise ValueError("permute: rank mismatch")
+        new_shape = [0] * n
+        m = np.zeros((n, n + 1), dtype=np.float64)
+        for new_d, old_d in enumerate(dimensions):
+            new_shape[new_d] = self.shape[old_d]
+            m[old_d, new_d] = 1.0
+        return self._transform(new_shape, m)
+
+    def transpose(self) -> "TransformedTensor":
+        """Tensors:1030."""
+        return self.permute(list(range(len(self.shape) - 1, -1, -1)))
+
+    def split(self, dimension: int) -> List["TransformedTensor"]:
+        """Tensors:1035-1074: slices along `dimension`, each of rank - 1."""
+        n = len(self.shape)
+        new_shape = list(self.shape[:dimension]) + list(self.shape[dimension + 1:])
+        base = np.zeros((n, n), dtype=np.float64)
+        for i in range(dimension):
+            base[i, i] = 1.0
+        for i in range(dimension + 1, n):
+            base[i, i - 1] = 1.0
+        out = []
+        for index in range(self.shape[dimension]):
+            m = base.copy()
+            m[dimension, n - 1] = float(index)
+            out.append(self._transform(new_shape, m))
+        return out
+
+    # -- elementwise operators (Tensors:857-863, :893-945) ------------------------------------------------------------
+    def _derived(self, node) -> "InlineTensor":
+        return InlineTensor(self.backend, node, list(self.shape), self.padding)
+
+    def _binary(self, op, rhs) -> "InlineTensor":
+        rhs = rhs if isinstance(rhs, Tensor) else self.backend.scalar(float(rhs))
+        shape = auto_broadcast_shape(self.shape, rhs.shape)
+        lhs, rhs = self.broadcast(shape), rhs.broadcast(shape)
+        return lhs._derived(Binary(op, lhs.closure(), rhs.closure()))
+
+    def __add__(self, o): return self._binary("add", o)
+    def __sub__(self, o): return self._binary("sub", o)
+    def __mul__(self, o): return self._binary("mul", o)
+    def __truediv__(self, o): return self._binary("div", o)
+    def __mod__(self, o): return self._binary("mod", o)
+    def __neg__(self): return self._derived(Unary("neg", self.closure()))
+    def __pos__(self): return self
+
+
+class InlineTensor(Tensor):
+    """Tensors:1272-1283.  `doBuffer = enqueueClosure(closure, shape).shared`: the buffer is shared while somebody holds
+    it and recomputed afterwards (Compute.scala README:157-166) -- modelled with a weak reference."""
+
+    def __init__(self, backend, node, shape, padding):
+        self.backend, self._node, self.shape, self.padding = backend, node, list(shape), float(padding)
+        self._weak = None
+
+    def closure(self):
+        return self._node
+
+    def _live(self):
+        return self._weak() if self._weak is not None else None
+
+    def _buffer(self):
+        buf = self._live()
+        if buf is None:
+            buf = self.backend.launch([self.closure()], self.shape)
+            self._weak = weakref.ref(buf)
+        return buf
+
+
+class FillTensor(InlineTensor):
+    """Tensors:1266-1269."""
+
+    def __init__(self, backend, value, shape, padding=0.0):
+        self.value = F32(value)
+        super().__init__(backend, Literal(value), shape, padding)
+
+
+class TransformedTensor(InlineTensor):
+    """Tensors:1285-1300."""
+
+    def __init__(self, backend, checkpoint, matrix, shape, padding):
+        rows = len(checkpoint.shape)
+        self.checkpoint = checkpoint
+        self.matrix = np.asarray(matrix, dtype=np.float64).reshape(rows, -1) if rows else np.zeros((0, len(shape) + 1))
+        super().__init__(backend, None, shape, padding)
+
+    def closure(self):
+        if self._node is None:
+            self._node = Xform(self.checkpoint, self.matrix)
+        return self._node
+
+
+class NonInlineTensor(Tensor):
+    """Tensors:1303-1312: closure = Extract(ArrayParameter(id = this))."""
+    _ident = None
+
+    def closure(self):
+        if self._ident is None:
+            self._ident = Ident(self)
+        return self._ident
+
+
+class ProducedTensor(NonInlineTensor):
+    """A NonInlineTensor whose buffer comes from a device producer (`.shared` semantics, see InlineTensor)."""
+
+    def __init__(self, backend, produce, shape, padding):
+        self.backend, self._produce, self.shape, self.padding = backend, produce, list(shape), float(padding)
+        self._weak = None
+
+    def _buffer(self):
+        buf = self._weak() if self._weak is not None else None
+        if buf is None:
+            buf = self._produce()
+            self._weak = weakref.ref(buf)
+        return buf
+
+
+class UploadTensor(NonInlineTensor):
+    """Tensor.apply (Tensors:445-463): host data, uploaded on first use and then kept on the device."""
+
+    def __init__(self, backend, flat, shape, padding):
+        self.backend, self._host, self.shape, self.padding = backend, flat, list(shape), float(padding)
+        self._buf = None
+
+    def _buffer(self):
+        if self._buf is None:
+            self._buf = self.backend.upload(self._host)
+            self._host = None
+        return self._buf
+
+
+class CachedTensor(NonInlineTensor):
+    """Tensors:602: holds its buffer until released."""
+
+    def __init__(self, backend, buf, shape, padding):
+        self.backend, self._buf, self.shape, self.padding = backend, buf, list(shape), float(padding)
+
+    def _buffer(self):
+        if self._buf is None:
+            raise RuntimeError("CachedTensor used after release")
+        return self._buf
+
+    def release(self):
+        """monadicClose of the cached buffer (TW:65-72 releases the old weight buffer this way)."""
+        self._buf = None
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# the `gpu` singleton (gpu.scala:15-27): module-level API bound to a lazily created default Backend
+# ----------------------------------------------------------------------------------------------------------------------
+
+_default: Optional[Backend] = None
+
+
+def default_backend() -> Backend:
+    global _default
+    if _default is None:
+        _default = Backend()
+    return _default
+
+
+def set_default_backend(backend: Optional[Backend]) -> None:
+    global _default
+    _default = backend
+
+
+def tensor(elements, padding: float = 0.0): return default_backend().tensor(elements, padding)
+def scalar(value, padding: float = 0.0): return default_backend().scalar(value, padding)
+def fill(value, shape, padding: float = 0.0): return default_backend().fill(value, shape, padding)
+def random(shape, seed, padding: float = 0.0): return default_backend().random(shape, seed, padding)
+def random_normal(shape, seed, padding: float = 0.0): return default_backend().random_normal(shape, seed, padding)
+def join(tensors, dimension=None): return tensors[0].backend.join(tensors, dimension)
+def abs_(t): return t.backend.abs(t)
+def sqrt(t): return t.backend.sqrt(t)
+def tanh(t): return t.backend.tanh(t)
+def exp(t): return t.backend.exp(t)
+def log(t): return t.backend.log(t)
+def minimum(a, b): return a.backend.min(a, b)
+def maximum(a, b): return a.backend.max(a, b)
+def plan_cache_contains(t): return t.backend.plan_cache_contains(t)
+def as_tensor(x): return x if isinstance(x, Tensor) else scalar(float(x))

@@ -1,0 +1,169 @@
+/* dls_b200.h -- C ABI of libdlsb200.so, the B200 (sm_100a) device layer that replaces
+ * Compute.scala's OpenCL trait + Memory + OpenCLKernelBuilder underneath the `Tensors` trait.
+ *
+ * Citations are file:line into the reference tree:
+ *   OpenCL  = Compute.scala/OpenCL/src/main/scala/com/thoughtworks/compute/OpenCL.scala
+ *   Tensors = Compute.scala/Tensors/src/main/scala/com/thoughtworks/compute/Tensors.scala
+ *   KB      = Compute.scala/OpenCLKernelBuilder/src/main/scala/com/thoughtworks/compute/OpenCLKernelBuilder.scala
+ *   Trees   = Compute.scala/Trees/src/main/scala/com/thoughtworks/compute/Trees.scala
+ *   TW      = plugins-TensorWeights/src/main/scala/com/thoughtworks/deeplearning/plugins/TensorWeights.scala
+ *
+ * Conventions
+ *   - every entry returns an int status (DLS_OK == 0); no exceptions cross the ABI; the message of the last
+ *     failure on the calling thread is dls_last_error() (replaces OpenCL.Exceptions.fromErrorCode, OpenCL:143-312,
+ *     and the program build log, OpenCL:885-915).
+ *   - handles are opaque and reference counted; retain/release are thread safe (replaces clRetain/Release*).
+ *   - all device work is asynchronous on a stream borrowed from the context's pool (replaces `dispatch`,
+ *     OpenCL:1298-1329); ordering between launches is expressed with dls_event dependencies exactly like the
+ *     reference's `waitingEvents` (Tensors:1235, :1246).  Buffers may be released while kernels that use them
+ *     are still in flight (stream-ordered free).
+ *   - plain pointers and sizes only: no torch / C++ types in any signature.
+ *   - there is NO CPU fallback: every compute entry fails with DLS_ERR_NO_DEVICE when no sm_100 device is usable.
+ */
+#ifndef DLS_B200_H
+#define DLS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLS_ABI_VERSION 1
+
+typedef struct dls_ctx dls_ctx;     /* one per device: stream pool, caching allocator, plan cache     */
+typedef struct dls_buf dls_buf;     /* refcounted device buffer of fp32 (OpenCL.DeviceBuffer, OpenCL:633-717) */
+typedef struct dls_event dls_event; /* refcounted completion event (OpenCL.Event, OpenCL:565-612)      */
+
+enum dls_status {
+  DLS_OK = 0,
+  DLS_ERR_INVALID = 1,      /* bad argument / malformed tree (IllegalArgumentException in the reference) */
+  DLS_ERR_NO_DEVICE = 2,    /* no CUDA device / not sm_100 (OpenCL.Exceptions.DeviceNotFound)           */
+  DLS_ERR_OOM = 3,          /* MemObjectAllocationFailure / OutOfResources                               */
+  DLS_ERR_CUDA = 4,         /* any other CUDA runtime error; text in dls_last_error()                    */
+  DLS_ERR_UNSUPPORTED = 5,  /* tree exceeds an interpreter limit (rank > 8, > 65535 leaves, ...)         */
+  DLS_ERR_COMM = 6          /* NCCL failure                                                              */
+};
+
+enum dls_rng_hash {         /* Tensors:98-117 */
+  DLS_HASH_WANG = 0,        /* WangHashingRandomNumberGenerator (the cpu/gpu singletons' default)        */
+  DLS_HASH_LCG = 1          /* LcgRandomNumberGenerator                                                  */
+};
+
+enum dls_gemm_mode {        /* contraction precision for the tensor-core path                            */
+  DLS_GEMM_FP32 = 0,        /* CUDA-core fp32 (bit-comparable with the unrolled elementwise chain)       */
+  DLS_GEMM_TF32 = 1,
+  DLS_GEMM_BF16 = 2
+};
+
+typedef struct dls_ctx_opts {
+  int32_t device;               /* CUDA ordinal (replaces deviceIds / UseAll*Devices, OpenCL:314-374)      */
+  int32_t streams_per_device;   /* replaces numberOfCommandQueuesPerDevice (OpenCL:425; cpu.scala uses 5) */
+  int32_t rng_hash;             /* enum dls_rng_hash                                                       */
+  int32_t gemm_mode;            /* enum dls_gemm_mode                                                      */
+  uint64_t allocator_cap_bytes; /* 0 = unlimited: free blocks cached above this are returned to the driver */
+  int32_t plan_cache_capacity;  /* 0 = default 4096 (replaces kernelCacheBuilder, Tensors:1139-1150)       */
+  int32_t reserved;
+} dls_ctx_opts;
+
+typedef struct dls_stats {
+  uint64_t kernel_launches;     /* kernels of this library launched so far                                 */
+  uint64_t plan_cache_hits;     /* Tensors:1165 kernelCache.getIfPresent hits                              */
+  uint64_t plan_cache_misses;
+  uint64_t bytes_in_use;        /* device bytes held by live dls_buf                                       */
+  uint64_t bytes_cached;        /* device bytes parked in the allocator's free lists                       */
+  uint64_t driver_allocs;       /* cudaMalloc calls (the reference does one clCreateBuffer per launch)     */
+  uint64_t h2d_bytes;
+  uint64_t d2h_bytes;
+} dls_stats;
+
+/* ---- library ------------------------------------------------------------------------------------------ */
+int dls_abi_version(void);
+const char *dls_last_error(void);                 /* thread local; never NULL                              */
+
+/* ---- context: replaces the lazy platform/device/context/queue-pool chain OpenCL:340-374, :1376-1393, :427-438 */
+int dls_ctx_create(const dls_ctx_opts *opts, dls_ctx **out);
+void dls_ctx_destroy(dls_ctx *ctx);               /* replaces the monadicClose chain OpenCL:1335, :443-446, Tensors:1159-1161 */
+int dls_ctx_sync(dls_ctx *ctx);                   /* wait for every stream of the pool                     */
+int dls_ctx_stats(dls_ctx *ctx, dls_stats *out);
+int dls_ctx_trim(dls_ctx *ctx);                   /* return cached free blocks to the driver               */
+void *dls_ctx_stream(dls_ctx *ctx, int index);    /* cudaStream_t of pool slot `index` (for event timing / NCCL plumbing) */
+
+/* ---- buffers: replaces allocateBuffer OpenCL:1399, allocateBufferFrom OpenCL:1415, DeviceBuffer OpenCL:633-717 */
+int dls_buf_alloc(dls_ctx *ctx, size_t n_floats, dls_buf **out);
+int dls_buf_from_host(dls_ctx *ctx, const float *src, size_t n_floats, dls_buf **out, dls_event **done);
+void dls_buf_retain(dls_buf *buf);                /* clRetainMemObject  OpenCL:637 */
+void dls_buf_release(dls_buf *buf);               /* clReleaseMemObject OpenCL:641 */
+size_t dls_buf_length(const dls_buf *buf);        /* floats (DeviceBuffer.length OpenCL:683-686)           */
+void *dls_buf_device_ptr(const dls_buf *buf);     /* raw device pointer (interop with NCCL / torch only)   */
+/* non-blocking read-back: replaces DeviceBuffer.toHostBuffer OpenCL:698-715 + nclEnqueueReadBuffer OpenCL:1224.
+ * `dst` must stay valid until `*done` completes (or pass done == NULL for a blocking read). */
+int dls_buf_read(dls_ctx *ctx, dls_buf *buf, size_t offset, float *dst, size_t n_floats,
+                 dls_event *const *deps, int n_deps, dls_event **done);
+int dls_buf_write(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, size_t n_floats, dls_event **done);
+
+/* page-locked host staging memory: replaces Memory.allocate / MemoryUtil.memAllocFloat (Memory.scala:184-208) for
+ * buffers that feed dls_buf_write / dls_buf_read at full PCIe rate without a bounce copy. */
+int dls_host_alloc(size_t n_floats, float **out);
+void dls_host_free(float *ptr);
+
+/* ---- events: replaces Event.retain/release OpenCL:568-574, waitForComplete OpenCL:603-605, clSetEventCallback OpenCL:1251 */
+void dls_event_retain(dls_event *ev);
+void dls_event_release(dls_event *ev);
+int dls_event_wait(dls_event *ev);
+int dls_event_query(dls_event *ev);               /* DLS_OK when complete, 1 when still running            */
+typedef void (*dls_event_cb)(void *user, int status);
+int dls_event_on_complete(dls_event *ev, dls_event_cb cb, void *user);  /* cb must not call launch APIs (cf. OpenCL:378-392) */
+int dls_event_elapsed_ms(dls_event *start, dls_event *end, float *ms);
+int dls_event_record(dls_ctx *ctx, int stream_index, dls_event **out); /* marker on a pool stream (timing)  */
+
+/* ---- expression trees: replaces enqueueClosure Tensors:1163-1264 (alpha-conversion Trees:266-268, kernelCache lookup
+ * Tensors:1165/:1258, code generation KB:135-221, clBuildProgram OpenCL:917-932, Kernel.enqueue OpenCL:788-844).
+ * `tree` is the serialised closure in wire format v1 (see DESIGN.md "Tree wire format"); `params[i]` is the buffer of
+ * the i-th ArrayParameter in first-visit order (the alpha-normalised numbering of Trees:807-822).
+ * The output buffer is freshly allocated from the caching allocator (`allocateBuffer(shape.product)`, Tensors:1217). */
+enum dls_launch_flags {
+  DLS_LAUNCH_DEFAULT = 0,
+  DLS_LAUNCH_REDUCE_SUM = 1     /* do not materialise: *out is a 1-float buffer holding the sum of all elements */
+};
+int dls_launch_tree(dls_ctx *ctx, const uint8_t *tree, size_t tree_len, dls_buf *const *params, int n_params,
+                    dls_event *const *deps, int n_deps, uint32_t flags, dls_buf **out, dls_event **done);
+/* test back door, replaces `kernelCache.getIfPresent(closure)` (TensorsSpec:48-52) */
+int dls_plan_cache_contains(dls_ctx *ctx, const uint8_t *tree, size_t tree_len, int *found);
+/* describe how a tree lowers (kernel family, program length, leaf modes) into `text` -- diagnostics only */
+int dls_plan_describe(dls_ctx *ctx, const uint8_t *tree, size_t tree_len, char *text, size_t cap);
+
+/* ---- reductions: replaces Tensor.sum = reduce(PlusPrograms) Tensors:673-766 (kernels Tensors:313-392) */
+int dls_sum(dls_ctx *ctx, dls_buf *in, size_t n_floats, dls_event *const *deps, int n_deps, dls_buf **out,
+            dls_event **done);
+/* out[o, i] = sum_k in[o, k, i] over a row-major [outer, k, inner] view: the batch-axis gradient sums that
+ * TensorLayers.sumAs unrolls on the host (TL:124-162) */
+int dls_sum_axis(dls_ctx *ctx, dls_buf *in, size_t outer, size_t k, size_t inner, dls_event *const *deps, int n_deps,
+                 dls_buf **out, dls_event **done);
+
+/* ---- RNG: replaces the `random` / `random_normal` programs Tensors:398-443 and their launches Tensors:479-524 */
+int dls_random(dls_ctx *ctx, size_t n_floats, uint32_t seed, dls_buf **out, dls_event **done);
+int dls_random_normal(dls_ctx *ctx, size_t n_floats, uint32_t seed, dls_buf **out, dls_event **done);
+
+/* ---- weights: fused `data - lr * delta` in place over a weight buffer; replaces (data - delta).doCache + buffer swap
+ * TW:63-72 when the delta is already materialised (gradient arena after the all-reduce). */
+int dls_sgd_update(dls_ctx *ctx, dls_buf *weight, dls_buf *delta, size_t n_floats, float learning_rate,
+                   dls_event *const *deps, int n_deps, dls_event **done);
+
+/* ---- dense contraction C[M,N] = A[M,K] * B[K,N] (row-major, fp32 in/out); the lowering target for the unrolled
+ * matmul trees of TensorsSpec:337-344 / :371-383 and the im2col convolution of TensorsSpec:144-210. */
+int dls_matmul(dls_ctx *ctx, dls_buf *a, dls_buf *b, size_t m, size_t n, size_t k, int transpose_a, int transpose_b,
+               dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done);
+
+/* ---- data-parallel exchange (new functionality: the reference has no collective) */
+int dls_comm_unique_id(uint8_t *id128);                              /* 128-byte NCCL unique id (rank 0)   */
+int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size);
+int dls_allreduce_sum(dls_ctx *ctx, dls_buf *buf, size_t n_floats, dls_event *const *deps, int n_deps,
+                      dls_event **done);
+int dls_comm_destroy(dls_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLS_B200_H */
