@@ -14,18 +14,21 @@ constexpr int kInlineParams = 128;
 
 struct VLeafDev {
   const float *ptr;                    // parameter pointer + base offset
-  long long ls[kMaxVecOuter];
-  int32_t inner;
-  int32_t streaming;
+  uint32_t ls[kMaxVecOuter];           // element stride per collapsed outer dim (0 <= stride < 2^31)
+  uint32_t flags;                      // bit 0: contiguous along the inner dim (128-bit loads), else broadcast along it
+                                       // bit 1: read-once stream (evict-first loads)
+};
+
+struct FastDiv {                       // n / d for n < 2^31: umulhi(n, mul) >> shr   (d == 1: mul == 0)
+  uint32_t d, mul, shr;
 };
 
 struct VecArgs {
   float *out;
-  long long total_tiles;               // float4 tiles
-  long long tiles_per_row;             // ceil(inner / 4)
-  long long n_valid;                   // launch coordinates (tail masking in reduce mode)
-  long long dims[kMaxVecOuter];
-  int32_t v_outer;
+  uint32_t total_tiles;                // float4 tiles (< 2^31)
+  uint32_t tail_valid;                 // valid elements in the last tile (1..4); only a flat launch can be ragged
+  FastDiv tpr;                         // tiles per row = ceil(inner / 4)
+  FastDiv dim1, dim2;                  // extents of collapsed outer dims 1 and 2 (OUTER == 3 only)
   int32_t n_slots;
   int32_t reduce;
   int32_t stream_store;
@@ -80,147 +83,153 @@ __device__ __forceinline__ float apply_binary(int op, float a, float s) {
 // ---- N1 ------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float4 splat(float x) { return make_float4(x, x, x, x); }
 
-#define DLS_V4(expr_x, expr_y, expr_z, expr_w) make_float4(expr_x, expr_y, expr_z, expr_w)
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f) {
+  return f.mul ? __umulhi(n, f.mul) >> f.shr : n;
+}
 
-template <bool IDX32>
+#define DLS_EACH(EXPR)                                                                       \
+  _Pragma("unroll") for (int u = 0; u < kVecUnroll; ++u) {                                   \
+    float4 r_;                                                                               \
+    { const float a = acc[u].x, b = s[u].x; (void)a; (void)b; r_.x = (EXPR); }               \
+    { const float a = acc[u].y, b = s[u].y; (void)a; (void)b; r_.y = (EXPR); }               \
+    { const float a = acc[u].z, b = s[u].z; (void)a; (void)b; r_.z = (EXPR); }               \
+    { const float a = acc[u].w, b = s[u].w; (void)a; (void)b; r_.w = (EXPR); }               \
+    acc[u] = r_;                                                                             \
+  }
+
+#define DLS_EACH1(EXPR)                                                                      \
+  _Pragma("unroll") for (int u = 0; u < kVecUnroll; ++u) {                                   \
+    float4 r_;                                                                               \
+    { const float a = acc[u].x; r_.x = (EXPR); }                                             \
+    { const float a = acc[u].y; r_.y = (EXPR); }                                             \
+    { const float a = acc[u].z; r_.z = (EXPR); }                                             \
+    { const float a = acc[u].w; r_.w = (EXPR); }                                             \
+    acc[u] = r_;                                                                             \
+  }
+
+// OUTER = number of collapsed outer dims the launch has: 0 (flat), 1 (rows x inner) or 3 (up to three outer dims).
+// Every lane owns kVecUnroll float4 tiles per trip, one grid stride apart (coalesced 128-bit accesses); tiles past the
+// end are clamped to the last tile (recomputed, never stored) so that no load needs a predicate.
+template <int OUTER>
 __global__ void __launch_bounds__(kBlock) ew_vec_kernel(const __grid_constant__ VecArgs A) {
   extern __shared__ float4 slot_mem[];  // [slot][unroll][thread]
-  typedef typename std::conditional<IDX32, unsigned int, unsigned long long>::type idx_t;
-  const idx_t total = (idx_t)A.total_tiles;
-  const idx_t tpr = (idx_t)A.tiles_per_row;
-  const idx_t nthreads = (idx_t)gridDim.x * kBlock;
+  const uint32_t total = A.total_tiles;
+  const uint32_t nthreads = gridDim.x * kBlock;
   float tsum = 0.f;
-  for (idx_t t0 = (idx_t)blockIdx.x * kBlock + threadIdx.x; t0 < total; t0 += nthreads * kVecUnroll) {
-    bool valid[kVecUnroll];
-    idx_t c4[kVecUnroll];
-    long long oc[kVecUnroll][kMaxVecOuter];
-    idx_t tile[kVecUnroll];
+  for (uint32_t t0 = blockIdx.x * kBlock + threadIdx.x; t0 < total; t0 += nthreads * kVecUnroll) {
+    uint32_t tile[kVecUnroll], c4[kVecUnroll], r0[kVecUnroll], r1[kVecUnroll], r2[kVecUnroll];
 #pragma unroll
     for (int u = 0; u < kVecUnroll; ++u) {
-      idx_t t = t0 + (idx_t)u * nthreads;
+      const uint32_t t = min(t0 + (uint32_t)u * nthreads, total - 1);
       tile[u] = t;
-      valid[u] = t < total;
-      idx_t row = 0;
-      c4[u] = t;
-      if (A.v_outer > 0) {
-        row = t / tpr;
-        c4[u] = t - row * tpr;
-      }
-      oc[u][0] = oc[u][1] = oc[u][2] = 0;
-      if (A.v_outer == 1) {
-        oc[u][0] = (long long)row;
-      } else if (A.v_outer == 2) {
-        idx_t q = row / (idx_t)A.dims[1];
-        oc[u][1] = (long long)(row - q * (idx_t)A.dims[1]);
-        oc[u][0] = (long long)q;
-      } else if (A.v_outer == 3) {
-        idx_t q = row / (idx_t)A.dims[2];
-        oc[u][2] = (long long)(row - q * (idx_t)A.dims[2]);
-        idx_t q2 = q / (idx_t)A.dims[1];
-        oc[u][1] = (long long)(q - q2 * (idx_t)A.dims[1]);
-        oc[u][0] = (long long)q2;
+      r0[u] = r1[u] = r2[u] = 0;
+      if (OUTER == 0) {
+        c4[u] = t;
+      } else {
+        const uint32_t row = fast_div(t, A.tpr);
+        c4[u] = t - row * A.tpr.d;
+        if (OUTER == 1) {
+          r0[u] = row;
+        } else {
+          const uint32_t q = fast_div(row, A.dim2);
+          r2[u] = row - q * A.dim2.d;
+          const uint32_t q2 = fast_div(q, A.dim1);
+          r1[u] = q - q2 * A.dim1.d;
+          r0[u] = q2;
+        }
       }
     }
     float4 acc[kVecUnroll];
-#pragma unroll
-    for (int u = 0; u < kVecUnroll; ++u) acc[u] = splat(0.f);
 
-    auto fetch_leaf = [&](unsigned int li, float4 *dst) {
+    // element offsets are 32-bit (the host only picks this kernel when every leaf spans < 2^32 floats): one IMAD for
+    // the offset, one IMAD.WIDE for the address, one LDG.128
+    auto fetch_leaf = [&](uint32_t li, float4 *dst) {
       const VLeafDev &L = A.leaves[li];
+      const bool contiguous = (L.flags & 1u) != 0;
 #pragma unroll
       for (int u = 0; u < kVecUnroll; ++u) {
-        dst[u] = splat(0.f);
-        if (!valid[u]) continue;
-        const float *p = L.ptr + oc[u][0] * L.ls[0] + oc[u][1] * L.ls[1] + oc[u][2] * L.ls[2];
-        if (L.inner) {
-          const float4 *q = reinterpret_cast<const float4 *>(p) + c4[u];
-          dst[u] = L.streaming ? __ldcs(q) : __ldg(q);
-        } else {
-          dst[u] = splat(__ldg(p));
-        }
+        uint32_t off = contiguous ? c4[u] * 4u : 0u;
+        if (OUTER >= 1) off += r0[u] * L.ls[0];
+        if (OUTER == 3) off += r1[u] * L.ls[1] + r2[u] * L.ls[2];
+        const float *p = L.ptr + off;
+        if (contiguous) dst[u] = __ldg(reinterpret_cast<const float4 *>(p));
+        else dst[u] = splat(__ldg(p));
       }
     };
 
     for (int pc = 0;; ++pc) {
-      const Instr in = A.code[pc];
+      // one 64-bit constant-bank load per instruction: {op:8, src:8, aux:16, operand:32}
+      const uint2 w = reinterpret_cast<const uint2 *>(A.code)[pc];
+      Instr in;
+      in.op = (uint8_t)(w.x & 0xffu);
+      in.src = (uint8_t)((w.x >> 8) & 0xffu);
+      in.aux = (uint16_t)(w.x >> 16);
+      in.operand = w.y;
       const int op = in.op;
       if (op == OP_END) break;
-      float4 s[kVecUnroll];
+      if (op >= OP_NEG && op <= OP_LOG) {
+        switch (op) {
+          case OP_NEG: DLS_EACH1(-a) break;
+          case OP_ABS: DLS_EACH1(fabsf(a)) break;
+          case OP_SQRT: DLS_EACH1(__fsqrt_rn(a)) break;
+          case OP_TANH: DLS_EACH1(tanhf(a)) break;
+          case OP_EXP: DLS_EACH1(expf(a)) break;
+          default: DLS_EACH1(logf(a)) break;
+        }
+        continue;
+      }
+      if (op == OP_SAVE) {
 #pragma unroll
-      for (int u = 0; u < kVecUnroll; ++u) s[u] = splat(0.f);
+        for (int u = 0; u < kVecUnroll; ++u) slot_mem[(in.operand * kVecUnroll + u) * kBlock + threadIdx.x] = acc[u];
+        continue;
+      }
+      float4 s[kVecUnroll];
       if (in.src == SRC_LEAF) {
         fetch_leaf(in.operand, s);
       } else if (in.src == SRC_LIT) {
 #pragma unroll
         for (int u = 0; u < kVecUnroll; ++u) s[u] = splat(__uint_as_float(in.operand));
-      } else if (in.src == SRC_SLOT) {
+      } else {
 #pragma unroll
         for (int u = 0; u < kVecUnroll; ++u) s[u] = slot_mem[(in.operand * kVecUnroll + u) * kBlock + threadIdx.x];
       }
-#define DLS_EACH(EXPR)                                                                 \
-  _Pragma("unroll") for (int u = 0; u < kVecUnroll; ++u) {                             \
-    float4 r_;                                                                         \
-    { const float a = acc[u].x, b = s[u].x; (void)a; (void)b; r_.x = (EXPR); }                           \
-    { const float a = acc[u].y, b = s[u].y; (void)a; (void)b; r_.y = (EXPR); }                           \
-    { const float a = acc[u].z, b = s[u].z; (void)a; (void)b; r_.z = (EXPR); }                           \
-    { const float a = acc[u].w, b = s[u].w; (void)a; (void)b; r_.w = (EXPR); }                           \
-    acc[u] = r_;                                                                       \
-  }
-      // the switch is on a grid-uniform value: one indirect branch per instruction, then straight-line lanes
-      if (op <= OP_LOG) {
-        switch (op) {
-          case OP_LOAD: DLS_EACH(b) break;
-          case OP_ADD: DLS_EACH(__fadd_rn(a, b)) break;
-          case OP_SUB: DLS_EACH(__fsub_rn(a, b)) break;
-          case OP_MUL: DLS_EACH(__fmul_rn(a, b)) break;
-          case OP_DIV: DLS_EACH(__fdiv_rn(a, b)) break;
-          case OP_MOD: DLS_EACH(fmodf(a, b)) break;
-          case OP_MIN: DLS_EACH(fminf(a, b)) break;
-          case OP_MAX: DLS_EACH(fmaxf(a, b)) break;
-          case OP_RSUB: DLS_EACH(__fsub_rn(b, a)) break;
-          case OP_RDIV: DLS_EACH(__fdiv_rn(b, a)) break;
-          case OP_RMOD: DLS_EACH(fmodf(b, a)) break;
-          case OP_NEG: DLS_EACH(-a) break;
-          case OP_ABS: DLS_EACH(fabsf(a)) break;
-          case OP_SQRT: DLS_EACH(__fsqrt_rn(a)) break;
-          case OP_TANH: DLS_EACH(tanhf(a)) break;
-          case OP_EXP: DLS_EACH(expf(a)) break;
-          default: DLS_EACH(logf(a)) break;
-        }
-      } else if (op == OP_SAVE) {
-#pragma unroll
-        for (int u = 0; u < kVecUnroll; ++u) slot_mem[(in.operand * kVecUnroll + u) * kBlock + threadIdx.x] = acc[u];
-      } else {  // OP_MAC / OP_MSUB
+      if (op >= OP_MAC) {  // OP_MAC / OP_MSUB: acc +- leaf[aux] * src, two roundings
         float4 f[kVecUnroll];
         fetch_leaf(in.aux, f);
 #pragma unroll
-        for (int u = 0; u < kVecUnroll; ++u) {
-          float4 p = DLS_V4(__fmul_rn(f[u].x, s[u].x), __fmul_rn(f[u].y, s[u].y), __fmul_rn(f[u].z, s[u].z),
-                            __fmul_rn(f[u].w, s[u].w));
-          acc[u] = op == OP_MAC ? DLS_V4(__fadd_rn(acc[u].x, p.x), __fadd_rn(acc[u].y, p.y), __fadd_rn(acc[u].z, p.z),
-                                         __fadd_rn(acc[u].w, p.w))
-                                : DLS_V4(__fsub_rn(acc[u].x, p.x), __fsub_rn(acc[u].y, p.y), __fsub_rn(acc[u].z, p.z),
-                                         __fsub_rn(acc[u].w, p.w));
-        }
+        for (int u = 0; u < kVecUnroll; ++u)
+          s[u] = make_float4(__fmul_rn(f[u].x, s[u].x), __fmul_rn(f[u].y, s[u].y), __fmul_rn(f[u].z, s[u].z),
+                             __fmul_rn(f[u].w, s[u].w));
+        if (op == OP_MAC) { DLS_EACH(__fadd_rn(a, b)) } else { DLS_EACH(__fsub_rn(a, b)) }
+        continue;
+      }
+      switch (op) {  // grid-uniform: one branch per instruction, then straight-line lanes
+        case OP_LOAD: DLS_EACH(b) break;
+        case OP_ADD: DLS_EACH(__fadd_rn(a, b)) break;
+        case OP_SUB: DLS_EACH(__fsub_rn(a, b)) break;
+        case OP_MUL: DLS_EACH(__fmul_rn(a, b)) break;
+        case OP_DIV: DLS_EACH(__fdiv_rn(a, b)) break;
+        case OP_MOD: DLS_EACH(fmodf(a, b)) break;
+        case OP_MIN: DLS_EACH(fminf(a, b)) break;
+        case OP_MAX: DLS_EACH(fmaxf(a, b)) break;
+        case OP_RSUB: DLS_EACH(__fsub_rn(b, a)) break;
+        case OP_RDIV: DLS_EACH(__fdiv_rn(b, a)) break;
+        default: DLS_EACH(fmodf(b, a)) break;  // OP_RMOD
       }
     }
 
 #pragma unroll
     for (int u = 0; u < kVecUnroll; ++u) {
-      if (!valid[u]) continue;
+      const bool live = t0 + (uint32_t)u * nthreads < total;   // clamped duplicates contribute nothing
       if (A.reduce) {
-        // only a rank-collapsed launch (v_outer == 0) can have a ragged last tile
-        long long first = (long long)tile[u] * 4;
-        long long left = A.v_outer == 0 ? A.n_valid - first : 4;
+        const uint32_t left = tile[u] == total - 1 ? A.tail_valid : 4u;
         float part = acc[u].x;
         if (left > 1) part += acc[u].y;
         if (left > 2) part += acc[u].z;
         if (left > 3) part += acc[u].w;
-        tsum += part;
-      } else {
-        float4 *q = reinterpret_cast<float4 *>(A.out) + tile[u];
-        if (A.stream_store) __stcs(q, acc[u]);
-        else *q = acc[u];
+        if (live) tsum += part;
+      } else if (live) {
+        reinterpret_cast<float4 *>(A.out)[tile[u]] = acc[u];
       }
     }
   }
@@ -331,9 +340,10 @@ int query_ew_occupancy(dls_ctx *ctx) {
   int b = 0;
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<true>, kBlock, 0));
+  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<1>, kBlock, 0));
   ctx->vec_blocks_per_sm = b > 0 ? b : 1;
   DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_gather_kernel<true>, kBlock, 0));
   ctx->gather_blocks_per_sm = b > 0 ? b : 1;
@@ -369,14 +379,31 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
   ReduceArgs red{ctx->red_partials[stream], ctx->red_counter[stream], out->ptr};
   if (P.kind == PLAN_VEC) {
     static thread_local VecArgs A;
+    auto mk_div = [](long long d) {
+      FastDiv f;
+      f.d = (uint32_t)d;
+      if (d <= 1) {
+        f.mul = 0;
+        f.shr = 0;
+      } else {
+        int lg = 0;
+        while ((1ll << lg) < d) ++lg;
+        const int p = 31 + lg;
+        f.mul = (uint32_t)((((unsigned long long)1 << p) + (unsigned long long)d - 1) / (unsigned long long)d);
+        f.shr = (uint32_t)(p - 32);
+      }
+      return f;
+    };
     A.out = out->ptr;
-    A.tiles_per_row = (P.v_inner + 3) / 4;
+    const long long tpr = (P.v_inner + 3) / 4;
     long long rows = 1;
     for (int j = 0; j < P.v_outer; ++j) rows *= P.v_dims[j];
-    A.total_tiles = rows * A.tiles_per_row;
-    A.n_valid = P.n_elems;
-    for (int j = 0; j < kMaxVecOuter; ++j) A.dims[j] = P.v_dims[j];
-    A.v_outer = P.v_outer;
+    const long long total_tiles = rows * tpr;
+    A.total_tiles = (uint32_t)total_tiles;
+    A.tail_valid = (uint32_t)(P.v_inner - (tpr - 1) * 4);
+    A.tpr = mk_div(tpr);
+    A.dim1 = mk_div(P.v_dims[1]);
+    A.dim2 = mk_div(P.v_dims[2]);
     A.n_slots = P.n_slots;
     A.reduce = reduce_sum ? 1 : 0;
     A.stream_store = (size_t)P.n_elems * 4 > (size_t)64 << 20;
@@ -384,26 +411,25 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
     for (size_t l = 0; l < P.vleaves.size(); ++l) {
       const VLeaf &V = P.vleaves[l];
       A.leaves[l].ptr = params[V.param]->ptr + V.base;
-      for (int j = 0; j < kMaxVecOuter; ++j) A.leaves[l].ls[j] = V.ls[j];
-      A.leaves[l].inner = V.inner;
-      A.leaves[l].streaming = V.streaming;
+      for (int j = 0; j < kMaxVecOuter; ++j) A.leaves[l].ls[j] = (uint32_t)V.ls[j];
+      A.leaves[l].flags = (V.inner ? 1u : 0u) | (V.streaming ? 2u : 0u);
     }
     memcpy(A.code, P.code.data(), P.code.size() * sizeof(Instr));
     size_t smem = (size_t)P.n_slots * kVecUnroll * kBlock * sizeof(float4);
     int per_sm = ctx->vec_blocks_per_sm;
     if (smem) {
       int b = 0;
-      DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<true>, kBlock, smem));
+      DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<1>, kBlock, smem));
       per_sm = b > 0 ? b : 1;
     }
-    long long want = (A.total_tiles + (long long)kBlock * kVecUnroll - 1) / ((long long)kBlock * kVecUnroll);
+    long long want = (total_tiles + (long long)kBlock * kVecUnroll - 1) / ((long long)kBlock * kVecUnroll);
     long long cap = (long long)ctx->sm_count * per_sm;
     if (reduce_sum && cap > kReduceMaxBlocks) cap = kReduceMaxBlocks;
     int grid = (int)std::min<long long>(want, cap);
-    if (A.total_tiles < (1ll << 31) - (long long)cap * kBlock * kVecUnroll)
-      ew_vec_kernel<true><<<grid, kBlock, smem, st>>>(A);
-    else
-      ew_vec_kernel<false><<<grid, kBlock, smem, st>>>(A);
+    // a 3-outer launch with leading extents of 1 was collapsed on the host: v_outer is 0, 1, 2 or 3
+    if (P.v_outer == 0) ew_vec_kernel<0><<<grid, kBlock, smem, st>>>(A);
+    else if (P.v_outer == 1) ew_vec_kernel<1><<<grid, kBlock, smem, st>>>(A);
+    else ew_vec_kernel<3><<<grid, kBlock, smem, st>>>(A);
   } else {
     DLS_CHECK(P.n_params <= kInlineParams, DLS_ERR_UNSUPPORTED, "more than 128 distinct parameters in one gather tree");
     int rc = upload_tables(P);

@@ -575,6 +575,7 @@ int Lowering::choose_kernel() {
     if (k > kMaxVecOuter + 1) vec_ok = false;
     const long long W = k ? ext[k - 1] : 1;
     if (vec_ok && k > 1 && (W % 4) != 0) vec_ok = false;
+    if (vec_ok && (P.n_elems / (W ? W : 1)) * ((W + 3) / 4) >= (1ll << 31) - (1ll << 24)) vec_ok = false;  // 32-bit tile ids
     if (vec_ok) {
       P.vleaves.clear();
       for (size_t l = 0; l < leaves.size() && vec_ok; ++l) {
@@ -593,8 +594,14 @@ int Lowering::choose_kernel() {
           V.ls[j] = st[l][j];
           if (V.ls[j] == 0) V.streaming = 0;
           if (V.inner && (V.ls[j] % 4) != 0) vec_ok = false;
+          if (V.ls[j] < 0 || V.ls[j] >= (1ll << 31)) vec_ok = false;  // the vector kernel uses 32-bit strides
         }
         if (V.inner && (V.base % 4) != 0) vec_ok = false;
+        {  // 32-bit element offsets inside the kernel: the farthest element a leaf touches must stay below 2^32
+          long long far = V.inner ? W : 0;
+          for (int j = 0; j + 1 < k; ++j) far += (ext[j] - 1) * V.ls[j];
+          if (far >= (1ll << 32)) vec_ok = false;
+        }
         P.vleaves.push_back(V);
       }
     }

@@ -213,6 +213,19 @@ def _fmod(a, b):
         return np.fmod(a, b).astype(F32)
 
 
+def _fmin(a, b):
+    """C fmin (KB:271-280) with -0 < +0 (IEEE 754-2019 minimum); the reference leaves the zero-sign case to its libm."""
+    out = np.fmin(a, b).astype(F32)
+    both_zero = (a == 0) & (b == 0)
+    return np.where(both_zero & (np.signbit(a) | np.signbit(b)), F32(-0.0), out).astype(F32)
+
+
+def _fmax(a, b):
+    out = np.fmax(a, b).astype(F32)
+    both_zero = (a == 0) & (b == 0)
+    return np.where(both_zero & ~(np.signbit(a) & np.signbit(b)), F32(0.0), out).astype(F32)
+
+
 _UNARY = {
     "neg": lambda a: (-a).astype(F32),
     "abs": lambda a: np.abs(a).astype(F32),
@@ -227,8 +240,8 @@ _BINARY = {
     "mul": lambda a, b: (a * b).astype(F32),
     "div": lambda a, b: (a / b).astype(F32),
     "mod": _fmod,
-    "min": lambda a, b: np.fmin(a, b).astype(F32),
-    "max": lambda a, b: np.fmax(a, b).astype(F32),
+    "min": _fmin,
+    "max": _fmax,
 }
 
 

@@ -78,7 +78,8 @@ def test_ragged_tail_lengths(backends, n):
     a, b = rnd(7, n), rnd(8, n)
 
     def build(M):
-        return (M.tensor(a) * M.tensor(b) - M.tensor(a)) / (M.tensor(b) * M.tensor(b) + M.scalar(1.0))
+        # fill, not scalar: `[1] + []` raises in the reference too (autoBroadcastShape indexes shape2(0), Tensors:208-222)
+        return (M.tensor(a) * M.tensor(b) - M.tensor(a)) / (M.tensor(b) * M.tensor(b) + M.fill(1.0, [n]))
     want, got, _ = both(backends, build)
     assert_bits(want, got)
 
@@ -239,6 +240,13 @@ def test_matmul_by_broadcast_and_unrolled_sum(backends):
     np.testing.assert_allclose(got.reshape(12, 8), a @ b, rtol=1e-4, atol=1e-5)
 
 
+def test_size_one_dim_against_scalar_raises_like_the_reference(backends):
+    # Tensors:208-222: shape1(i) == 1 sends the lookup to shape2(i), which does not exist for a rank-0 operand
+    for M in backends:
+        with pytest.raises(IndexError):
+            M.tensor([2.0]) + M.scalar(1.0)
+
+
 def test_empty_tensor(backends):
     want, got, _ = both(backends, lambda M: M.tensor([]) + M.scalar(1.0))
     assert want.size == 0 and got.size == 0
@@ -294,7 +302,9 @@ def test_random_normal_close(backends, n, seed):
     O, B = backends
     want = np.asarray(O.random_normal([n], seed).flat_array())
     got = B.random_normal([n], seed).flat_array()
-    ok = (ulp_diff(want, got) <= 4) | (np.abs(want - got) <= 2e-6) | (np.isinf(want) & np.isinf(got))
+    with np.errstate(invalid="ignore"):
+        ok = (ulp_diff(want, got) <= 4) | (np.abs(want - got) <= 2e-6) | (np.isinf(want) & np.isinf(got))
+    ok |= np.isnan(want) & np.isnan(got)          # u1 == 0 is not guarded by the reference (Tensors:409-425)
     assert ok.all(), (want[~ok][:5], got[~ok][:5])
 
 
