@@ -29,6 +29,25 @@ BYTES_MAP, BYTES_SUM = 12, 4                 # algorithmic bytes per element (SU
 METRIC = "fused elementwise + reduce HBM throughput (tanh(a*b+c) materialised, then sum)"
 
 
+def config_dict(rows):
+    n = rows * COLS
+    return {"workload": "C2: y = tanh(a*b+c) materialised (c broadcast per row), then y.sum; a,b = %dx%d fp32 per GPU" % (rows, COLS),
+            "elements_per_gpu": n, "algorithmic_bytes_per_element": BYTES_MAP + BYTES_SUM,
+            "l2": "inputs (2 x %.2f GiB) and output exceed the 126 MB L2, no flush needed" % (n * 4 / 2 ** 30),
+            "rng": "reference Wang-hash uniform mapped to [-2,2), seeds 1,2,3", "parallelism": "independent shard per GPU"}
+
+
+def load_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture (profiles/summarise.py); None when no capture exists for this build."""
+    path = os.path.join(ROOT, "profiles", "r1_c2_traffic.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["ew_vec_kernel<1>"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -158,7 +177,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2 tanh(a*b+c) row-broadcast + sum, 2^28 fp32 (CPU arm: bounded sample)"},
+        "config": dict(config_dict(ROWS), cpu_sample=sample),
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference's own CPU path (Compute.scala on a CPU OpenCL device) is unavailable on this box (no JVM, "
@@ -306,16 +325,13 @@ def main():
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2: y = tanh(a*b+c) materialised (c broadcast per row), then y.sum; a,b = %dx%d fp32 per GPU"
-                               % (rows, COLS), "elements_per_gpu": n, "algorithmic_bytes_per_element": BYTES_MAP + BYTES_SUM,
-                   "l2": "inputs (2 x %.2f GiB) and output exceed the 126 MB L2, no flush needed" % (n * 4 / 2 ** 30),
-                   "rng": "reference Wang-hash uniform mapped to [-2,2), seeds 1,2,3", "parallelism": "independent shard per GPU"},
+        "config": config_dict(rows),
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": (2 * n + rows) * 4, "d2h_bytes_per_step": 4,
                 "steps": args.e2e_steps, "ms_per_step": e2e_ms / args.e2e_steps},
         "gpu_launches": launches,
         "roofline": {"kernel": "ew_vec_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "ms_per_launch": ms_map,
+                     "frac": achieved / peak, "traffic": load_traffic() if rows == ROWS else None, "peak_source": peak_src, "ms_per_launch": ms_map,
                      "algorithmic_bytes_per_launch": n * BYTES_MAP},
         "kernels": {"sum_kernel": {"ms": ms_sum, "gbs": n * BYTES_SUM / (ms_sum / 1e3) / 1e9, "frac": n * BYTES_SUM / (ms_sum / 1e3) / 1e9 / peak},
                     "ew_vec_kernel+reduce (fused tanh(a*b+c).sum)": {"ms": ms_fused, "gbs": n * 8 / (ms_fused / 1e3) / 1e9,
