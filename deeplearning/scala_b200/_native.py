@@ -35,6 +35,10 @@ class CtxOpts(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class GemmOpts(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("bias_mode", C.c_int32), ("activation", C.c_int32), ("reserved", C.c_int32)]
+
+
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("kernel_launches", "plan_cache_hits", "plan_cache_misses", "bytes_in_use",
                                           "bytes_cached", "driver_allocs", "h2d_bytes", "d2h_bytes")]
@@ -83,6 +87,8 @@ _SIG = {
     "dls_random_normal": (C.c_int, [_P, C.c_size_t, C.c_uint32, _PP, _PP]),
     "dls_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _PP, C.c_int, _PP]),
     "dls_matmul": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, _PP, C.c_int, _PP, _PP]),
+    "dls_matmul_ex": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
+                                C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),
     "dls_comm_unique_id": (C.c_int, [C.c_char_p]),
     "dls_comm_init": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_int]),
     "dls_allreduce_sum": (C.c_int, [_P, _P, C.c_size_t, _PP, C.c_int, _PP]),

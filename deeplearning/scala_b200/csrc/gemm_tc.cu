@@ -1,0 +1,512 @@
+// gemm_tc.cu -- N4: dense contraction on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands
+// staged by TMA), hand-written for sm_100a.  D[M,N] (fp32, row-major) = A * B with BF16 or TF32 operands and fp32
+// accumulation, plus an optional fused epilogue (bias along rows or columns, tanh / relu).
+//
+// This is the lowering target for the contractions the reference can only express as host-unrolled elementwise trees:
+// the two matmul formulations of TensorsSpec:337-344 / :371-383, the im2col convolution of TensorsSpec:144-210 and the
+// weight-gradient sums of TensorLayers.sumAs (TL:124-162).  There is nothing comparable in the reference's device layer.
+//
+// Kernel anatomy (one persistent CTA per SM, 192 threads):
+//   warp 0, lane 0 : TMA producer   -- cp.async.bulk.tensor.2d into a 4-stage ring of 128B-swizzled smem tiles
+//   warp 1, lane 0 : MMA issuer     -- tcgen05.mma.cta_group::1 (M=128, N=256, K=32 bytes per instruction), commit -> mbarrier
+//   warps 2..5     : epilogue       -- tcgen05.ld (32 lanes x 32 columns) -> registers -> swizzled smem -> TMA store
+// Two 256-column accumulators (all 512 TMEM columns) are double buffered, so the epilogue of tile i overlaps the main
+// loop of tile i+1.  Operands may be K-major ([rows][K], K contiguous) or MN-major ([K][rows], rows contiguous): the
+// major-ness only changes the TMA boxes and the UMMA shared-memory descriptors, never the data in HBM.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.h"
+#include "gemm_tc.h"
+
+namespace dls {
+
+namespace tc {
+
+constexpr int BM = 128;              // UMMA M (one TMEM lane per output row)
+constexpr int BN = 256;              // UMMA N (one TMEM column per output column)
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = BM * 128;
+constexpr int B_STAGE_BYTES = BN * 128;
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;   // 48 KiB
+constexpr int EPI_WARPS = 4;
+constexpr int EPI_CHUNK = 32;                                // columns per tcgen05.ld / TMA-store box
+constexpr int EPI_BUF_BYTES = 32 * EPI_CHUNK * 4;            // one warp's 32 rows x 32 fp32 columns
+constexpr int EPI_BYTES = EPI_WARPS * 2 * EPI_BUF_BYTES;     // double buffered per warp: 32 KiB
+constexpr int NUM_THREADS = 32 * (2 + EPI_WARPS);
+constexpr int BAR_BYTES = 256;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // + slack for 1 KiB alignment
+constexpr int TMEM_COLS = 512;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Spin on the phase parity; a wait that lasts seconds can only be a protocol bug, so trap instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  long long t0 = 0;
+  for (uint32_t spins = 0;; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if ((spins & 0xFFF) == 0xFFF) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 8000000000LL) __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
+
+__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate,
+                                     bool tf32) {
+  if (tf32) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// UMMA shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout): start address, leading / stride byte
+// offsets in 16-byte units, version 1 (Blackwell), layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+struct Tile {
+  int m0, n0;
+};
+// Grouped raster: 8 tile-rows share their B tiles through L2 while the group sweeps N.
+__device__ __forceinline__ Tile tile_coord(int t, int tiles_m, int tiles_n) {
+  constexpr int GROUP = 8;
+  const int per_group = GROUP * tiles_n;
+  const int g = t / per_group;
+  const int first_m = g * GROUP;
+  const int gsz = min(GROUP, tiles_m - first_m);
+  const int r = t - g * per_group;
+  Tile c;
+  c.m0 = (first_m + r % gsz) * BM;
+  c.n0 = (r / gsz) * BN;
+  return c;
+}
+
+template <bool TF32, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+    gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
+                   const float *__restrict__ bias, int bias_mode, int act, int direct_store) {
+  constexpr int ELEM = TF32 ? 4 : 2;
+  constexpr int BLOCK_K = 128 / ELEM;       // one 128-byte swizzle row of K per stage
+  constexpr int UMMA_K = 32 / ELEM;         // K per tcgen05.mma
+  constexpr int MN_ATOM = 128 / ELEM;       // rows covered by one 128-byte line of an MN-major operand
+  static_assert(!(TF32 && (A_MN || B_MN)), "TF32 operands are K-major only (MN-major fp32 needs the 32B-atom swizzle)");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t *epi_smem = smem + STAGES * STAGE_BYTES;
+  uint64_t *bars = (uint64_t *)(epi_smem + EPI_BYTES);
+  // bars[0..S) full, [S..2S) empty, [2S..2S+2) tmem_full, [2S+2..2S+4) tmem_empty, then the TMEM base address
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * STAGES + 2 + s); };
+  uint32_t *tmem_slot = (uint32_t *)(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
+  const int n_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), EPI_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const Tile tc = tile_coord(t, tiles_m, tiles_n);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t a_dst = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t b_dst = a_dst + A_STAGE_BYTES;
+          mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+          const int k0 = kb * BLOCK_K;
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / MN_ATOM; ++j)
+              tma_load_2d(a_dst + j * BLOCK_K * 128, &map_a, full_bar(stage), tc.m0 + j * MN_ATOM, k0);
+          } else {
+            tma_load_2d(a_dst, &map_a, full_bar(stage), k0, tc.m0);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / MN_ATOM; ++j)
+              tma_load_2d(b_dst + j * BLOCK_K * 128, &map_b, full_bar(stage), tc.n0 + j * MN_ATOM, k0);
+          } else {
+            tma_load_2d(b_dst, &map_b, full_bar(stage), k0, tc.n0);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      // instruction descriptor (cute::UMMA::InstrDescriptor): D = fp32, A/B format, major-ness, N >> 3, M >> 4
+      const uint32_t fmt = TF32 ? 2u : 1u;
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      // K-major: 8-row groups are 1024 B apart (SBO), one swizzle atom along K (LBO unused).
+      // MN-major: 8 K-rows of 128 B form an atom (SBO = 1024 B), atoms along MN are BLOCK_K * 128 B apart (LBO).
+      const uint32_t a_lbo = A_MN ? BLOCK_K * 128 : 0, b_lbo = B_MN ? BLOCK_K * 128 : 0;
+      const uint32_t a_kstep = A_MN ? UMMA_K * 128 : 32, b_kstep = B_MN ? UMMA_K * 128 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
+            umma(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u, TF32);
+          }
+          umma_commit(empty_bar(stage));   // frees the smem slot once these MMAs have read it
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(tfull_bar(as));        // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===== epilogue warps: TMEM lane quarter = warp % 4 =====
+    const int quarter = warp & 3;
+    uint8_t *my_smem = epi_smem + (warp - 2) * 2 * EPI_BUF_BYTES;
+    int it = 0;
+    int buf = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      const Tile tc = tile_coord(t, tiles_m, tiles_n);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(tfull_bar(as), aphase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row = tc.m0 + quarter * 32 + lane;
+      float row_bias = 0.f;
+      if (bias_mode == 1 && row < M) row_bias = __ldg(bias + row);
+#pragma unroll 1
+      for (int c = 0; c < BN / EPI_CHUNK; ++c) {
+        const int col0 = tc.n0 + c * EPI_CHUNK;
+        if (col0 >= N) break;                                     // warp uniform
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN + c * EPI_CHUNK);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+              "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+              "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+              "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr)
+            : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = __uint_as_float(v[j]);
+          if (bias_mode == 1) x = __fadd_rn(x, row_bias);
+          else if (bias_mode == 2) x = __fadd_rn(x, (col0 + j < N) ? __ldg(bias + col0 + j) : 0.f);
+          if (act == 1) x = tanhf(x);
+          else if (act == 2) x = fmaxf(x, 0.f);
+          f[j] = x;
+        }
+        if (direct_store) {
+          if (row < M) {
+            float *dst = C + (long long)row * ldc + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < N) dst[j] = f[j];
+          }
+        } else {
+          // the TMA store that last read this staging buffer must have finished reading it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          uint8_t *sb = my_smem + buf * EPI_BUF_BYTES + lane * 128;   // 128B-swizzled: 16 B chunk j -> j ^ (row % 8)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 q = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+            *reinterpret_cast<float4 *>(sb + ((j ^ (lane & 7)) << 4)) = q;
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&map_c, smem_u32(my_smem + buf * EPI_BUF_BYTES), col0, tc.m0 + quarter * 32);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          buf ^= 1;
+        }
+      }
+      // all of this warp's TMEM reads of accumulator `as` are complete: hand it back to the MMA issuer
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(as));
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---- fp32 -> bf16 operand staging ------------------------------------------------------------------------------------
+// [rows, cols] fp32 (dense) -> [rows, pitch] bf16 with pitch a multiple of 8 elements so every row starts 16-byte
+// aligned (a TMA requirement).  Round to nearest even.
+__global__ void __launch_bounds__(256) to_bf16_flat_kernel(const float4 *__restrict__ in, uint4 *__restrict__ out, size_t n8) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 a = __ldcs(in + 2 * i), b = __ldcs(in + 2 * i + 1);
+    __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
+    __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
+    uint4 o;
+    o.x = *reinterpret_cast<uint32_t *>(&p0);
+    o.y = *reinterpret_cast<uint32_t *>(&p1);
+    o.z = *reinterpret_cast<uint32_t *>(&p2);
+    o.w = *reinterpret_cast<uint32_t *>(&p3);
+    out[i] = o;
+  }
+}
+__global__ void __launch_bounds__(256) to_bf16_rows_kernel(const float *__restrict__ in, __nv_bfloat16 *__restrict__ out,
+                                                           long long rows, long long cols, long long pitch) {
+  const long long total = rows * pitch;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / pitch, c = i - r * pitch;
+    out[i] = __float2bfloat16_rn(c < cols ? in[r * cols + c] : 0.f);
+  }
+}
+
+// fp32 [rows, cols] dense -> fp32 [cols, pitch] (its transpose, pitch % 4 == 0): TF32 operands that arrive MN-major are
+// made K-major once, because tcgen05 reads MN-major 32-bit operands only through the 32-byte-atom swizzle.
+__global__ void __launch_bounds__(256) transpose_f32_kernel(const float *__restrict__ in, float *__restrict__ out, int rows,
+                                                            int cols, long long pitch) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  const int tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+  for (int t = blockIdx.x; t < tiles_c * tiles_r; t += gridDim.x) {
+    const int r0 = (t / tiles_c) * 32, c0 = (t % tiles_c) * 32;
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      const int r = r0 + ty + j, c = c0 + tx;
+      tile[ty + j][tx] = (r < rows && c < cols) ? in[(long long)r * cols + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      const int c = c0 + ty + j, r = r0 + tx;
+      if (c < cols && r < rows) out[(long long)c * pitch + r] = tile[tx][ty + j];
+    }
+    __syncthreads();
+  }
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encoder() {
+  static encode_tiled_fn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (encode_tiled_fn)p;
+    else
+      cudaGetLastError();
+  });
+  return fn;
+}
+
+// 2-D row-major tensor [outer][inner] with a 128B-swizzled box.
+static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, const void *base, uint64_t inner, uint64_t outer,
+                    uint64_t pitch_elems, uint32_t box_inner, uint32_t box_outer) {
+  encode_tiled_fn enc = get_encoder();
+  DLS_CHECK(enc != nullptr, DLS_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {pitch_elems * (uint64_t)elem_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r) + " (inner " + std::to_string(inner) +
+              ", outer " + std::to_string(outer) + ", pitch " + std::to_string(pitch_elems) + ")");
+    return DLS_ERR_CUDA;
+  }
+  return DLS_OK;
+}
+
+template <bool TF32, bool A_MN, bool B_MN>
+static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mc,
+                          float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct) {
+  auto kern = gemm_tc_kernel<TF32, A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    DLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    configured = true;
+  }
+  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
+  kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+}  // namespace tc
+
+int launch_to_bf16(dls_ctx *ctx, int stream, const float *in, void *out, long long rows, long long cols, long long pitch) {
+  cudaStream_t st = ctx->streams[stream];
+  if (rows * cols == 0) return DLS_OK;
+  if (pitch == cols && ((uintptr_t)in % 16) == 0) {
+    const size_t n8 = (size_t)(rows * cols) / 8;       // cols % 8 == 0 here
+    const int grid = (int)std::min<size_t>((n8 + 255) / 256, (size_t)ctx->sm_count * 8);
+    tc::to_bf16_flat_kernel<<<grid, 256, 0, st>>>((const float4 *)in, (uint4 *)out, n8);
+  } else {
+    const long long total = rows * pitch;
+    const int grid = (int)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 8);
+    tc::to_bf16_rows_kernel<<<grid, 256, 0, st>>>(in, (__nv_bfloat16 *)out, rows, cols, pitch);
+  }
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+int launch_transpose_f32(dls_ctx *ctx, int stream, const float *in, float *out, int rows, int cols, long long pitch) {
+  if ((long long)rows * cols == 0) return DLS_OK;
+  const long long tiles = (long long)((rows + 31) / 32) * ((cols + 31) / 32);
+  const int grid = (int)std::min<long long>(tiles, (long long)ctx->sm_count * 16);
+  tc::transpose_f32_kernel<<<grid, 256, 0, ctx->streams[stream]>>>(in, out, rows, cols, pitch);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn, long long lda, const void *B, bool b_mn,
+                   long long ldb, float *C, long long ldc, int M, int N, int K, const GemmEpilogue &epi) {
+  using namespace tc;
+  DLS_CHECK(kind == DLS_GEMM_BF16 || kind == DLS_GEMM_TF32, DLS_ERR_INVALID, "launch_gemm_tc: kind must be BF16 or TF32");
+  const bool tf32 = kind == DLS_GEMM_TF32;
+  DLS_CHECK(!(tf32 && (a_mn || b_mn)), DLS_ERR_UNSUPPORTED, "launch_gemm_tc: TF32 operands must be K-major");
+  const int elem = tf32 ? 4 : 2;
+  const int block_k = 128 / elem, mn_atom = 128 / elem;
+  DLS_CHECK((lda * elem) % 16 == 0 && (ldb * elem) % 16 == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0,
+            DLS_ERR_INVALID, "launch_gemm_tc: operand rows must be 16-byte aligned");
+  const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap ma, mb, mc;
+  int rc;
+  // K-major [rows][K]: box = BLOCK_K x tile rows.  MN-major [K][rows]: box = 128 bytes of rows x BLOCK_K.
+  rc = a_mn ? make_map(&ma, dt, elem, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, mn_atom, block_k)
+            : make_map(&ma, dt, elem, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, block_k, BM);
+  if (rc) return rc;
+  rc = b_mn ? make_map(&mb, dt, elem, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, mn_atom, block_k)
+            : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, BN);
+  if (rc) return rc;
+  const int direct = ((ldc % 4) != 0 || ((uintptr_t)C % 16) != 0) ? 1 : 0;
+  if (!direct) {
+    rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, EPI_CHUNK, 32);
+    if (rc) return rc;
+  } else {
+    mc = ma;   // unused by the kernel in direct-store mode
+  }
+  cudaStream_t st = ctx->streams[stream];
+  if (tf32) return launch_variant<true, false, false>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
+  if (!a_mn && !b_mn) return launch_variant<false, false, false>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
+  if (!a_mn && b_mn) return launch_variant<false, false, true>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
+  if (a_mn && !b_mn) return launch_variant<false, true, false>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
+  return launch_variant<false, true, true>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
+}
+
+}  // namespace dls

@@ -3,6 +3,7 @@
 // fp32 accumulate) lives in gemm_tc.cu and is selected by dls_ctx_opts.gemm_mode.
 // Lowering target for the unrolled matmul trees (TensorsSpec:337-344, :371-383) and im2col convolution (:144-210).
 #include "common.h"
+#include "gemm_tc.h"
 
 namespace dls {
 
@@ -87,32 +88,124 @@ int launch_sgemm(dls_ctx *ctx, int stream, const float *A, const float *B, float
 
 using namespace dls;
 
-extern "C" int dls_matmul(dls_ctx *ctx, dls_buf *a, dls_buf *b, size_t m, size_t n, size_t k, int transpose_a, int transpose_b,
-                          dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done) {
+namespace {
+
+struct Scratch {   // a block borrowed from the caching allocator for the lifetime of one launch sequence
+  dls_ctx *ctx;
+  Block blk;
+  explicit Scratch(dls_ctx *c) : ctx(c) {}
+  ~Scratch() { free_block(ctx, blk); }   // stream-ordered: reuse waits for the streams that touched it
+};
+
+// fp32 operand -> what the tensor-core kernel wants.  BF16: a bf16 copy with the same orientation (both major-nesses
+// are native).  TF32: the fp32 buffer itself when it is K-major with 16-byte rows, otherwise a transposed / re-pitched copy.
+int stage_operand(dls_ctx *ctx, int stream, int mode, const float *src, long long rows, long long cols, bool want_k_major_is_rows,
+                  Scratch &sc, const void **ptr, long long *pitch, bool *mn_major) {
+  // `rows x cols` is the stored (row-major) shape; `want_k_major_is_rows` says the contraction index is the ROW index,
+  // i.e. the operand is MN-major as stored.
+  if (mode == DLS_GEMM_BF16) {
+    const long long p = (cols + 7) & ~7LL;
+    int rc = alloc_block(ctx, (size_t)(rows * p) * 2, stream, &sc.blk);
+    if (rc) return rc;
+    rc = launch_to_bf16(ctx, stream, src, sc.blk.ptr, rows, cols, p);
+    if (rc) return rc;
+    *ptr = sc.blk.ptr;
+    *pitch = p;
+    *mn_major = want_k_major_is_rows;
+    return DLS_OK;
+  }
+  // TF32
+  if (!want_k_major_is_rows && cols % 4 == 0 && ((uintptr_t)src % 16) == 0) {
+    *ptr = src;
+    *pitch = cols;
+    *mn_major = false;
+    return DLS_OK;
+  }
+  if (!want_k_major_is_rows) {   // K-major but ragged rows: re-pitch through a double transpose-free copy (rare, small)
+    const long long p = (cols + 3) & ~3LL;
+    int rc = alloc_block(ctx, (size_t)(rows * p) * 4, stream, &sc.blk);
+    if (rc) return rc;
+    DLS_CUDA(cudaMemcpy2DAsync(sc.blk.ptr, (size_t)p * 4, src, (size_t)cols * 4, (size_t)cols * 4, (size_t)rows,
+                               cudaMemcpyDeviceToDevice, ctx->streams[stream]));
+    *ptr = sc.blk.ptr;
+    *pitch = p;
+    *mn_major = false;
+    return DLS_OK;
+  }
+  const long long p = (rows + 3) & ~3LL;   // transposed copy: [cols][rows]
+  int rc = alloc_block(ctx, (size_t)(cols * p) * 4, stream, &sc.blk);
+  if (rc) return rc;
+  rc = launch_transpose_f32(ctx, stream, src, (float *)sc.blk.ptr, (int)rows, (int)cols, p);
+  if (rc) return rc;
+  *ptr = sc.blk.ptr;
+  *pitch = p;
+  *mn_major = false;
+  return DLS_OK;
+}
+
+}  // namespace
+
+extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k, int transpose_a,
+                             int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
+                             dls_event **done) {
   DLS_CHECK(ctx && a && b && out, DLS_ERR_INVALID, "dls_matmul: NULL argument");
   DLS_CHECK(m * k <= a->n && k * n <= b->n, DLS_ERR_INVALID, "dls_matmul: operand shorter than its shape");
   DLS_CHECK(m < (1u << 31) && n < (1u << 31) && k < (1u << 31), DLS_ERR_UNSUPPORTED, "dls_matmul: dimension too large");
+  dls_gemm_opts o{};
+  o.mode = -1;
+  if (opts) o = *opts;
+  const int mode = o.mode < 0 ? ctx->opts.gemm_mode : o.mode;
+  DLS_CHECK(mode == DLS_GEMM_FP32 || mode == DLS_GEMM_TF32 || mode == DLS_GEMM_BF16, DLS_ERR_INVALID, "dls_matmul: bad gemm mode");
+  DLS_CHECK(o.bias_mode >= 0 && o.bias_mode <= 2 && o.activation >= 0 && o.activation <= 2, DLS_ERR_INVALID,
+            "dls_matmul: bad epilogue options");
+  DLS_CHECK(o.bias_mode == 0 || (bias && bias->n >= (o.bias_mode == 1 ? m : n)), DLS_ERR_INVALID,
+            "dls_matmul: bias buffer missing or too short");
+  DLS_CHECK(mode != DLS_GEMM_FP32 || (o.bias_mode == 0 && o.activation == 0), DLS_ERR_UNSUPPORTED,
+            "dls_matmul: fused epilogues need a tensor-core gemm mode");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   DLS_CUDA(cudaSetDevice(ctx->device));
   const int stream = pick_stream(ctx);
-  dls_buf *ins[2] = {a, b};
-  int rc = wait_inputs(ctx, stream, ins, 2, deps, n_deps);
+  dls_buf *ins[3] = {a, b, o.bias_mode ? bias : nullptr};
+  int rc = wait_inputs(ctx, stream, ins, 3, deps, n_deps);
   if (rc) return rc;
-  dls_buf *o = nullptr;
-  rc = new_buf(ctx, m * n, stream, &o);
+  dls_buf *c = nullptr;
+  rc = new_buf(ctx, m * n, stream, &c);
   if (rc) return rc;
   if (m * n != 0) {
-    if (k == 0) {
-      cudaMemsetAsync(o->ptr, 0, m * n * sizeof(float), ctx->streams[stream]);
+    if (mode == DLS_GEMM_FP32) {
+      if (k == 0) DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
+      else rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, c->ptr, (int)m, (int)n, (int)k, transpose_a != 0, transpose_b != 0);
     } else {
-      rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, o->ptr, (int)m, (int)n, (int)k, transpose_a != 0, transpose_b != 0);
+      // K == 0 still runs the epilogue over a zero accumulator?  No MMA would ever be issued: handle on the slow path.
+      if (k == 0) {
+        DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
+      } else {
+        Scratch sa(ctx), sb(ctx);
+        const void *pa, *pb;
+        long long lda, ldb;
+        bool a_mn, b_mn;
+        // a is stored [K][M] when transposed (contraction index = row index), else [M][K]
+        rc = stage_operand(ctx, stream, mode, a->ptr, transpose_a ? k : m, transpose_a ? m : k, transpose_a != 0, sa, &pa, &lda, &a_mn);
+        // b is stored [N][K] when transposed, else [K][N] (contraction index = row index)
+        if (!rc) rc = stage_operand(ctx, stream, mode, b->ptr, transpose_b ? n : k, transpose_b ? k : n, transpose_b == 0, sb, &pb, &ldb, &b_mn);
+        GemmEpilogue epi;
+        epi.bias = o.bias_mode ? bias->ptr : nullptr;
+        epi.bias_mode = o.bias_mode;
+        epi.act = o.activation;
+        if (!rc) rc = launch_gemm_tc(ctx, stream, mode, pa, a_mn, lda, pb, b_mn, ldb, c->ptr, (long long)n, (int)m, (int)n, (int)k, epi);
+      }
     }
   }
-  if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 2, done);
+  if (!rc) rc = finish_output(ctx, stream, &c, 1, ins, 3, done);
   if (rc) {
-    dls_buf_release(o);
+    dls_buf_release(c);
     return rc;
   }
-  *out = o;
+  *out = c;
   return DLS_OK;
+}
+
+extern "C" int dls_matmul(dls_ctx *ctx, dls_buf *a, dls_buf *b, size_t m, size_t n, size_t k, int transpose_a, int transpose_b,
+                          dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done) {
+  return dls_matmul_ex(ctx, a, b, nullptr, m, n, k, transpose_a, transpose_b, nullptr, deps, n_deps, out, done);
 }

@@ -206,6 +206,33 @@ class Backend:
         perm = [i if i < dimension else (n - 1 if i == dimension else i - 1) for i in range(n)]
         return joined.permute(perm)
 
+    def matmul(self, a: "Tensor", b: "Tensor", transpose_a: bool = False, transpose_b: bool = False, bias=None,
+               bias_mode: str = "none", activation: str = "none", mode: Optional[str] = None) -> "NonInlineTensor":
+        """out = act(op(a) op(b) + bias) as ONE contraction kernel (`dls_matmul_ex`): what the reference can only spell
+        as a host-unrolled `split(1) ... reduce(_ + _)` chain (TensorsSpec:337-344, :371-383).  `mode` None = this
+        backend's gemm_mode; "fp32" is the CUDA-core kernel (same left-fold rounding as the chain), "tf32" / "bf16" run
+        on the tcgen05 tensor cores with fp32 accumulation."""
+        if len(a.shape) != 2 or len(b.shape) != 2:
+            raise ValueError("matmul: operands must be matrices, got %r and %r" % (a.shape, b.shape))
+        m, k = (a.shape[1], a.shape[0]) if transpose_a else (a.shape[0], a.shape[1])
+        n, k2 = (b.shape[0], b.shape[1]) if transpose_b else (b.shape[1], b.shape[0])
+        if k != k2:
+            raise ValueError("matmul: inner dimensions differ (%d vs %d)" % (k, k2))
+        opts = N.GemmOpts(mode={None: -1, "fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}[mode],
+                          bias_mode={"none": 0, "row": 1, "col": 2}[bias_mode],
+                          activation={"none": 0, "tanh": 1, "relu": 2}[activation], reserved=0)
+        if opts.bias_mode and (bias is None or bias.size != (m if bias_mode == "row" else n)):
+            raise ValueError("matmul: bias must have %d elements" % (m if bias_mode == "row" else n))
+
+        def produce():
+            ba, bb = a._buffer(), b._buffer()
+            bbias = bias._buffer() if opts.bias_mode else None
+            h = C.c_void_p()
+            N.check(N.lib.dls_matmul_ex(self.ctx, ba.handle, bb.handle, bbias.handle if bbias else None, m, n, k,
+                                        int(transpose_a), int(transpose_b), C.byref(opts), None, 0, C.byref(h), None))
+            return DeviceBuffer(self, h, m * n)
+        return ProducedTensor(self, produce, [m, n], a.padding)
+
     def abs(self, t): return t._derived(Unary("abs", t.closure()))
     def sqrt(self, t): return t._derived(Unary("sqrt", t.closure()))
     def tanh(self, t): return t._derived(Unary("tanh", t.closure()))
@@ -539,6 +566,7 @@ def fill(value, shape, padding: float = 0.0): return default_backend().fill(valu
 def random(shape, seed, padding: float = 0.0): return default_backend().random(shape, seed, padding)
 def random_normal(shape, seed, padding: float = 0.0): return default_backend().random_normal(shape, seed, padding)
 def join(tensors, dimension=None): return tensors[0].backend.join(tensors, dimension)
+def matmul(a, b, **kw): return a.backend.matmul(a, b, **kw)
 def abs_(t): return t.backend.abs(t)
 def sqrt(t): return t.backend.sqrt(t)
 def tanh(t): return t.backend.tanh(t)

@@ -156,6 +156,22 @@ int dls_sgd_update(dls_ctx *ctx, dls_buf *weight, dls_buf *delta, size_t n_float
 int dls_matmul(dls_ctx *ctx, dls_buf *a, dls_buf *b, size_t m, size_t n, size_t k, int transpose_a, int transpose_b,
                dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done);
 
+/* Same contraction with an explicit precision and a fused epilogue, out = act(op(A) op(B) + bias): the body of a custom
+ * TensorLayer forward (`TensorLayer(forward)`, TL:98-108) such as tanh(W x + b) in one kernel.  mode = -1 takes the
+ * context's gemm_mode.  BF16 / TF32 run on the tcgen05 tensor cores with fp32 accumulation; stated tolerance against the
+ * fp32 chain: 1e-3 relative (TF32), 4e-3 relative (BF16). */
+enum dls_bias_mode { DLS_BIAS_NONE = 0, DLS_BIAS_ROW = 1 /* bias[m]: left-aligned broadcast, Tensors:208-222 */, DLS_BIAS_COL = 2 /* bias[n] */ };
+enum dls_activation { DLS_ACT_NONE = 0, DLS_ACT_TANH = 1, DLS_ACT_RELU = 2 /* Tensor.max(x, fill 0) */ };
+typedef struct dls_gemm_opts {
+  int32_t mode;        /* enum dls_gemm_mode, or -1 = context default */
+  int32_t bias_mode;   /* enum dls_bias_mode   */
+  int32_t activation;  /* enum dls_activation  */
+  int32_t reserved;
+} dls_gemm_opts;
+int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k, int transpose_a,
+                  int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
+                  dls_event **done);
+
 /* ---- data-parallel exchange (new functionality: the reference has no collective) */
 int dls_comm_unique_id(uint8_t *id128);                              /* 128-byte NCCL unique id (rank 0)   */
 int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size);

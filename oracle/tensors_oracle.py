@@ -696,6 +696,55 @@ def maximum(a: Tensor, b: Tensor) -> InlineTensor:
     return a._binary("max", b)
 
 
+def round_operand(x: np.ndarray, kind: Optional[str]) -> np.ndarray:
+    """What the tensor cores see of an fp32 operand: bf16 = round to nearest even to 8 significand bits (the staging
+    kernel's cvt.rn.bf16.f32); tf32 = the low 13 mantissa bits ignored (tcgen05 kind::tf32 reads 32-bit containers)."""
+    x = np.ascontiguousarray(x, dtype=F32)
+    if kind is None or kind == "fp32":
+        return x
+    bits = x.view(np.uint32).astype(np.uint64)
+    if kind == "bf16":
+        rounded = (bits + 0x7FFF + ((bits >> 16) & 1)) & 0xFFFF0000
+        out = rounded.astype(np.uint32).view(F32)
+        return np.where(np.isnan(x), x, out).astype(F32)
+    if kind == "tf32":
+        return (bits & 0xFFFFE000).astype(np.uint32).view(F32)
+    raise ValueError(kind)
+
+
+def matmul(a: Tensor, b: Tensor, transpose_a: bool = False, transpose_b: bool = False, bias: Optional[Tensor] = None,
+           bias_mode: str = "none", activation: str = "none", operands: Optional[str] = None) -> NonInlineTensor:
+    """The contraction the reference spells as a host-unrolled chain (TensorsSpec:337-344): out[i,k] =
+    ((a[i,0]*b[0,k] + a[i,1]*b[1,k]) + a[i,2]*b[2,k]) + ..., one fp32 rounding per node, j ascending (Scala `reduce` on
+    an IndexedSeq is a left fold).  `operands` optionally rounds the inputs the way a tensor-core mode reads them."""
+    def thunk():
+        A = a.materialise().reshape(a.shape).astype(F32)
+        B = b.materialise().reshape(b.shape).astype(F32)
+        if transpose_a:
+            A = A.T
+        if transpose_b:
+            B = B.T
+        A, B = round_operand(A, operands), round_operand(B, operands)
+        m, k = A.shape
+        n = B.shape[1]
+        acc = np.zeros((m, n), dtype=F32)
+        for j in range(k):
+            term = (A[:, j:j + 1] * B[j:j + 1, :]).astype(F32)
+            acc = term if j == 0 else (acc + term).astype(F32)
+        if bias_mode == "row":
+            acc = (acc + bias.materialise().astype(F32).reshape(-1, 1)).astype(F32)
+        elif bias_mode == "col":
+            acc = (acc + bias.materialise().astype(F32).reshape(1, -1)).astype(F32)
+        if activation == "tanh":
+            acc = np.tanh(acc.astype(np.float64)).astype(F32)
+        elif activation == "relu":
+            acc = _fmax(acc, np.zeros_like(acc))
+        return acc.reshape(-1)
+    m = a.shape[1] if transpose_a else a.shape[0]
+    n = b.shape[0] if transpose_b else b.shape[1]
+    return BufferTensor(thunk, [m, n], a.padding)
+
+
 def join(tensors: Sequence[Tensor], dimension: Optional[int] = None) -> Tensor:
     """Tensors:560-598: evaluate every element at the HEAD tensor's shape, write them as the new last
     dimension (KB:632-652), then optionally permute it to `dimension`."""

@@ -1,0 +1,105 @@
+"""Parity of the tcgen05 / TMEM contraction kernel (csrc/gemm_tc.cu, through `dls_matmul_ex`) with the CPU oracle.
+
+Two bars per case:
+  1. against the oracle evaluated on operands rounded the way the tensor cores read them (bf16 RNE / tf32 truncation):
+     only the fp32 accumulation order differs, so the bound is tight -- 2e-6 * sum_k |a_ik| |b_kj| per element.
+     This is the check that the TMA boxes, swizzles, UMMA descriptors and the epilogue address every element correctly.
+  2. against the plain fp32 chain of the reference (TensorsSpec:337-344): relative Frobenius error below the tolerance
+     stated in include/dls_b200.h (TF32 1e-3, BF16 4e-3).
+The fp32 mode (CUDA cores) must match the chain bit for bit.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+STATED_REL = {"tf32": 1e-3, "bf16": 4e-3}
+
+
+@pytest.fixture(scope="module")
+def backends():
+    from oracle import tensors_oracle as O
+    import deeplearning.scala_b200.tensors as B
+    B.default_backend().ctx
+    return O, B
+
+
+def operands(m, n, k, ta, tb, seed):
+    rng = np.random.RandomState(seed)
+    a = rng.standard_normal((k, m) if ta else (m, k)).astype(np.float32)
+    b = rng.standard_normal((n, k) if tb else (k, n)).astype(np.float32)
+    return a, b
+
+
+def run_case(backends, mode, m, n, k, ta, tb, seed=0, **epi):
+    O, B = backends
+    a, b = operands(m, n, k, ta, tb, seed)
+    bias = None
+    okw, bkw = {}, {}
+    if epi.get("bias_mode", "none") != "none":
+        bias = np.random.RandomState(seed + 1).standard_normal(m if epi["bias_mode"] == "row" else n).astype(np.float32)
+        okw["bias"], bkw["bias"] = O.tensor(bias), B.tensor(bias)
+    got = B.matmul(B.tensor(a), B.tensor(b), transpose_a=ta, transpose_b=tb, mode=mode, **bkw, **epi).flat_array().reshape(m, n)
+    exact = O.matmul(O.tensor(a), O.tensor(b), transpose_a=ta, transpose_b=tb, operands=mode, **okw, **epi).flat_array().reshape(m, n)
+    chain = O.matmul(O.tensor(a), O.tensor(b), transpose_a=ta, transpose_b=tb, **okw, **epi).flat_array().reshape(m, n)
+    A = np.abs(a.T if ta else a).astype(np.float64)
+    Bm = np.abs(b.T if tb else b).astype(np.float64)
+    scale = A @ Bm + 1.0
+    return got, exact, chain, scale
+
+
+SHAPES = [
+    # m, n, k, ta, tb
+    (128, 256, 64, False, True),       # exactly one tile, one k block, both K-major
+    (128, 256, 256, False, True),      # several k blocks: ring wrap-around
+    (256, 512, 128, False, False),     # B MN-major ([K,N] row-major): the forward layer layout
+    (256, 512, 128, True, True),       # A MN-major
+    (256, 512, 128, True, False),      # both MN-major: the weight-gradient layout
+    (300, 520, 200, False, False),     # ragged M, N, K (TMA zero fill / clipped stores)
+    (10, 128, 500, False, False),      # C1 layer 2: out[10,128] = W2[10,500] h[500,128]
+    (500, 128, 784, False, False),     # C1 layer 1
+    (500, 784, 128, False, True),      # C1 dW1 = delta[500,128] x[784,128]^T
+    (64, 10, 96, False, False),        # N % 4 != 0: direct-store epilogue
+    (1, 1, 1, False, False),
+    (129, 257, 65, True, False),
+    (1500, 1100, 333, False, True),    # more tiles than one wave of accumulators per CTA
+]
+
+
+@pytest.mark.parametrize("mode", ["bf16", "tf32"])
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "%dx%dx%d%s%s" % (s[0], s[1], s[2], "T" if s[3] else "N", "T" if s[4] else "N"))
+def test_tensor_core_contraction(backends, mode, shape):
+    m, n, k, ta, tb = shape
+    got, exact, chain, scale = run_case(backends, mode, m, n, k, ta, tb, seed=m + n + k)
+    err = np.abs(got.astype(np.float64) - exact.astype(np.float64)) / scale
+    assert err.max() <= 2e-6, "kernel differs from the operand-rounded oracle: %g at %r" % (err.max(), np.unravel_index(err.argmax(), err.shape))
+    rel = np.linalg.norm(got.astype(np.float64) - chain) / max(np.linalg.norm(chain), 1e-30)
+    assert rel <= STATED_REL[mode], "relative Frobenius error %g above the stated %g" % (rel, STATED_REL[mode])
+
+
+@pytest.mark.parametrize("mode", ["bf16", "tf32"])
+@pytest.mark.parametrize("epi", [dict(bias_mode="row", activation="tanh"), dict(bias_mode="col", activation="relu"),
+                                 dict(bias_mode="row", activation="none")], ids=["row+tanh", "col+relu", "row"])
+def test_fused_epilogue(backends, mode, epi):
+    m, n, k = 200, 264, 160
+    got, exact, chain, scale = run_case(backends, mode, m, n, k, False, False, seed=5, **epi)
+    # tanh / relu are 1-Lipschitz: the pre-activation bound carries over, plus 2 ulp of tanhf
+    err = np.abs(got.astype(np.float64) - exact.astype(np.float64)) / scale
+    assert err.max() <= 4e-6, err.max()
+
+
+@pytest.mark.parametrize("shape", [(96, 80, 200, False, False), (33, 65, 17, True, True), (500, 128, 784, False, False)],
+                         ids=["NN", "TT", "c1"])
+def test_fp32_contraction_matches_the_chain_bit_for_bit(backends, shape):
+    m, n, k, ta, tb = shape
+    got, exact, chain, scale = run_case(backends, "fp32", m, n, k, ta, tb, seed=3)
+    assert (got.view(np.uint32) == chain.view(np.uint32)).all()
+
+
+def test_empty_contraction(backends):
+    O, B = backends
+    a = np.zeros((4, 0), dtype=np.float32)
+    b = np.zeros((0, 8), dtype=np.float32)
+    for mode in ("fp32", "bf16", "tf32"):
+        got = B.matmul(B.tensor(a), B.tensor(b), mode=mode).flat_array()
+        assert got.shape == (32,) and (got == 0).all()
