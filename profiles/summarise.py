@@ -21,6 +21,9 @@ KEYS = OrderedDict([
     ("smsp__inst_executed.sum", "warp instructions"),
     ("lts__t_sector_hit_rate.pct", "L2 hit rate %"),
     ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor pipe %"),
+    ("sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "tensor memory (TMEM) pipe active % of elapsed"),
+    ("sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg", "tensor HMMA sub-pipe active cycles (avg per SM)"),
+    ("sm__cycles_elapsed.avg", "SM cycles elapsed (avg)"),
     ("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "stall long_scoreboard / issue"),
     ("smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "stall wait / issue"),
     ("smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "stall not_selected / issue"),

@@ -13,7 +13,11 @@ def main():
     be = B.default_backend()
     cases = [(4096, 8192, 4096, False, True), (4096, 8192, 4096, False, False), (4096, 4096, 8192, False, True),
              (4096, 8192, 4096, True, False), (8192, 8192, 8192, False, True)]
-    modes = sys.argv[1:] or ["bf16", "tf32"]
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    modes = args or ["bf16", "tf32"]
+    for a in sys.argv[1:]:
+        if a.startswith("--case="):
+            cases = [cases[int(a.split("=")[1])]]
     for mode in modes:
         for (m, n, k, ta, tb) in cases:
             a = B.random([k, m] if ta else [m, k], seed=1).do_cache()
