@@ -64,6 +64,11 @@ struct dls_buf {
   dls::Block block;
   int last_stream = 0;     // stream of the most recent writer
   cudaEvent_t ready = nullptr;  // recorded after the most recent writer (multi-stream contexts only)
+  // tensor-core operand shadows (matmul.cu): a bf16 copy and a transposed fp32 copy of this buffer for a given
+  // [rows, cols] interpretation, kept until the buffer is written again or released, so a tensor that feeds several
+  // contractions (an activation in forward and in the weight-gradient GEMM) is staged once.
+  dls::Block shadow[2];
+  long long shadow_rows[2] = {0, 0}, shadow_cols[2] = {0, 0};
 };
 
 struct dls_ctx {

@@ -366,7 +366,35 @@ __global__ void __launch_bounds__(256) to_bf16_rows_kernel(const float *__restri
   }
 }
 
-// fp32 [rows, cols] dense -> fp32 [cols, pitch] (its transpose, pitch % 4 == 0): TF32 operands that arrive MN-major are
+// fp32 -> tf32 (10-bit mantissa), round to nearest, ties away: tcgen05 kind::tf32 ignores the low 13 mantissa bits of its
+// 32-bit operands, i.e. truncates; truncation is biased (every product shrinks by ~2^-11 twice) and misses the stated
+// 1e-3, so operands are rounded once when they are staged.
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+__global__ void __launch_bounds__(256) to_tf32_rows_kernel(const float *__restrict__ in, float *__restrict__ out, long long rows,
+                                                           long long cols, long long pitch) {
+  const long long total = rows * pitch;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / pitch, c = i - r * pitch;
+    out[i] = c < cols ? round_tf32(in[r * cols + c]) : 0.f;
+  }
+}
+__global__ void __launch_bounds__(256) to_tf32_flat_kernel(const float4 *__restrict__ in, float4 *__restrict__ out, size_t n4) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 v = __ldcs(in + i);
+    v.x = round_tf32(v.x);
+    v.y = round_tf32(v.y);
+    v.z = round_tf32(v.z);
+    v.w = round_tf32(v.w);
+    out[i] = v;
+  }
+}
+
+// fp32 [rows, cols] dense -> tf32-rounded fp32 [cols, pitch] (its transpose, pitch % 4 == 0): TF32 operands that arrive MN-major are
 // made K-major once, because tcgen05 reads MN-major 32-bit operands only through the 32-byte-atom swizzle.
 __global__ void __launch_bounds__(256) transpose_f32_kernel(const float *__restrict__ in, float *__restrict__ out, int rows,
                                                             int cols, long long pitch) {
@@ -384,7 +412,7 @@ __global__ void __launch_bounds__(256) transpose_f32_kernel(const float *__restr
 #pragma unroll
     for (int j = 0; j < 32; j += 8) {
       const int c = c0 + ty + j, r = r0 + tx;
-      if (c < cols && r < rows) out[(long long)c * pitch + r] = tile[tx][ty + j];
+      if (c < cols && r < rows) out[(long long)c * pitch + r] = round_tf32(tile[tx][ty + j]);
     }
     __syncthreads();
   }
@@ -458,6 +486,23 @@ int launch_to_bf16(dls_ctx *ctx, int stream, const float *in, void *out, long lo
     const long long total = rows * pitch;
     const int grid = (int)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 8);
     tc::to_bf16_rows_kernel<<<grid, 256, 0, st>>>(in, (__nv_bfloat16 *)out, rows, cols, pitch);
+  }
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+int launch_to_tf32(dls_ctx *ctx, int stream, const float *in, float *out, long long rows, long long cols, long long pitch) {
+  cudaStream_t st = ctx->streams[stream];
+  if (rows * cols == 0) return DLS_OK;
+  if (pitch == cols && ((uintptr_t)in % 16) == 0) {
+    const size_t n4 = (size_t)(rows * cols) / 4;
+    const int grid = (int)std::min<size_t>((n4 + 255) / 256, (size_t)ctx->sm_count * 8);
+    tc::to_tf32_flat_kernel<<<grid, 256, 0, st>>>((const float4 *)in, (float4 *)out, n4);
+  } else {
+    const long long total = rows * pitch;
+    const int grid = (int)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 8);
+    tc::to_tf32_rows_kernel<<<grid, 256, 0, st>>>(in, out, rows, cols, pitch);
   }
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;

@@ -21,7 +21,10 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
 // fp32 [rows, cols] dense -> bf16 [rows, pitch] (pitch % 8 == 0, pad columns zero), round to nearest even.
 int launch_to_bf16(dls_ctx *ctx, int stream, const float *in, void *out, long long rows, long long cols, long long pitch);
 
-// fp32 [rows, cols] dense -> fp32 [cols, pitch] (transpose; pitch % 4 == 0, pad columns zero)
+// fp32 [rows, cols] dense -> tf32-rounded (RNA) fp32 [rows, pitch] (pitch % 4 == 0, pad columns zero)
+int launch_to_tf32(dls_ctx *ctx, int stream, const float *in, float *out, long long rows, long long cols, long long pitch);
+
+// fp32 [rows, cols] dense -> tf32-rounded fp32 [cols, pitch] (transpose; pitch % 4 == 0)
 int launch_transpose_f32(dls_ctx *ctx, int stream, const float *in, float *out, int rows, int cols, long long pitch);
 
 // matmul.cu

@@ -84,62 +84,77 @@ int launch_sgemm(dls_ctx *ctx, int stream, const float *A, const float *B, float
   return DLS_OK;
 }
 
+// out = act(out + bias) in place: the fused epilogue of the tensor-core kernel for the CUDA-core fp32 mode.
+__global__ void __launch_bounds__(256) bias_act_kernel(float *__restrict__ c, size_t m, size_t n, const float *__restrict__ bias,
+                                                       int bias_mode, int act) {
+  const size_t total = m * n;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    float x = c[i];
+    if (bias_mode == 1) x = __fadd_rn(x, __ldg(bias + i / n));
+    else if (bias_mode == 2) x = __fadd_rn(x, __ldg(bias + i % n));
+    if (act == 1) x = tanhf(x);
+    else if (act == 2) x = fmaxf(x, 0.f);
+    c[i] = x;
+  }
+}
+
+int launch_bias_act(dls_ctx *ctx, int stream, float *c, size_t m, size_t n, const float *bias, int bias_mode, int act) {
+  if (m * n == 0 || (bias_mode == 0 && act == 0)) return DLS_OK;
+  const int grid = (int)std::min<size_t>((m * n + 255) / 256, (size_t)ctx->sm_count * 8);
+  bias_act_kernel<<<grid, 256, 0, ctx->streams[stream]>>>(c, m, n, bias, bias_mode, act);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
 }  // namespace dls
 
 using namespace dls;
 
 namespace {
 
-struct Scratch {   // a block borrowed from the caching allocator for the lifetime of one launch sequence
-  dls_ctx *ctx;
-  Block blk;
-  explicit Scratch(dls_ctx *c) : ctx(c) {}
-  ~Scratch() { free_block(ctx, blk); }   // stream-ordered: reuse waits for the streams that touched it
-};
-
 // fp32 operand -> what the tensor-core kernel wants.  BF16: a bf16 copy with the same orientation (both major-nesses
-// are native).  TF32: the fp32 buffer itself when it is K-major with 16-byte rows, otherwise a transposed / re-pitched copy.
-int stage_operand(dls_ctx *ctx, int stream, int mode, const float *src, long long rows, long long cols, bool want_k_major_is_rows,
-                  Scratch &sc, const void **ptr, long long *pitch, bool *mn_major) {
-  // `rows x cols` is the stored (row-major) shape; `want_k_major_is_rows` says the contraction index is the ROW index,
-  // i.e. the operand is MN-major as stored.
-  if (mode == DLS_GEMM_BF16) {
-    const long long p = (cols + 7) & ~7LL;
-    int rc = alloc_block(ctx, (size_t)(rows * p) * 2, stream, &sc.blk);
-    if (rc) return rc;
-    rc = launch_to_bf16(ctx, stream, src, sc.blk.ptr, rows, cols, p);
-    if (rc) return rc;
-    *ptr = sc.blk.ptr;
-    *pitch = p;
-    *mn_major = want_k_major_is_rows;
-    return DLS_OK;
+// are native to the kernel).  TF32: an fp32 copy rounded to tf32 (round to nearest; the tensor core would truncate), K-major
+// (transposed when the operand is stored MN-major), rows padded to 16 bytes.  Copies are cached on the buffer (dls_buf::shadow) until it is written again.
+//   rows x cols       : the stored row-major shape
+//   contraction_is_row: the contraction index is the ROW index, i.e. the operand is MN-major as stored
+int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long rows, long long cols, bool contraction_is_row,
+                  const void **ptr, long long *pitch, bool *mn_major, Block *private_blk = nullptr) {
+  const float *src = buf->ptr;
+  const int slot = mode == DLS_GEMM_BF16 ? 0 : 1;
+  long long no_rows = 0, no_cols = 0;
+  Block &sh = private_blk ? *private_blk : buf->shadow[slot];
+  long long &tag_r = private_blk ? no_rows : buf->shadow_rows[slot];
+  long long &tag_c = private_blk ? no_cols : buf->shadow_cols[slot];
+  const bool transposed = mode == DLS_GEMM_TF32 && contraction_is_row;
+  const long long p = mode == DLS_GEMM_BF16 ? ((cols + 7) & ~7LL) : transposed ? ((rows + 3) & ~3LL) : ((cols + 3) & ~3LL);
+  // slot 1 holds either the transposed or the re-pitched fp32 copy; the sign of shadow_rows tells which
+  const long long tag_rows = transposed ? -rows : rows;
+  if (!(sh.ptr && tag_r == tag_rows && tag_c == cols)) {
+    if (sh.ptr) free_block(ctx, sh);
+    int rc;
+    if (mode == DLS_GEMM_BF16) {
+      rc = alloc_block(ctx, (size_t)(rows * p) * 2, stream, &sh);
+      if (!rc) rc = launch_to_bf16(ctx, stream, src, sh.ptr, rows, cols, p);
+    } else if (transposed) {
+      rc = alloc_block(ctx, (size_t)(cols * p) * 4, stream, &sh);
+      if (!rc) rc = launch_transpose_f32(ctx, stream, src, (float *)sh.ptr, (int)rows, (int)cols, p);
+    } else {
+      rc = alloc_block(ctx, (size_t)(rows * p) * 4, stream, &sh);
+      if (!rc) rc = launch_to_tf32(ctx, stream, src, (float *)sh.ptr, rows, cols, p);
+    }
+    if (rc) {
+      if (sh.ptr) free_block(ctx, sh);
+      return rc;
+    }
+    tag_r = tag_rows;
+    tag_c = cols;
+  } else {
+    sh.stream_mask |= 1u << stream;
   }
-  // TF32
-  if (!want_k_major_is_rows && cols % 4 == 0 && ((uintptr_t)src % 16) == 0) {
-    *ptr = src;
-    *pitch = cols;
-    *mn_major = false;
-    return DLS_OK;
-  }
-  if (!want_k_major_is_rows) {   // K-major but ragged rows: re-pitch through a double transpose-free copy (rare, small)
-    const long long p = (cols + 3) & ~3LL;
-    int rc = alloc_block(ctx, (size_t)(rows * p) * 4, stream, &sc.blk);
-    if (rc) return rc;
-    DLS_CUDA(cudaMemcpy2DAsync(sc.blk.ptr, (size_t)p * 4, src, (size_t)cols * 4, (size_t)cols * 4, (size_t)rows,
-                               cudaMemcpyDeviceToDevice, ctx->streams[stream]));
-    *ptr = sc.blk.ptr;
-    *pitch = p;
-    *mn_major = false;
-    return DLS_OK;
-  }
-  const long long p = (rows + 3) & ~3LL;   // transposed copy: [cols][rows]
-  int rc = alloc_block(ctx, (size_t)(cols * p) * 4, stream, &sc.blk);
-  if (rc) return rc;
-  rc = launch_transpose_f32(ctx, stream, src, (float *)sc.blk.ptr, (int)rows, (int)cols, p);
-  if (rc) return rc;
-  *ptr = sc.blk.ptr;
+  *ptr = sh.ptr;
   *pitch = p;
-  *mn_major = false;
+  *mn_major = mode == DLS_GEMM_BF16 ? contraction_is_row : false;
   return DLS_OK;
 }
 
@@ -160,8 +175,6 @@ extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias
             "dls_matmul: bad epilogue options");
   DLS_CHECK(o.bias_mode == 0 || (bias && bias->n >= (o.bias_mode == 1 ? m : n)), DLS_ERR_INVALID,
             "dls_matmul: bias buffer missing or too short");
-  DLS_CHECK(mode != DLS_GEMM_FP32 || (o.bias_mode == 0 && o.activation == 0), DLS_ERR_UNSUPPORTED,
-            "dls_matmul: fused epilogues need a tensor-core gemm mode");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   DLS_CUDA(cudaSetDevice(ctx->device));
   const int stream = pick_stream(ctx);
@@ -175,24 +188,29 @@ extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias
     if (mode == DLS_GEMM_FP32) {
       if (k == 0) DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
       else rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, c->ptr, (int)m, (int)n, (int)k, transpose_a != 0, transpose_b != 0);
+      if (!rc) rc = launch_bias_act(ctx, stream, c->ptr, m, n, o.bias_mode ? bias->ptr : nullptr, o.bias_mode, o.activation);
     } else {
       // K == 0 still runs the epilogue over a zero accumulator?  No MMA would ever be issued: handle on the slow path.
       if (k == 0) {
         DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
+        rc = launch_bias_act(ctx, stream, c->ptr, m, n, o.bias_mode ? bias->ptr : nullptr, o.bias_mode, o.activation);
       } else {
-        Scratch sa(ctx), sb(ctx);
         const void *pa, *pb;
         long long lda, ldb;
         bool a_mn, b_mn;
         // a is stored [K][M] when transposed (contraction index = row index), else [M][K]
-        rc = stage_operand(ctx, stream, mode, a->ptr, transpose_a ? k : m, transpose_a ? m : k, transpose_a != 0, sa, &pa, &lda, &a_mn);
+        rc = stage_operand(ctx, stream, mode, a, transpose_a ? k : m, transpose_a ? m : k, transpose_a != 0, &pa, &lda, &a_mn);
         // b is stored [N][K] when transposed, else [K][N] (contraction index = row index)
-        if (!rc) rc = stage_operand(ctx, stream, mode, b->ptr, transpose_b ? n : k, transpose_b ? k : n, transpose_b == 0, sb, &pb, &ldb, &b_mn);
+        // the same buffer on both sides with two different interpretations: the second copy must not evict the first
+        Block own;
+        if (!rc) rc = stage_operand(ctx, stream, mode, b, transpose_b ? n : k, transpose_b ? k : n, transpose_b == 0, &pb, &ldb, &b_mn,
+                                    a == b ? &own : nullptr);
         GemmEpilogue epi;
         epi.bias = o.bias_mode ? bias->ptr : nullptr;
         epi.bias_mode = o.bias_mode;
         epi.act = o.activation;
         if (!rc) rc = launch_gemm_tc(ctx, stream, mode, pa, a_mn, lda, pb, b_mn, ldb, c->ptr, (long long)n, (int)m, (int)n, (int)k, epi);
+        if (own.ptr) free_block(ctx, own);
       }
     }
   }

@@ -135,6 +135,8 @@ int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_writt
     if (!b) continue;
     b->block.stream_mask |= 1u << stream;
     b->last_stream = stream;
+    for (int k = 0; k < 2; ++k)   // the contents changed: operand shadows are stale
+      if (b->shadow[k].ptr) free_block(ctx, b->shadow[k]);
     if (ctx->n_streams > 1) {
       if (!b->ready) DLS_CUDA(cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming));
       DLS_CUDA(cudaEventRecord(b->ready, st));
@@ -303,6 +305,7 @@ void dls_buf_release(dls_buf *buf) {
   {
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     if (buf->ready) cudaEventDestroy(buf->ready);
+    for (int k = 0; k < 2; ++k) free_block(ctx, buf->shadow[k]);
     free_block(ctx, buf->block);
   }
   delete buf;

@@ -1,0 +1,157 @@
+"""The training loops of BASELINE.json's configs on the new backend: C1 (MLP 784-500-10), C3 (CIFAR-shaped CNN),
+C4 (wide MLP 4 x 4096) and C5 (C3 under data parallelism), written the way a DeepLearning.scala user writes them --
+weights are `TensorWeight`s (TW:139-153), layers are `TensorLayer`s (TL:98-108), one step is `loss.train` (TL:70-76),
+the learning rate is an optimizer plugin overriding `delta` (the pattern of CumulativeFloatLayersSpec:26-32).
+Shapes, seeds and layouts follow SURVEY.md section 8(d).  Synthetic data only.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import tensors as T
+from .layers import Layers
+from .plugins import Plugins
+
+
+class Exchange:
+    """Gradient exchange of data-parallel training (new functionality): SUM all-reduce of one
+    materialised gradient buffer over NCCL / NVLink, in place.  The reference's implicit loss is a sum over the batch,
+    so N shards summed equal the full-batch gradient (no averaging)."""
+
+    def __init__(self, backend: T.Backend, rank: int, world_size: int, unique_id: bytes):
+        import ctypes as C
+        from . import _native as N
+        self.backend, self.rank, self.world_size = backend, rank, world_size
+        self._N, self._C = N, C
+        N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
+
+    @staticmethod
+    def unique_id() -> bytes:
+        import ctypes as C
+        from . import _native as N
+        buf = C.create_string_buffer(128)
+        N.check(N.lib.dls_comm_unique_id(buf))
+        return buf.raw
+
+    def allreduce(self, tensor: T.Tensor) -> T.Tensor:
+        N = self._N
+        cached = tensor.do_cache()                     # materialise the local partial gradient
+        N.check(N.lib.dls_allreduce_sum(self.backend.ctx, cached._buffer().handle, cached.size, None, 0, None))
+        return cached
+
+
+class Trainer:
+    """One mixin stack + its weights.  `optimizer_delta` = learning_rate * (all-reduced) delta (TW:155-161)."""
+
+    def __init__(self, backend: Optional[T.Backend] = None, learning_rate: float = 0.01, exchange=None):
+        self.backend = backend or T.default_backend()
+        self.learning_rate = float(learning_rate)
+        self.exchange = exchange
+
+        def delta(weight, d):
+            if self.exchange is not None:
+                d = self.exchange.allreduce(d.broadcast(weight.data.shape))
+            return d * self.learning_rate
+        self.P = Plugins(cumulative=False, optimizer_delta=delta, backend=self.backend)
+        self.L = Layers(self.P)
+        self.weights: List = []
+
+    def weight(self, shape: Sequence[int], seed: int, scale: float = 0.01):
+        """`TensorWeight.allocate(Tensor.randomNormal(shape, seed) * scale)`: counter-based RNG, so every rank of a
+        data-parallel job initialises identical replicas without a broadcast."""
+        # Box-Muller in the reference does not guard u1 == 0 (Tensors:409-425): work-item 61 ^ seed draws hash 0 and
+        # writes inf / NaN.  A seed with bit 30 set moves that work-item beyond every tensor used here.
+        w = self.P.weight(self.backend.random_normal(list(shape), seed=seed | 0x40000000) * scale)
+        self.weights.append(w)
+        return w
+
+    def run(self, loss_layer) -> float:
+        """`loss.train` then the scalar loss read back (4 bytes D2H)."""
+        out = loss_layer.train().map(lambda data: float(data.sum().flat_array()[0])).run()
+        if self.P.handled_exceptions:
+            raise self.P.handled_exceptions.pop(0)
+        return out
+
+    def parameters(self) -> List[np.ndarray]:
+        return [w.data.flat_array().reshape(w.data.shape) for w in self.weights]
+
+
+class Mlp(Trainer):
+    """Feature-major MLP: h_{l+1} = act(W_l h_l + b_l), activations `[features, batch]` (left-aligned broadcast makes the
+    bias a per-row vector).  C1: sizes (784, 500, 10), tanh hidden, linear output, loss sum((out - onehot)^2).
+    C4: sizes (4096,)*5, no bias, tanh everywhere, loss sum(out)."""
+
+    def __init__(self, sizes: Sequence[int], bias: bool = True, last_activation: str = "none", seed0: int = 11, **kw):
+        super().__init__(**kw)
+        self.sizes = list(sizes)
+        self.last_activation = last_activation
+        self.layers = []
+        seed = seed0
+        for fan_in, fan_out in zip(self.sizes[:-1], self.sizes[1:]):
+            w = self.weight([fan_out, fan_in], seed)
+            b = self.weight([fan_out], seed + 100) if bias else None
+            seed += 1
+            self.layers.append((w, b))
+
+    def forward(self, x: T.Tensor):
+        h = self.P.lift(x)
+        for i, (w, b) in enumerate(self.layers):
+            act = "tanh" if i + 1 < len(self.layers) else self.last_activation
+            h = self.L.linear(w, h, b, "row" if b is not None else "none", act)
+        return h
+
+    def step(self, x: T.Tensor, target: Optional[T.Tensor] = None) -> float:
+        out = self.forward(x)
+        return self.run(self.L.squared_error(out, target) if target is not None else out)
+
+
+class Cnn(Trainer):
+    """C3: NHWC input, three 'same' 3x3 convolutions (ReLU) with 2x nearest-neighbour down-sampling between them,
+    flatten, FC -> 256 (ReLU) -> 10, loss sum((out - onehot)^2)."""
+
+    def __init__(self, image: int = 32, channels: Sequence[int] = (3, 32, 64, 128), hidden: int = 256, classes: int = 10,
+                 seed0: int = 51, **kw):
+        super().__init__(**kw)
+        self.image, self.channels = image, list(channels)
+        self.convs = []
+        seed = seed0
+        for cin, cout in zip(self.channels[:-1], self.channels[1:]):
+            self.convs.append((self.weight([3, 3, cin, cout], seed, scale=0.05), self.weight([cout], seed + 100)))
+            seed += 1
+        side = image // (2 ** (len(self.convs) - 1))
+        self.flat = side * side * self.channels[-1]
+        self.fc1 = (self.weight([self.flat, hidden], seed), self.weight([hidden], seed + 100))
+        self.fc2 = (self.weight([hidden, classes], seed + 1), self.weight([classes], seed + 101))
+
+    def forward(self, x: T.Tensor):
+        L = self.L
+        h = self.P.lift(x)
+        batch = x.shape[0]
+        for i, (w, b) in enumerate(self.convs):
+            h = L.conv2d_3x3(h, w, b, "relu")
+            if i + 1 < len(self.convs):
+                h = L.downsample(h, 2)
+        h = L.reshape(h, [batch, self.flat])
+        h = L.linear(h, self.fc1[0], self.fc1[1], "col", "relu")
+        return L.linear(h, self.fc2[0], self.fc2[1], "col", "none")
+
+    def step(self, x: T.Tensor, target: T.Tensor) -> float:
+        return self.run(self.L.squared_error(self.forward(x), target))
+
+
+def one_hot(labels: np.ndarray, classes: int, feature_major: bool) -> np.ndarray:
+    eye = np.eye(classes, dtype=np.float32)[labels]
+    return np.ascontiguousarray(eye.T if feature_major else eye)
+
+
+def shard(array: np.ndarray, axis: int, rank: int, world_size: int) -> np.ndarray:
+    """Batch shard of one rank: contiguous split of `axis` (the batch axis) into world_size equal parts."""
+    n = array.shape[axis]
+    if n % world_size:
+        raise ValueError("batch %d is not divisible by %d ranks" % (n, world_size))
+    per = n // world_size
+    index = [slice(None)] * array.ndim
+    index[axis] = slice(rank * per, (rank + 1) * per)
+    return np.ascontiguousarray(array[tuple(index)])

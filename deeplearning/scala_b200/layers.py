@@ -1,0 +1,275 @@
+"""First-class differentiable tensor operations on top of `TensorLayer(forward)` (TL:98-108).
+
+The reference ships only `+`, `*`, `translate`, `split` and `join` for tensors (TL:164-340); every real model adds its
+own operations through the `TensorLayer.apply` extension point, writing the forward tensor expression and the backward
+`Do[Tensor] => Unit` by hand, exactly like plugins-FloatLayers does for scalars (FloatLayers.scala:58-274: `-`, `/`,
+`exp`, `log`, `abs`, `min`, `max`, ...).  This module is that set of custom layers for the new backend (SURVEY.md
+section 8(f).2): the elementwise ones mirror FloatLayers case by case, and the contractions (`matmul`, `linear`,
+`conv2d_3x3`) emit `Tensor.matmul` -- the tcgen05 GEMM -- directly instead of the host-unrolled
+`split(j).reduce(_ + _)` chains of TensorsSpec:337-393 / :144-210.
+
+Conventions (all inherited from the reference):
+  * `train` seeds the backward pass with the scalar 1.0f (TL:55, :72): the implicit loss is the SUM of the outputs;
+  * broadcasting is left-aligned (Tensors:208-222), so bias vectors live on the leading dimension (`bias_mode="row"`,
+    feature-major activations `[features, batch]`) or are reshaped to `[1, n]` (`bias_mode="col"`);
+  * a layer's forward value is pinned with `doCache` while its tape is alive and released with the `Do`.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+from . import tensors as T
+from .do import Do, sequence
+from .plugins import Plugins, Tape, TensorLayer, broadcast_then_sum
+
+_BIG = 3.4028234663852886e38
+
+
+class Layers:
+    def __init__(self, plugins: Plugins):
+        self.P = plugins
+
+    # -- helpers ---------------------------------------------------------------------------------------------------
+    def _pinned(self, inputs: Sequence, build, view=None) -> TensorLayer:
+        """`build(tapes) -> (data, backward)`; `data` is materialised and pinned (doCache) until the Do is released.
+        `view(cached, tapes)` optionally re-shapes the pinned buffer into the tape's data (same buffer)."""
+        P = self.P
+        inputs = [P.lift(i) for i in inputs]
+
+        def bind(tapes):
+            def acquire():
+                data, backward = build(tapes)
+                cached = data.do_cache()
+                tape = Tape(cached if view is None else view(cached, tapes), backward(cached))
+                return tape, cached.release
+            return Do(acquire)
+        return P.layer(sequence([i.forward() for i in inputs]).flat_map(bind))
+
+    def _lazy(self, inputs: Sequence, build) -> TensorLayer:
+        """Same, but the forward value stays a lazy expression (fused into whatever consumes it)."""
+        P = self.P
+        inputs = [P.lift(i) for i in inputs]
+
+        def make(tapes):
+            data, backward = build(tapes)
+            return Tape(data, backward(data))
+        return P.layer(sequence([i.forward() for i in inputs]).map(make))
+
+    # -- elementwise (mirrors FloatLayers.scala:58-274 on tensors) -----------------------------------------------------
+    def minus(self, a, b) -> TensorLayer:
+        def build(tapes):
+            t0, t1 = tapes
+            s0, s1 = list(t0.data.shape), list(t1.data.shape)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: broadcast_then_sum(d, s0)))
+                    t1.backward(do_delta.map(lambda d: broadcast_then_sum(-d, s1)))
+                return run
+            return t0.data - t1.data, backward
+        return self._lazy([a, b], build)
+
+    def negate(self, a) -> TensorLayer:
+        return self._unary(a, lambda x: -x, lambda d, x, y: -d)
+
+    def tanh(self, a) -> TensorLayer:
+        return self._unary(a, T.tanh, lambda d, x, y: d * (1.0 - y * y), pin=True)
+
+    def exp(self, a) -> TensorLayer:
+        return self._unary(a, T.exp, lambda d, x, y: d * y, pin=True)
+
+    def log(self, a) -> TensorLayer:
+        return self._unary(a, T.log, lambda d, x, y: d / x)
+
+    def relu(self, a) -> TensorLayer:
+        """`Tensor.max(x, fill 0)`; the derivative 1[y > 0] is `min(y * FLT_MAX, 1)` (the algebra has no comparison)."""
+        return self._unary(a, lambda x: T.maximum(x, x.backend.scalar(0.0)), lambda d, x, y: d * relu_mask(y), pin=True)
+
+    def _unary(self, a, forward, delta, pin: bool = False) -> TensorLayer:
+        def build(tapes):
+            (t0,) = tapes
+            x = t0.data
+
+            def backward(y):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: delta(d, x, y)))
+                return run
+            return forward(x), backward
+        return (self._pinned if pin else self._lazy)([a], build)
+
+    def squared_error(self, out, target) -> TensorLayer:
+        """(out - target)^2 elementwise; under `train` the loss is its sum.  `target` gets no gradient."""
+        def build(tapes):
+            t0, t1 = tapes
+            diff = t0.data - t1.data
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: d * (diff * 2.0)))
+                return run
+            return diff * diff, backward
+        return self._lazy([out, target], build)
+
+    # -- views -----------------------------------------------------------------------------------------------------
+    def reshape(self, a, new_shape) -> TensorLayer:
+        new_shape = [int(s) for s in new_shape]
+
+        def build(tapes):
+            (t0,) = tapes
+            shape0 = list(t0.data.shape)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: d.broadcast(new_shape).reshape(shape0)))
+                return run
+            return t0.data.reshape(new_shape), backward
+        return self._lazy([a], build)
+
+    def downsample(self, a, factor: int = 2) -> TensorLayer:
+        """Nearest-neighbour 1/factor resampling of the two middle dims of an NHWC tensor by `Tensor.scale`
+        (Tensors:950-965): out[b, y, x, c] = in[b, factor*y, factor*x, c].  Backward routes each delta to the sample it
+        was read from (a `scale` back up, masked to the sampled positions)."""
+        def build(tapes):
+            (t0,) = tapes
+            b, h, w, c = t0.data.shape
+            out_shape = [b, h // factor, w // factor, c]
+            mask = sample_mask(t0.data.backend, h, w, factor)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: d.broadcast(out_shape).scale([b, h, w, c]) * mask))
+                return run
+            return t0.data.scale(out_shape), backward
+        return self._lazy([a], build)
+
+    # -- contractions ------------------------------------------------------------------------------------------------
+    def matmul(self, a, b, transpose_a: bool = False, transpose_b: bool = False) -> TensorLayer:
+        return self.linear(a, b, transpose_a=transpose_a, transpose_b=transpose_b)
+
+    def linear(self, a, b, bias=None, bias_mode: str = "none", activation: str = "none", transpose_a: bool = False,
+               transpose_b: bool = False) -> TensorLayer:
+        """y = act(op(a) op(b) + bias) as ONE tcgen05 GEMM with a fused epilogue; backward is two more GEMMs
+        (delta_a = dz op(b)^T, delta_b = op(a)^T dz) and one row / column reduction for the bias.
+        Feature-major dense layer: linear(W, x, bias, "row", "tanh"); batch-major: linear(x, W, bias, "col", ...)."""
+        if activation not in ("none", "tanh", "relu"):
+            raise ValueError("linear: unknown activation %r" % (activation,))
+        inputs = [a, b] + ([bias] if bias_mode != "none" else [])
+
+        def build(tapes):
+            ta, tb = tapes[0], tapes[1]
+            A, B = ta.data, tb.data
+            bias_t = tapes[2].data if bias_mode != "none" else None
+            y = T.matmul(A, B, transpose_a=transpose_a, transpose_b=transpose_b, bias=bias_t, bias_mode=bias_mode,
+                         activation=activation)
+            out_shape = list(y.shape)
+
+            def backward(y_cached):
+                def run(do_delta: Do):
+                    memo = {}
+
+                    def dz_of(d):                                   # shared by the three consumers below
+                        if "dz" not in memo:
+                            d = d.broadcast(out_shape)
+                            if activation == "tanh":
+                                d = d * (1.0 - y_cached * y_cached)
+                            elif activation == "relu":
+                                d = d * relu_mask(y_cached)
+                            memo["dz"] = d.do_cache()
+                        return memo["dz"]
+
+                    def delta_a(d):
+                        dz = dz_of(d)
+                        if transpose_a:                             # a is stored [K, M]: delta = op(b) dz^T
+                            return T.matmul(B, dz, transpose_a=transpose_b, transpose_b=True)
+                        return T.matmul(dz, B, transpose_b=not transpose_b)
+
+                    def delta_b(d):
+                        dz = dz_of(d)
+                        if transpose_b:                             # b is stored [N, K]: delta = dz^T op(a)
+                            return T.matmul(dz, A, transpose_a=True, transpose_b=transpose_a)
+                        return T.matmul(A, dz, transpose_a=not transpose_a)
+
+                    ta.backward(do_delta.map(delta_a))
+                    tb.backward(do_delta.map(delta_b))
+                    if bias_mode != "none":
+                        axis = 1 if bias_mode == "row" else 0
+                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), axis)))
+                return run
+            return y, backward
+        return self._pinned(inputs, build)
+
+    def conv2d_3x3(self, x, w, bias=None, activation: str = "none") -> TensorLayer:
+        """'Same' 3x3 convolution of an NHWC tensor with weights [3, 3, Cin, Cout] (the layout and the index convention
+        of TensorsSpec:144-210: out[b,y,x,f] = bias[f] + sum x[b, y-(ky-1), x-(kx-1), c] * w[ky,kx,c,f], zero padding from
+        the bounds check of `translate`).  Lowered as im2col + GEMM: the nine translated views are written by ONE
+        multi-root gather launch (`Tensor.join`), then out = col[BHW, Cin*9] . wmat[Cin*9, Cout] on the tensor cores."""
+        offsets = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
+        inputs = [x, w] + ([bias] if bias is not None else [])
+
+        def build(tapes):
+            tx, tw = tapes[0], tapes[1]
+            X, W = tx.data, tw.data
+            bsz, h, wd, cin = X.shape
+            cout = W.shape[3]
+            m = bsz * h * wd
+            col = T.join([X.translate([0, oy, ox, 0]) for (oy, ox) in offsets]).reshape([m, cin * 9]).do_cache()
+            wmat = W.permute([2, 0, 1, 3]).reshape([cin * 9, cout]).do_cache()
+            bias_t = tapes[2].data if bias is not None else None
+            y = T.matmul(col, wmat, bias=bias_t, bias_mode="col" if bias is not None else "none", activation=activation)
+
+            def backward(y_cached):
+                def run(do_delta: Do):
+                    memo = {}
+
+                    def dz_of(d):
+                        if "dz" not in memo:
+                            d = d.broadcast([bsz, h, wd, cout]).reshape([m, cout])
+                            if activation == "tanh":
+                                d = d * (1.0 - y_cached * y_cached)
+                            elif activation == "relu":
+                                d = d * relu_mask(y_cached)
+                            memo["dz"] = d.do_cache()
+                        return memo["dz"]
+
+                    def delta_x(d):
+                        dcol = T.matmul(dz_of(d), wmat, transpose_b=True).reshape([bsz, h, wd, cin, 9])
+                        parts = [s.translate([0, -oy, -ox, 0]) for s, (oy, ox) in zip(dcol.split(4), offsets)]
+                        acc = parts[0]
+                        for p in parts[1:]:
+                            acc = acc + p
+                        return acc
+
+                    def delta_w(d):
+                        dw = T.matmul(col, dz_of(d), transpose_a=True)              # [Cin*9, Cout]
+                        return dw.reshape([cin, 3, 3, cout]).permute([1, 2, 0, 3])
+
+                    tx.backward(do_delta.map(delta_x))
+                    tw.backward(do_delta.map(delta_w))
+                    if bias is not None:
+                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), 0)))
+                return run
+            return y, backward
+
+        def view(cached, tapes):                                    # [B*H*W, Cout] -> [B, H, W, Cout], same buffer
+            bsz, h, wd, _ = tapes[0].data.shape
+            return cached.reshape([bsz, h, wd, tapes[1].data.shape[3]])
+        return self._pinned(inputs, build, view)
+
+
+def relu_mask(y):
+    """1[y > 0] for y = max(x, 0) >= 0, spelled with the operators the algebra has (Tensors:546-558)."""
+    return T.minimum(y * _BIG, y.backend.scalar(1.0))
+
+
+_MASKS = {}
+
+
+def sample_mask(backend, h: int, w: int, factor: int):
+    """[1, h, w, 1] tensor that is 1 where both coordinates are multiples of `factor` (broadcasts over batch and channel)."""
+    import numpy as np
+    key = (id(backend), h, w, factor)
+    if key not in _MASKS:
+        m = np.zeros((1, h, w, 1), dtype=np.float32)
+        m[0, ::factor, ::factor, 0] = 1.0
+        _MASKS[key] = backend.tensor(m).do_cache()
+    return _MASKS[key]

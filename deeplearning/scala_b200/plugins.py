@@ -102,10 +102,9 @@ class TensorLayer(Differentiable):
             self._accumulated = self.raw_forward.flat_map(self._accumulator).shared()
         return self._accumulated.map(self._cumulative_tape)
 
-    @staticmethod
-    def _accumulator(tape: Tape) -> Do:
+    def _accumulator(self, tape: Tape) -> Do:
         def acquire():
-            zero = Do.now(T.scalar(0.0))
+            zero = Do.now(self.plugins.scalar(0.0))
             state = {"delta": zero, "zero": zero}
 
             def flush():                                                     # Accumulator.release, CTL:39-52
@@ -130,7 +129,7 @@ class TensorLayer(Differentiable):
     def train(self) -> Do:
         """TL:70-76: forward, backward with the scalar delta 1.0f (TL:55), yield the forward data."""
         def step(tape):
-            tape.backward(Do.now(T.scalar(1.0)))
+            tape.backward(Do.now(self.plugins.scalar(1.0)))
             return Do.now(tape.data)
         return self.forward().flat_map(step)
 
@@ -166,13 +165,17 @@ class TensorWeight(Differentiable):
 
 
 class Plugins:
-    def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None):
+    def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None, backend=None):
         self.cumulative = cumulative
+        self.backend = backend                                                    # None = the `gpu` singleton
         self.optimizer_delta = optimizer_delta or (lambda weight, delta: delta)   # Weights.scala:46-51 default
         self.handled_exceptions: List[BaseException] = []
 
     def handle_exception(self, exc):                                         # Differentiables.scala:10-14
         self.handled_exceptions.append(exc)
+
+    def scalar(self, value: float):
+        return (self.backend or T.default_backend()).scalar(value)
 
     # -- Do helpers used by hand-written layers --------------------------------------------------------------------
     @staticmethod
@@ -185,7 +188,7 @@ class Plugins:
 
     # -- constructors ----------------------------------------------------------------------------------------------
     def lift(self, x) -> Differentiable:
-        return x if isinstance(x, Differentiable) else TensorLiteral(self, T.as_tensor(x))
+        return x if isinstance(x, Differentiable) else TensorLiteral(self, x if isinstance(x, T.Tensor) else self.scalar(float(x)))
 
     def layer(self, raw_forward: Do) -> TensorLayer:
         """TensorLayer.apply (TL:98-108): the extension point for custom differentiable operations."""
@@ -254,7 +257,7 @@ class Plugins:
         def bind(tape):
             def acquire():
                 slices = tape.data.split(dimension)
-                zero = Do.now(T.scalar(0.0))
+                zero = Do.now(self.scalar(0.0))
                 slots: List[Do] = [zero] * len(slices)
 
                 def flush():

@@ -131,6 +131,9 @@ class Backend:
         """enqueueClosure (Tensors:1163-1264): serialise, materialise every parameter tensor, launch."""
         blob, params = serialize(roots, out_shape)
         bufs = [p._buffer() for p in params]                         # Tensors:1208-1212
+        for b in bufs:
+            if b.backend is not self:                                # buffers of another context: no stream ordering
+                raise ValueError("a tensor of another Backend instance was used in this expression")
         arr = (C.c_void_p * max(1, len(bufs)))(*[b.handle for b in bufs])
         out = C.c_void_p()
         flags = N.DLS_LAUNCH_REDUCE_SUM if reduce_sum else N.DLS_LAUNCH_DEFAULT
@@ -232,6 +235,23 @@ class Backend:
                                         int(transpose_a), int(transpose_b), C.byref(opts), None, 0, C.byref(h), None))
             return DeviceBuffer(self, h, m * n)
         return ProducedTensor(self, produce, [m, n], a.padding)
+
+    def sum_axis(self, t: "Tensor", axis: int) -> "NonInlineTensor":
+        """Sum away one dimension: what TensorLayers.sumAs spells as `split(axis).reduce(_ + _)` (TL:124-162), as one
+        row / column reduction kernel (`dls_sum_axis`) instead of a host-unrolled chain of `shape[axis]` additions."""
+        shape = list(t.shape)
+        if not 0 <= axis < len(shape):
+            raise ValueError("sum_axis: axis %d out of range for shape %r" % (axis, shape))
+        outer = int(np.prod(shape[:axis], dtype=np.int64))
+        k = shape[axis]
+        inner = int(np.prod(shape[axis + 1:], dtype=np.int64))
+
+        def produce():
+            buf = t._buffer()
+            h = C.c_void_p()
+            N.check(N.lib.dls_sum_axis(self.ctx, buf.handle, outer, k, inner, None, 0, C.byref(h), None))
+            return DeviceBuffer(self, h, outer * inner)
+        return ProducedTensor(self, produce, shape[:axis] + shape[axis + 1:], t.padding)
 
     def abs(self, t): return t._derived(Unary("abs", t.closure()))
     def sqrt(self, t): return t._derived(Unary("sqrt", t.closure()))
@@ -430,7 +450,10 @@ class Tensor:
         rhs = rhs if isinstance(rhs, Tensor) else self.backend.scalar(float(rhs))
         shape = auto_broadcast_shape(self.shape, rhs.shape)
         lhs, rhs = self.broadcast(shape), rhs.broadcast(shape)
-        return lhs._derived(Binary(op, lhs.closure(), rhs.closure()))
+        out = lhs._derived(Binary(op, lhs.closure(), rhs.closure()))
+        if isinstance(lhs, FillTensor) and not isinstance(rhs, FillTensor):
+            out.backend = rhs.backend          # a literal belongs to no device: launch where the data lives
+        return out
 
     def __add__(self, o): return self._binary("add", o)
     def __sub__(self, o): return self._binary("sub", o)
@@ -439,6 +462,11 @@ class Tensor:
     def __mod__(self, o): return self._binary("mod", o)
     def __neg__(self): return self._derived(Unary("neg", self.closure()))
     def __pos__(self): return self
+    # host sugar: a Python number on the left is `Tensor.scalar(number)` (a FillTensor) combined with the same operator
+    def __radd__(self, o): return self.backend.scalar(float(o))._binary("add", self)
+    def __rsub__(self, o): return self.backend.scalar(float(o))._binary("sub", self)
+    def __rmul__(self, o): return self.backend.scalar(float(o))._binary("mul", self)
+    def __rtruediv__(self, o): return self.backend.scalar(float(o))._binary("div", self)
 
 
 class InlineTensor(Tensor):
@@ -567,6 +595,7 @@ def random(shape, seed, padding: float = 0.0): return default_backend().random(s
 def random_normal(shape, seed, padding: float = 0.0): return default_backend().random_normal(shape, seed, padding)
 def join(tensors, dimension=None): return tensors[0].backend.join(tensors, dimension)
 def matmul(a, b, **kw): return a.backend.matmul(a, b, **kw)
+def sum_axis(t, axis): return t.backend.sum_axis(t, axis)
 def abs_(t): return t.backend.abs(t)
 def sqrt(t): return t.backend.sqrt(t)
 def tanh(t): return t.backend.tanh(t)

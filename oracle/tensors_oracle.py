@@ -698,7 +698,8 @@ def maximum(a: Tensor, b: Tensor) -> InlineTensor:
 
 def round_operand(x: np.ndarray, kind: Optional[str]) -> np.ndarray:
     """What the tensor cores see of an fp32 operand: bf16 = round to nearest even to 8 significand bits (the staging
-    kernel's cvt.rn.bf16.f32); tf32 = the low 13 mantissa bits ignored (tcgen05 kind::tf32 reads 32-bit containers)."""
+    kernel's cvt.rn.bf16.f32); tf32 = round to nearest, ties away, to 11 significand bits (the staging kernel's
+    cvt.rna.tf32.f32; the tensor core itself ignores the low 13 mantissa bits, which are zero after staging)."""
     x = np.ascontiguousarray(x, dtype=F32)
     if kind is None or kind == "fp32":
         return x
@@ -708,7 +709,8 @@ def round_operand(x: np.ndarray, kind: Optional[str]) -> np.ndarray:
         out = rounded.astype(np.uint32).view(F32)
         return np.where(np.isnan(x), x, out).astype(F32)
     if kind == "tf32":
-        return (bits & 0xFFFFE000).astype(np.uint32).view(F32)
+        out = ((bits + 0x1000) & 0xFFFFE000).astype(np.uint32).view(F32)
+        return np.where(np.isfinite(x), out, x).astype(F32)
     raise ValueError(kind)
 
 
@@ -743,6 +745,20 @@ def matmul(a: Tensor, b: Tensor, transpose_a: bool = False, transpose_b: bool = 
     m = a.shape[1] if transpose_a else a.shape[0]
     n = b.shape[0] if transpose_b else b.shape[1]
     return BufferTensor(thunk, [m, n], a.padding)
+
+
+def sum_axis(t: Tensor, axis: int) -> NonInlineTensor:
+    """`t.split(axis).reduce(_ + _)` (TL:124-162): left fold over the slices, one fp32 rounding per addition."""
+    shape = list(t.shape)
+
+    def thunk():
+        a = t.materialise().reshape(shape).astype(F32)
+        a = np.moveaxis(a, axis, 0)
+        acc = a[0].copy() if a.shape[0] else np.zeros(a.shape[1:], dtype=F32)
+        for j in range(1, a.shape[0]):
+            acc = (acc + a[j]).astype(F32)
+        return acc.reshape(-1)
+    return BufferTensor(thunk, shape[:axis] + shape[axis + 1:], t.padding)
 
 
 def join(tensors: Sequence[Tensor], dimension: Optional[int] = None) -> Tensor:

@@ -1,7 +1,7 @@
 """Parity of the tcgen05 / TMEM contraction kernel (csrc/gemm_tc.cu, through `dls_matmul_ex`) with the CPU oracle.
 
 Two bars per case:
-  1. against the oracle evaluated on operands rounded the way the tensor cores read them (bf16 RNE / tf32 truncation):
+  1. against the oracle evaluated on operands rounded the way the staging kernels round them (bf16 RNE / tf32 round-to-nearest-away):
      only the fp32 accumulation order differs, so the bound is tight -- 2e-6 * sum_k |a_ik| |b_kj| per element.
      This is the check that the TMA boxes, swizzles, UMMA descriptors and the epilogue address every element correctly.
   2. against the plain fp32 chain of the reference (TensorsSpec:337-344): relative Frobenius error below the tolerance

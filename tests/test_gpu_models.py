@@ -1,0 +1,116 @@
+"""One SGD step of the BASELINE.json model configs through the product stack (TensorWeights + TensorLayers + the custom
+layers of layers.py, i.e. tcgen05 GEMM / gather / reduction / fused elementwise kernels behind the C ABI) against the
+plain-numpy restatement of the reference's autodiff rules in oracle/models_oracle.py.
+
+Bars: fp32 mode -- loss and every updated parameter within 1e-5 relative (reductions bar of north_star);
+tensor-core modes -- gradients within 2e-4 of the oracle evaluated with the same operand rounding (only the
+accumulation order differs), and within the stated 1e-3 (TF32) / 4e-3 (BF16) of the fp32 oracle.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+LR = 0.01
+
+
+@pytest.fixture(scope="module")
+def env():
+    from oracle import models_oracle as MO
+    from oracle import tensors_oracle as O
+    import deeplearning.scala_b200.tensors as B
+    import deeplearning.scala_b200.harness as H
+    B.default_backend().ctx
+    return MO, O, B, H
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30)
+
+
+def make_backend(B, mode):
+    be = B.Backend(gemm_mode=mode)
+    be.ctx
+    return be
+
+
+def mlp_case(env, mode, sizes, batch, bias, last_activation, with_target, steps=2):
+    MO, O, B, H = env
+    be = make_backend(B, mode)
+    try:
+        model = H.Mlp(sizes, bias=bias, last_activation=last_activation, backend=be, learning_rate=LR)
+        rng = np.random.RandomState(7)
+        x = rng.rand(sizes[0], batch).astype(np.float32)
+        target = H.one_hot(rng.randint(0, sizes[-1], size=batch), sizes[-1], feature_major=True) if with_target else None
+        ref = [(w.data.flat_array().reshape(w.data.shape), None if b is None else b.data.flat_array()) for w, b in model.layers]
+        rounding = None if mode == "fp32" else (lambda a: O.round_operand(a, mode))
+        out = []
+        for _ in range(steps):
+            got_loss = model.step(be.tensor(x), None if target is None else be.tensor(target))
+            before = ref
+            want_loss, ref, _ = MO.mlp_step(ref, x, target, LR, last_activation, rounding)
+            _, ref32, _ = MO.mlp_step(before, x, target, LR, last_activation, None)
+            got = [(w.data.flat_array().reshape(w.data.shape), None if b is None else b.data.flat_array()) for w, b in model.layers]
+            out.append((got_loss, want_loss, before, got, ref, ref32))
+            ref = got            # continue from the product's weights so steps do not compound differences
+        return out
+    finally:
+        be.close()
+
+
+@pytest.mark.parametrize("sizes,batch", [((20, 16, 6), 12), ((784, 500, 10), 128)], ids=["tiny", "c1"])
+def test_mlp_step_fp32(env, sizes, batch):
+    for got_loss, want_loss, before, got, ref, _ in mlp_case(env, "fp32", sizes, batch, True, "none", True):
+        assert abs(got_loss - want_loss) <= 1e-5 * abs(want_loss)
+        for (gw, gb), (rw, rb), (ow, ob) in zip(got, ref, before):
+            assert rel(ow - gw, ow - rw) <= 1e-5          # the applied update lr * gradient
+            assert rel(ob - gb, ob - rb) <= 1e-5
+            assert rel(gw, rw) <= 1e-6
+
+
+@pytest.mark.parametrize("mode,stated", [("tf32", 1e-3), ("bf16", 4e-3)])
+def test_c1_mlp_step_on_tensor_cores(env, mode, stated):
+    for got_loss, want_loss, before, got, ref, ref32 in mlp_case(env, mode, (784, 500, 10), 128, True, "none", True):
+        assert abs(got_loss - want_loss) <= 2e-4 * abs(want_loss)
+        for (gw, gb), (rw, rb), (fw, fb), (ow, ob) in zip(got, ref, ref32, before):
+            assert rel(ow - gw, ow - rw) <= 2e-4
+            assert rel(ob - gb, ob - rb) <= 2e-4
+            assert rel(ow - gw, ow - fw) <= 3 * stated    # gradients chain three rounded contractions
+            assert rel(gw, fw) <= stated
+
+
+def test_wide_mlp_sum_loss_bf16(env):
+    """C4's structure (no bias, tanh everywhere, loss = sum of outputs) at a size the oracle finishes quickly."""
+    for got_loss, want_loss, before, got, ref, _ in mlp_case(env, "bf16", (256, 256, 256), 384, False, "tanh", False, steps=1):
+        assert abs(got_loss - want_loss) <= 2e-4 * abs(want_loss) + 1e-3
+        for (gw, _), (rw, _), (ow, _) in zip(got, ref, before):
+            assert rel(ow - gw, ow - rw) <= 2e-4
+
+
+def cnn_case(env, mode, image, channels, hidden, batch):
+    MO, O, B, H = env
+    be = make_backend(B, mode)
+    try:
+        model = H.Cnn(image=image, channels=channels, hidden=hidden, classes=10, backend=be, learning_rate=LR)
+        rng = np.random.RandomState(21)
+        x = rng.rand(batch, image, image, channels[0]).astype(np.float32)
+        target = H.one_hot(rng.randint(0, 10, size=batch), 10, feature_major=False)
+        read = lambda pair: (pair[0].data.flat_array().reshape(pair[0].data.shape), pair[1].data.flat_array())
+        convs, fc1, fc2 = [read(p) for p in model.convs], read(model.fc1), read(model.fc2)
+        rounding = None if mode == "fp32" else (lambda a: O.round_operand(a, mode))
+        got_loss = model.step(be.tensor(x), be.tensor(target))
+        want_loss, nconvs, nfc1, nfc2 = MO.cnn_step(convs, fc1, fc2, x, target, LR, rounding)
+        got = [read(p) for p in model.convs] + [read(model.fc1), read(model.fc2)]
+        return got_loss, want_loss, convs + [fc1, fc2], got, nconvs + [nfc1, nfc2]
+    finally:
+        be.close()
+
+
+@pytest.mark.parametrize("mode,tol", [("fp32", 1e-5), ("tf32", 2e-4), ("bf16", 2e-4)])
+def test_cnn_step(env, mode, tol):
+    got_loss, want_loss, before, got, ref = cnn_case(env, mode, 8, (3, 4, 6, 8), 16, 4)
+    assert abs(got_loss - want_loss) <= tol * abs(want_loss)
+    for i, ((gw, gb), (rw, rb), (ow, ob)) in enumerate(zip(got, ref, before)):
+        assert rel(ow - gw, ow - rw) <= tol, "weight gradient of layer %d" % i
+        assert rel(ob - gb, ob - rb) <= tol, "bias gradient of layer %d" % i
