@@ -193,10 +193,17 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rows", type=int, default=ROWS, help="debug: smaller problem (INVALID as a bench number)")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1", "c3", "c4", "c5"],
+                    help="c2 (default) = BASELINE configs[1]; c1/c3/c4/c5 = the training configs (samples/s)")
+    ap.add_argument("--gemm-mode", default="bf16", choices=["fp32", "tf32", "bf16"], help="contraction precision of the training legs")
+    ap.add_argument("--no-train", action="store_true", help="skip the short training legs appended to the C2 line")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload != "c2":
+        main_train(args, rank, world, local)
+        return
     if args.impl == "reference":
         run_reference(args, rank)
         return
@@ -351,10 +358,170 @@ def main():
                                "cores": threads, "kind": "port",
                                "sample": "%d reps over %d of %d rows (2^24 elements): C restatement of the generated map "
                                          "kernel on %d threads + the single-work-item 16-lane sum" % (reps, sample_rows, ROWS, threads)}
-    if rank == 0:
-        print(json.dumps(out))
     sampler.stop()
     be.close()
+    if not args.no_train and rows == ROWS:
+        out["train"] = train_legs(args, rank, world, local, dist)
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+# ---- training legs (BASELINE metric "train samples/sec at 1/2/4/8 B200") ----------------------------------------------------
+
+def make_exchange(be, rank, world, dist):
+    """NCCL communicator of libdlsb200 itself (dls_comm_init); the unique id travels over torch.distributed."""
+    if world == 1:
+        return None
+    import torch
+    from deeplearning.scala_b200.harness import Exchange
+    uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        uid = torch.tensor(list(Exchange.unique_id()), dtype=torch.uint8, device="cuda")
+    dist.broadcast(uid, 0)
+    return Exchange(be, rank, world, bytes(uid.cpu().tolist()))
+
+
+def train_once(workload, args, rank, world, local, dist, steps, warmup, e2e_steps):
+    import deeplearning.scala_b200.tensors as B
+    import bench_train
+    be = B.Backend(device=local, gemm_mode=args.gemm_mode)
+    exchange = make_exchange(be, rank, world, dist) if workload == "c5" else None
+
+    def barrier():
+        be.synchronize()
+        if dist is not None:
+            dist.barrier()
+        be.synchronize()
+    r = bench_train.run(workload, be, steps, warmup, e2e_steps, exchange, rank, world, barrier)
+    times = [r["ms_total"], r["e2e_ms_per_step"]]
+    if dist is not None:
+        import torch
+        t = torch.tensor(times, device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        times = t.tolist()
+    r["ms_total"], r["e2e_ms_per_step"] = times
+    r["ms_per_step"] = times[0] / steps
+    r["samples_per_s"] = world * r["batch_per_gpu"] * steps / (times[0] / 1e3)
+    r["e2e_samples_per_s"] = world * r["batch_per_gpu"] / (times[1] / 1e3)
+    r["tflops"] = world * r["flop_per_step_per_gpu"] / (r["ms_per_step"] / 1e3) / 1e12
+    r["gemm_mode"] = args.gemm_mode
+    del exchange
+    be.close()
+    return r
+
+
+def train_legs(args, rank, world, local, dist):
+    """Short runs of the training configs appended to the C2 line: C1, C3 (as C5 when world > 1) and C4."""
+    legs = {}
+    for workload, steps in (("c1", 50), ("c5" if world > 1 else "c3", 10), ("c4", 5)):
+        try:
+            r = train_once(workload, args, rank, world, local, dist, steps, 3, 3)
+            legs[workload] = {k: r[k] for k in ("workload", "samples_per_s", "e2e_samples_per_s", "ms_per_step", "tflops",
+                                                "launches_per_step", "gemm_mode", "last_loss")}
+        except Exception as exc:                      # a training leg must never take the headline line down
+            legs[workload] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+    return legs
+
+
+def train_reference(args, rank):
+    """CPU arm of a training workload: the numpy restatement of the reference's autodiff rules (oracle/models_oracle.py)
+    on the host cores (BLAS threads), one step per timed step on the full batch of the config."""
+    if rank != 0:
+        return
+    from oracle import models_oracle as MO
+    import deeplearning.scala_b200.harness as H
+    rng = np.random.RandomState(7)
+    w = args.workload
+    if w == "c1":
+        batch, sizes = 128, (784, 500, 10)
+        weights = [(rng.randn(o, i).astype(np.float32) * 0.01, rng.randn(o).astype(np.float32) * 0.01) for i, o in zip(sizes[:-1], sizes[1:])]
+        x = rng.rand(784, batch).astype(np.float32)
+        t = H.one_hot(rng.randint(0, 10, size=batch), 10, True)
+        step = lambda: MO.mlp_step(weights, x, t, 0.01)
+        sample = "full C1 step (batch 128)"
+    elif w == "c4":
+        batch, width = 512, 4096
+        weights = [(rng.randn(width, width).astype(np.float32) * 0.01, None) for _ in range(4)]
+        x = rng.randn(width, batch).astype(np.float32)
+        step = lambda: MO.mlp_step(weights, x, None, 1e-4, "tanh")
+        sample = "C4 model on a 512-sample slice of the 8192 batch (fp64 BLAS accumulate)"
+    else:
+        batch = 32
+        chans = (3, 32, 64, 128)
+        convs = [(rng.randn(3, 3, ci, co).astype(np.float32) * 0.05, rng.randn(co).astype(np.float32) * 0.01) for ci, co in zip(chans[:-1], chans[1:])]
+        fc1 = (rng.randn(8192, 256).astype(np.float32) * 0.01, np.zeros(256, np.float32))
+        fc2 = (rng.randn(256, 10).astype(np.float32) * 0.01, np.zeros(10, np.float32))
+        x = rng.rand(batch, 32, 32, 3).astype(np.float32)
+        t = H.one_hot(rng.randint(0, 10, size=batch), 10, False)
+        step = lambda: MO.cnn_step(convs, fc1, fc2, x, t, 1e-3)
+        sample = "C3 model on a 32-sample slice of the 256 batch"
+    for _ in range(max(1, min(args.warmup, 2))):
+        step()
+    steps = max(1, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = batch * steps / dt
+    cores = os.cpu_count() or 1
+    print(json.dumps({"impl": "reference", "metric": "train samples/sec", "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+                      "steps": steps, "warmup": args.warmup, "ms_per_step": dt * 1e3 / steps, "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "f32 (fp64 accumulate)", "data": "synthetic",
+                      "config": {"workload": args.workload},
+                      "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+                      "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main_train(args, rank, world, local):
+    if args.impl == "reference":
+        train_reference(args, rank)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    workload = args.workload
+    if workload == "c3" and world > 1:
+        workload = "c5"
+    sampler = ClockSampler(local)
+    time.sleep(0.25)
+    wall0 = time.time()
+    r = train_once(workload, args, rank, world, local, dist, args.steps, args.warmup, args.e2e_steps)
+    wall1 = time.time()
+    clocks = sampler.window(wall0, wall1)
+    sampler.stop()
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    tensor_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    out = {"metric": "train samples/sec", "value": r["samples_per_s"], "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": {"fp32": "f32", "tf32": "tf32 (fp32 accumulate)", "bf16": "bf16 (fp32 accumulate)"}[args.gemm_mode],
+           "data": "synthetic",
+           "config": {"workload": r["workload"], "batch_per_gpu": r["batch_per_gpu"], "parameters": r["parameters"],
+                      "parallelism": "dp%d" % world if workload == "c5" else "single GPU replica",
+                      "l2": "working set per step exceeds L2 for c3/c4; c1 (3.6 MB) is L2 resident by nature"},
+           "clocks": clocks,
+           "e2e": {"value": r["e2e_samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": r["h2d_bytes_per_step"],
+                   "d2h_bytes_per_step": r["d2h_bytes_per_step"], "ms_per_step": r["e2e_ms_per_step"], "steps": r["e2e_steps"]},
+           "gpu_launches": int(r["launches_per_step"] * args.steps),
+           "roofline": {"kernel": "gemm_tc_kernel (all contractions of the step)", "bound": "tensor", "achieved": r["tflops"] / world,
+                        "peak": tensor_peak, "unit": "TFLOP/s", "frac": r["tflops"] / world / tensor_peak, "traffic": None,
+                        "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
+                        "note": "whole-step FLOP / whole-step time (includes elementwise, staging and host launch gaps)"},
+           "launches_per_step": r["launches_per_step"], "driver_allocs_in_timed_region": r["driver_allocs_in_timed_region"],
+           "loss": {"first": r["first_loss"], "last": r["last_loss"]}}
+    if rank == 0:
+        print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
 
