@@ -83,6 +83,28 @@ __global__ void __launch_bounds__(kBlock) sum_axis_rows_kernel(const float *__re
   }
 }
 
+// few columns, long k (bias gradients: [B*H*W, F] summed over rows): stage 1 sums `chunk` consecutive rows per lane into
+// partial[outer, chunks, inner]; stage 2 is the column kernel over the chunks.  Lanes stay coalesced along `inner`.
+__global__ void __launch_bounds__(kBlock) sum_axis_chunks_kernel(const float *__restrict__ in, float *__restrict__ partial,
+                                                                 size_t outer, size_t k, size_t inner, size_t chunks, size_t chunk) {
+  const size_t total = outer * chunks * inner;
+  for (size_t t = (size_t)blockIdx.x * kBlock + threadIdx.x; t < total; t += (size_t)gridDim.x * kBlock) {
+    const size_t i = t % inner, c = (t / inner) % chunks, o = t / (inner * chunks);
+    const size_t j0 = c * chunk, j1 = min(k, j0 + chunk);
+    const float *p = in + (o * k + j0) * inner + i;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    size_t j = j0;
+    for (; j + 4 <= j1; j += 4, p += 4 * inner) {
+      a0 += __ldg(p);
+      a1 += __ldg(p + inner);
+      a2 += __ldg(p + 2 * inner);
+      a3 += __ldg(p + 3 * inner);
+    }
+    for (; j < j1; ++j, p += inner) a0 += __ldg(p);
+    partial[t] = (a0 + a1) + (a2 + a3);
+  }
+}
+
 int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, size_t k, size_t inner, float *out) {
   cudaStream_t st = ctx->streams[stream];
   if (outer * inner == 0) return DLS_OK;
@@ -91,9 +113,26 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
     return DLS_OK;
   }
   size_t cap = (size_t)ctx->sm_count * 8;
+  const size_t lanes_wanted = (size_t)ctx->sm_count * kBlock * 4;
   if (inner == 1 && k >= 64) {
     size_t want = (outer + kBlock / 32 - 1) / (kBlock / 32);
     sum_axis_rows_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, out, outer, k);
+  } else if (outer * inner * 8 <= lanes_wanted && k >= 256) {
+    // two stages: enough chunks to fill the machine, at least 32 rows each
+    size_t chunks = std::min(lanes_wanted / (outer * inner), (k + 31) / 32);
+    const size_t chunk = (k + chunks - 1) / chunks;
+    chunks = (k + chunk - 1) / chunk;
+    Block scratch;
+    int rc = alloc_block(ctx, outer * chunks * inner * sizeof(float), stream, &scratch);
+    if (rc) return rc;
+    size_t want = (outer * chunks * inner + kBlock - 1) / kBlock;
+    sum_axis_chunks_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, (float *)scratch.ptr, outer, k, inner,
+                                                                                          chunks, chunk);
+    want = (outer * inner + kBlock - 1) / kBlock;
+    sum_axis_cols_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>((const float *)scratch.ptr, out, outer, chunks,
+                                                                                        inner);
+    free_block(ctx, scratch);   // stream ordered: the next user of the block runs after these kernels
+    ctx->stats.kernel_launches++;
   } else {
     size_t want = (outer * inner + kBlock - 1) / kBlock;
     sum_axis_cols_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, out, outer, k, inner);

@@ -135,7 +135,11 @@ template <bool TF32, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
-                   const float *__restrict__ bias, int bias_mode, int act, int direct_store) {
+                   const float *__restrict__ bias, int bias_mode, int act, int direct_store, int splits, int kb_per_split,
+                   int c_rows) {
+  // splits > 1 (split-K): work item w = split * n_tiles + tile covers k blocks [split * kb_per_split, ...) and writes its
+  // partial tile at row offset split * tiles_m * BM of a [splits * tiles_m * BM, N] scratch matrix (c_rows = its row count);
+  // the epilogue (bias / activation) then runs in splitk_reduce_kernel.
   constexpr int ELEM = TF32 ? 4 : 2;
   constexpr int BLOCK_K = 128 / ELEM;       // one 128-byte swizzle row of K per stage
   constexpr int UMMA_K = 32 / ELEM;         // K per tcgen05.mma
@@ -158,6 +162,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
   const int n_tiles = tiles_m * tiles_n;
   const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  const int n_work = n_tiles * splits;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -188,9 +193,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const Tile tc = tile_coord(t, tiles_m, tiles_n);
-        for (int kb = 0; kb < num_kb; ++kb) {
+      for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
+        const Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n);
+        const int kb0 = (w / n_tiles) * kb_per_split, kb1 = min(num_kb, kb0 + kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t a_dst = smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_dst = a_dst + A_STAGE_BYTES;
@@ -231,13 +237,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(tempty_bar(as), aphase ^ 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = (w / n_tiles) * kb_per_split, kb1 = min(num_kb, kb0 + kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
@@ -246,7 +253,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
             const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
-            umma(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u, TF32);
+            umma(d_tmem, ad, bd, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u, TF32);
           }
           umma_commit(empty_bar(stage));   // frees the smem slot once these MMAs have read it
           if (++stage == STAGES) {
@@ -263,15 +270,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     uint8_t *my_smem = epi_smem + (warp - 2) * 2 * EPI_BUF_BYTES;
     int it = 0;
     int buf = 0;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
-      const Tile tc = tile_coord(t, tiles_m, tiles_n);
+    for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
+      Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n);
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       mbar_wait(tfull_bar(as), aphase);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const int row = tc.m0 + quarter * 32 + lane;
       float row_bias = 0.f;
-      if (bias_mode == 1 && row < M) row_bias = __ldg(bias + row);
+      if (bias_mode == 1 && tc.m0 + quarter * 32 + lane < M) row_bias = __ldg(bias + tc.m0 + quarter * 32 + lane);
+      tc.m0 += (w / n_tiles) * tiles_m * BM;                      // split-K: rows of this split's partial matrix
+      const int row = tc.m0 + quarter * 32 + lane;
 #pragma unroll 1
       for (int c = 0; c < BN / EPI_CHUNK; ++c) {
         const int col0 = tc.n0 + c * EPI_CHUNK;
@@ -300,7 +308,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           f[j] = x;
         }
         if (direct_store) {
-          if (row < M) {
+          if (row < c_rows) {
             float *dst = C + (long long)row * ldc + col0;
 #pragma unroll
             for (int j = 0; j < 32; ++j)
@@ -456,18 +464,39 @@ static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, co
   return DLS_OK;
 }
 
+// out[i] = act(sum_s partial[s * stride + i] + bias), i < m * n: the second half of a split-K contraction.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restrict__ partial, float *__restrict__ out, size_t m,
+                                                            size_t n, size_t stride, int splits, const float *__restrict__ bias,
+                                                            int bias_mode, int act) {
+  const size_t total = m * n;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    float x = __ldg(partial + i);
+    for (int s = 1; s < splits; ++s) x = __fadd_rn(x, __ldg(partial + (size_t)s * stride + i));
+    if (bias_mode == 1) x = __fadd_rn(x, __ldg(bias + i / n));
+    else if (bias_mode == 2) x = __fadd_rn(x, __ldg(bias + i % n));
+    if (act == 1) x = tanhf(x);
+    else if (act == 2) x = fmaxf(x, 0.f);
+    out[i] = x;
+  }
+}
+
+struct SplitPlan {
+  int splits = 1, kb_per_split = 0, c_rows = 0;
+};
+
 template <bool TF32, bool A_MN, bool B_MN>
 static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mc,
-                          float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct) {
+                          float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct, const SplitPlan &sp) {
   auto kern = gemm_tc_kernel<TF32, A_MN, B_MN>;
   static bool configured = false;
   if (!configured) {
     DLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     configured = true;
   }
-  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * sp.splits;
   const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
-  kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct);
+  kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, sp.splits,
+                                              sp.kb_per_split, sp.c_rows);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;
@@ -539,19 +568,64 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   rc = b_mn ? make_map(&mb, dt, elem, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, mn_atom, block_k)
             : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, BN);
   if (rc) return rc;
-  const int direct = ((ldc % 4) != 0 || ((uintptr_t)C % 16) != 0) ? 1 : 0;
-  if (!direct) {
-    rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, EPI_CHUNK, 32);
+  // split-K: a contraction with few output tiles and a long K (the weight gradients of a convolution: M x N = Cin*9 x Cout,
+  // K = batch * H * W) would leave most SMs idle; cut K into `splits` ranges, one work item each, then reduce the partials.
+  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int num_kb = (K + block_k - 1) / block_k;
+  SplitPlan sp;
+  sp.kb_per_split = num_kb;
+  sp.c_rows = M;
+  if (tiles * 2 <= ctx->sm_count && num_kb >= 16 && N % 4 == 0) {
+    int want = std::min(ctx->sm_count / tiles, num_kb / 8);
+    sp.kb_per_split = (num_kb + want - 1) / want;
+    sp.splits = (num_kb + sp.kb_per_split - 1) / sp.kb_per_split;
+  }
+  cudaStream_t st = ctx->streams[stream];
+  Block scratch;
+  float *dst = C;
+  long long ld_dst = ldc;
+  GemmEpilogue kepi = epi;
+  const int m_pad = ((M + BM - 1) / BM) * BM;
+  if (sp.splits > 1) {
+    const long long ldp = (N + 3) & ~3LL;
+    rc = alloc_block(ctx, (size_t)sp.splits * m_pad * ldp * sizeof(float), stream, &scratch);
     if (rc) return rc;
+    dst = (float *)scratch.ptr;
+    ld_dst = ldp;
+    sp.c_rows = sp.splits * m_pad;
+    kepi = GemmEpilogue();
+  }
+  const int direct = ((ld_dst % 4) != 0 || ((uintptr_t)dst % 16) != 0) ? 1 : 0;
+  if (!direct) {
+    rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dst, (uint64_t)N, (uint64_t)sp.c_rows, (uint64_t)ld_dst, EPI_CHUNK, 32);
   } else {
     mc = ma;   // unused by the kernel in direct-store mode
   }
-  cudaStream_t st = ctx->streams[stream];
-  if (tf32) return launch_variant<true, false, false>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
-  if (!a_mn && !b_mn) return launch_variant<false, false, false>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
-  if (!a_mn && b_mn) return launch_variant<false, false, true>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
-  if (a_mn && !b_mn) return launch_variant<false, true, false>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
-  return launch_variant<false, true, true>(ctx, st, ma, mb, mc, C, M, N, K, ldc, epi, direct);
+  if (!rc) {
+    if (tf32) rc = launch_variant<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
+    else if (!a_mn && !b_mn) rc = launch_variant<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
+    else if (!a_mn && b_mn) rc = launch_variant<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
+    else if (a_mn && !b_mn) rc = launch_variant<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
+    else rc = launch_variant<false, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
+  }
+  if (!rc && sp.splits > 1) {
+    // partial s lives at rows [s * m_pad, s * m_pad + M) of the scratch matrix; when N is not a multiple of 4 the scratch
+    // pitch differs from N, so reduce row by row through the (m, n) index
+    if (ld_dst == N) {
+      const size_t total = (size_t)M * N;
+      const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->sm_count * 8);
+      tc::splitk_reduce_kernel<<<grid, 256, 0, st>>>(dst, C, (size_t)M, (size_t)N, (size_t)m_pad * ld_dst, sp.splits, epi.bias,
+                                                     epi.bias_mode, epi.act);
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) rc = cuda_fail(e, "splitk_reduce_kernel", __FILE__, __LINE__);
+      ctx->stats.kernel_launches++;
+    } else {
+      set_error("launch_gemm_tc: split-K needs N % 4 == 0");
+      rc = DLS_ERR_UNSUPPORTED;
+    }
+  }
+  if (scratch.ptr) free_block(ctx, scratch);
+  return rc;
 }
 
 }  // namespace dls

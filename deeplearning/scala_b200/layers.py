@@ -31,17 +31,29 @@ class Layers:
 
     # -- helpers ---------------------------------------------------------------------------------------------------
     def _pinned(self, inputs: Sequence, build, view=None) -> TensorLayer:
-        """`build(tapes) -> (data, backward)`; `data` is materialised and pinned (doCache) until the Do is released.
-        `view(cached, tapes)` optionally re-shapes the pinned buffer into the tape's data (same buffer)."""
+        """`build(tapes) -> (data, backward[, owned])`; `data` is materialised and pinned (doCache) until the Do is
+        released.  `view(cached, tapes)` optionally re-shapes the pinned buffer into the tape's data (same buffer).
+        `owned` lists further pinned buffers (im2col matrix, dz, ...) that are released with the Do, so device memory is
+        returned to the allocator at a deterministic point instead of whenever the host collector finds the closures
+        (with plain TensorLayers every backward has run by then; CumulativeTensorLayers flush later, so there the
+        buffers are left to the collector)."""
         P = self.P
         inputs = [P.lift(i) for i in inputs]
 
         def bind(tapes):
             def acquire():
-                data, backward = build(tapes)
+                built = build(tapes)
+                data, backward = built[0], built[1]
+                owned = built[2] if len(built) > 2 else []
                 cached = data.do_cache()
                 tape = Tape(cached if view is None else view(cached, tapes), backward(cached))
-                return tape, cached.release
+
+                def release():
+                    cached.release()
+                    if not P.cumulative:
+                        while owned:
+                            owned.pop().release()
+                return tape, release
             return Do(acquire)
         return P.layer(sequence([i.forward() for i in inputs]).flat_map(bind))
 
@@ -162,6 +174,7 @@ class Layers:
             y = T.matmul(A, B, transpose_a=transpose_a, transpose_b=transpose_b, bias=bias_t, bias_mode=bias_mode,
                          activation=activation)
             out_shape = list(y.shape)
+            owned = []
 
             def backward(y_cached):
                 def run(do_delta: Do):
@@ -175,6 +188,7 @@ class Layers:
                             elif activation == "relu":
                                 d = d * relu_mask(y_cached)
                             memo["dz"] = d.do_cache()
+                            owned.append(memo["dz"])
                         return memo["dz"]
 
                     def delta_a(d):
@@ -195,7 +209,7 @@ class Layers:
                         axis = 1 if bias_mode == "row" else 0
                         tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), axis)))
                 return run
-            return y, backward
+            return y, backward, owned
         return self._pinned(inputs, build)
 
     def conv2d_3x3(self, x, w, bias=None, activation: str = "none") -> TensorLayer:
@@ -216,6 +230,7 @@ class Layers:
             wmat = W.permute([2, 0, 1, 3]).reshape([cin * 9, cout]).do_cache()
             bias_t = tapes[2].data if bias is not None else None
             y = T.matmul(col, wmat, bias=bias_t, bias_mode="col" if bias is not None else "none", activation=activation)
+            owned = [col, wmat]
 
             def backward(y_cached):
                 def run(do_delta: Do):
@@ -229,6 +244,7 @@ class Layers:
                             elif activation == "relu":
                                 d = d * relu_mask(y_cached)
                             memo["dz"] = d.do_cache()
+                            owned.append(memo["dz"])
                         return memo["dz"]
 
                     def delta_x(d):
@@ -248,7 +264,7 @@ class Layers:
                     if bias is not None:
                         tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), 0)))
                 return run
-            return y, backward
+            return y, backward, owned
 
         def view(cached, tapes):                                    # [B*H*W, Cout] -> [B, H, W, Cout], same buffer
             bsz, h, wd, _ = tapes[0].data.shape

@@ -63,6 +63,9 @@ SHAPES = [
     (1, 1, 1, False, False),
     (129, 257, 65, True, False),
     (1500, 1100, 333, False, True),    # more tiles than one wave of accumulators per CTA
+    (27, 32, 20000, True, False),      # split-K: conv1 weight gradient shape (one tile, very long K)
+    (288, 64, 8192, True, False),      # split-K with three row tiles
+    (40, 100, 5000, False, True),      # split-K, K-major operands, ragged
 ]
 
 
@@ -103,3 +106,19 @@ def test_empty_contraction(backends):
     for mode in ("fp32", "bf16", "tf32"):
         got = B.matmul(B.tensor(a), B.tensor(b), mode=mode).flat_array()
         assert got.shape == (32,) and (got == 0).all()
+
+
+@pytest.mark.parametrize("shape", [(1, 70000, 32), (3, 5000, 10), (1, 300, 4096), (64, 1000, 1), (2, 37, 5), (1, 262144, 8)],
+                         ids=lambda s: "%dx%dx%d" % s)
+def test_sum_axis(backends, shape):
+    """`split(axis).reduce(_ + _)` (TL:124-162) as one reduction: column kernel, two-stage tall kernel, row kernel."""
+    O, B = backends
+    outer, k, inner = shape
+    x = np.random.RandomState(k).standard_normal((outer, k, inner)).astype(np.float32)
+    got = B.sum_axis(B.tensor(x), 1).flat_array().reshape(outer, inner)
+    want = x.astype(np.float64).sum(axis=1)
+    scale = np.abs(x).astype(np.float64).sum(axis=1) + 1e-30
+    assert (np.abs(got - want) / scale).max() <= 1e-5
+    if k <= 5000:
+        fold = O.sum_axis(O.tensor(x), 1).flat_array().reshape(outer, inner)
+        assert (np.abs(got - fold) / scale).max() <= 1e-5
