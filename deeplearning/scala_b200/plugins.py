@@ -146,7 +146,12 @@ class TensorWeight(Differentiable):
 
     def forward(self) -> Do:
         def acquire():
-            data = self.data                                                 # TW:31 data.doCache (already pinned)
+            # TW:31 `data.doCache`: the tape holds its OWN reference to the weight buffer (clRetainMemObject in the
+            # reference), so a backward pass that swaps the weight does not pull the buffer from under other consumers.
+            # It is dropped with the tape object rather than at the Do's release: the reference's own specs read the
+            # result of `train` after running it (CumulativeTensorLayersSpec:96-127).
+            current = self.data
+            data = T.CachedTensor(current.backend, current._buffer(), list(current.shape), current.padding)
 
             def backward(do_delta: Do):
                 try:
@@ -159,9 +164,9 @@ class TensorWeight(Differentiable):
     def backward(self, original_delta: Do):
         """TW:50-74: delta = optimizer.delta; newData = (data - delta).doCache; release the old buffer; swap."""
         delta = original_delta.map(lambda d: self.plugins.optimizer_delta(self, d)).run()
-        # The old buffer is released when the last tape that pinned it goes away (TW:31 retains it per forward);
-        # here that is the DeviceBuffer reference count.
-        self.data = (self.data - delta).do_cache()
+        old = self.data
+        self.data = (old - delta).do_cache()
+        old.release()                                                        # TW:65-72; tapes keep their own reference
 
 
 class Plugins:

@@ -519,9 +519,13 @@ class NonInlineTensor(Tensor):
     _ident = None
 
     def closure(self):
-        if self._ident is None:
-            self._ident = Ident(self)
-        return self._ident
+        # one Ident per tensor while any tree still uses it (so `t + t` shares the leaf); held weakly, because a strong
+        # tensor <-> Ident cycle would keep device buffers alive until the host's cycle collector runs
+        ident = self._ident() if self._ident is not None else None
+        if ident is None:
+            ident = Ident(self)
+            self._ident = weakref.ref(ident)
+        return ident
 
 
 class ProducedTensor(NonInlineTensor):

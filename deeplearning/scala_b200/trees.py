@@ -32,7 +32,7 @@ class Literal(Node):
 
 class Ident(Node):
     """Extract(ArrayParameter(id = tensor)) (Tensors.scala:1126-1132)."""
-    __slots__ = ("tensor",)
+    __slots__ = ("tensor", "__weakref__")
 
     def __init__(self, tensor):
         self.tensor = tensor
