@@ -185,6 +185,9 @@ def run_reference(args, rank):
 
 
 def main():
+    # NCCL prints its version banner to stdout at NCCL_DEBUG=VERSION and above; stdout carries exactly one JSON line
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE"):
+        os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)

@@ -114,3 +114,54 @@ def test_cnn_step(env, mode, tol):
     for i, ((gw, gb), (rw, rb), (ow, ob)) in enumerate(zip(got, ref, before)):
         assert rel(ow - gw, ow - rw) <= tol, "weight gradient of layer %d" % i
         assert rel(ob - gb, ob - rb) <= tol, "bias gradient of layer %d" % i
+
+
+def _dp_rank(rank, world, uid_queue, out_queue):
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import deeplearning.scala_b200.tensors as B
+    import deeplearning.scala_b200.harness as H
+    be = B.Backend(device=rank, gemm_mode="fp32")
+    be.ctx
+    if rank == 0:
+        uid = H.Exchange.unique_id()
+        for _ in range(world - 1):
+            uid_queue.put(uid)
+    else:
+        uid = uid_queue.get(timeout=120)
+    ex = H.Exchange(be, rank, world, uid)
+    model = H.Mlp((24, 16, 6), bias=True, backend=be, learning_rate=LR, exchange=ex)
+    rng = np.random.RandomState(5)
+    x = rng.rand(24, 16).astype(np.float32)
+    t = H.one_hot(rng.randint(0, 6, size=16), 6, feature_major=True)
+    before = [(w.data.flat_array().reshape(w.data.shape), b.data.flat_array()) for w, b in model.layers]
+    loss = model.step(be.tensor(H.shard(x, 1, rank, world)), be.tensor(H.shard(t, 1, rank, world)))
+    after = [(w.data.flat_array().reshape(w.data.shape), b.data.flat_array()) for w, b in model.layers]
+    out_queue.put((rank, loss, before, after, x, t))
+    be.close()
+
+
+def test_data_parallel_step_equals_the_full_batch_step(env):
+    """C5's exchange on two B200s: replicas initialised from the same counter-based RNG, batch sharded, every weight
+    gradient SUM-all-reduced over NCCL before the update  ==  the oracle's full-batch step."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (ranks must not share a device)")
+    import torch.multiprocessing as mp
+    MO = env[0]
+    ctx = mp.get_context("spawn")
+    uid_q, out_q = ctx.Queue(), ctx.Queue()
+    procs = [ctx.Process(target=_dp_rank, args=(r, 2, uid_q, out_q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = sorted([out_q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=60)
+    (_, loss0, before, after0, x, t), (_, loss1, _, after1, _, _) = results
+    want_loss, want, _ = MO.mlp_step(before, x, t, LR)
+    assert abs((loss0 + loss1) - want_loss) <= 1e-5 * abs(want_loss)
+    for (w0, b0), (w1, b1), (rw, rb), (ow, ob) in zip(after0, after1, want, before):
+        assert (w0 == w1).all() and (b0 == b1).all()            # replicas stay bit-identical
+        assert rel(ow - w0, ow - rw) <= 1e-5
+        assert rel(ob - b0, ob - rb) <= 1e-5
