@@ -42,6 +42,8 @@ struct GatherArgs {
   const Instr *code;
   const GLeaf *leaves;
   const double *dpool;
+  const GLoop *loops;
+  const long long *lpool;
   long long n;
   long long shape[kMaxRank];
   int32_t rank;
@@ -281,6 +283,72 @@ __device__ __forceinline__ float gather_leaf(const GatherArgs &A, unsigned int l
   return ok ? __ldg(p + addr) : L->padding;
 }
 
+// One leaf of a folded chain: the launch-coordinate part of its address is computed once, the per-term constant comes
+// from the loop table (uniform loads: every lane is at the same term).
+struct LoopLeaf {
+  const float *p;
+  const long long *tab;
+  long long lin;                       // LL_LINEAR: sum_x g_x * ls_x
+  long long gy[kLoopMonoRows];         // LL_MONO: g_col * coef per row
+  long long extent[kLoopMonoRows], stride[kLoopMonoRows];
+  unsigned checked;
+  int rows, kind;
+  float padding;
+};
+
+__device__ __forceinline__ void loop_leaf_init(LoopLeaf &S, const GatherArgs &A, const GLoop *G, int pos, const long long *g) {
+  const GLeaf *L = A.leaves + G->leaf[pos];
+  S.p = A.params[L->param];
+  S.tab = A.lpool + G->table[pos];
+  S.kind = G->leaf_kind[pos];
+  S.padding = L->padding;
+  S.rows = L->rows;
+  S.lin = 0;
+  S.checked = 0;
+  if (S.kind == LL_LINEAR) {
+    for (int d = 0; d < A.rank; ++d) S.lin += g[d] * L->ls[d];
+  } else {
+#pragma unroll
+    for (int y = 0; y < kLoopMonoRows; ++y) {
+      const GRow &R = L->row[y];
+      const bool live = y < S.rows;
+      S.gy[y] = live && R.col >= 0 ? g[R.col] * R.coef : 0;
+      S.extent[y] = live ? R.extent : 1;
+      S.stride[y] = live ? R.stride : 0;
+      if (live && R.checked) S.checked |= 1u << y;
+    }
+  }
+}
+
+__device__ __forceinline__ float loop_leaf_at(const LoopLeaf &S, int t) {
+  if (S.kind == LL_LINEAR) return __ldg(S.p + S.lin + __ldg(S.tab + t));
+  bool ok = true;
+  long long addr = 0;
+  const long long *row = S.tab + (long long)t * S.rows;
+#pragma unroll
+  for (int y = 0; y < kLoopMonoRows; ++y) {
+    if (y < S.rows) {
+      const long long idx = S.gy[y] + __ldg(row + y);
+      if (S.checked & (1u << y)) ok = ok && idx >= 0 && idx < S.extent[y];
+      addr += idx * S.stride[y];
+    }
+  }
+  return ok ? __ldg(S.p + addr) : S.padding;
+}
+
+__device__ __noinline__ float run_loop(const GatherArgs &A, const GLoop *G, const long long *g, float acc) {
+  LoopLeaf a, b;
+  loop_leaf_init(a, A, G, 0, g);
+  const int n = G->count;
+  if (G->kind == LOOP_MAC) {
+    loop_leaf_init(b, A, G, 1, g);
+    for (int t = 0; t < n; ++t) acc = __fadd_rn(acc, __fmul_rn(loop_leaf_at(a, t), loop_leaf_at(b, t)));
+  } else {
+    for (int t = 0; t < n; ++t) acc = __fadd_rn(acc, loop_leaf_at(a, t));
+  }
+  return acc;
+}
+
 template <bool IDX32>
 __global__ void __launch_bounds__(kBlock) ew_gather_kernel(const __grid_constant__ GatherArgs A) {
   extern __shared__ float slot_f[];  // [slot][thread]
@@ -320,6 +388,8 @@ __global__ void __launch_bounds__(kBlock) ew_gather_kernel(const __grid_constant
       else if (op == OP_STORE) {
         if (A.reduce) tsum += acc;
         else A.out[(long long)e * A.n_roots + in.operand] = acc;
+      } else if (op == OP_LOOP) {
+        acc = run_loop(A, A.loops + in.operand, g, acc);
       } else {
         float f = gather_leaf<IDX32>(A, in.aux, g);
         float p = __fmul_rn(f, s);
@@ -355,15 +425,21 @@ static int upload_tables(Plan &P) {
   size_t code_b = P.code.size() * sizeof(Instr);
   size_t leaf_b = P.gleaves.size() * sizeof(GLeaf);
   size_t pool_b = P.dpool.size() * sizeof(double);
+  size_t loop_b = P.loops.size() * sizeof(GLoop);
+  size_t lpool_b = P.lpool.size() * sizeof(long long);
   auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
   P.d_code_off = 0;
   P.d_leaf_off = up(code_b);
   P.d_pool_off = P.d_leaf_off + up(leaf_b);
-  P.d_tables_bytes = P.d_pool_off + up(pool_b) + 256;
+  P.d_loop_off = P.d_pool_off + up(pool_b);
+  P.d_lpool_off = P.d_loop_off + up(loop_b);
+  P.d_tables_bytes = P.d_lpool_off + up(lpool_b) + 256;
   std::vector<uint8_t> host(P.d_tables_bytes, 0);
   memcpy(host.data() + P.d_code_off, P.code.data(), code_b);
   if (leaf_b) memcpy(host.data() + P.d_leaf_off, P.gleaves.data(), leaf_b);
   if (pool_b) memcpy(host.data() + P.d_pool_off, P.dpool.data(), pool_b);
+  if (loop_b) memcpy(host.data() + P.d_loop_off, P.loops.data(), loop_b);
+  if (lpool_b) memcpy(host.data() + P.d_lpool_off, P.lpool.data(), lpool_b);
   DLS_CUDA(cudaMalloc(&P.d_tables, P.d_tables_bytes));
   DLS_CUDA(cudaMemcpy(P.d_tables, host.data(), P.d_tables_bytes, cudaMemcpyHostToDevice));
   return DLS_OK;
@@ -439,6 +515,8 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
     A.code = reinterpret_cast<const Instr *>((const uint8_t *)P.d_tables + P.d_code_off);
     A.leaves = reinterpret_cast<const GLeaf *>((const uint8_t *)P.d_tables + P.d_leaf_off);
     A.dpool = reinterpret_cast<const double *>((const uint8_t *)P.d_tables + P.d_pool_off);
+    A.loops = reinterpret_cast<const GLoop *>((const uint8_t *)P.d_tables + P.d_loop_off);
+    A.lpool = reinterpret_cast<const long long *>((const uint8_t *)P.d_tables + P.d_lpool_off);
     A.n = P.n_elems;
     for (int d = 0; d < kMaxRank; ++d) A.shape[d] = d < P.out_rank ? P.out_shape[d] : 1;
     A.rank = P.out_rank;

@@ -28,6 +28,8 @@ int launch_to_tf32(dls_ctx *ctx, int stream, const float *in, float *out, long l
 int launch_transpose_f32(dls_ctx *ctx, int stream, const float *in, float *out, int rows, int cols, long long pitch);
 
 // matmul.cu
+int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k,
+               bool transpose_a, bool transpose_b, int bias_mode, int activation, dls_buf *c);
 int launch_sgemm(dls_ctx *ctx, int stream, const float *A, const float *B, float *C, int M, int N, int K, bool ta, bool tb);
 
 }  // namespace dls

@@ -160,6 +160,44 @@ int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long ro
 
 }  // namespace
 
+namespace dls {
+
+// c[M, N] = act(op(a) op(b) + bias) on `stream` (inputs already waited for): the body of dls_matmul_ex, also the
+// target of trees that the lowering recognised as one dense contraction (Plan::contraction).
+int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k,
+               bool transpose_a, bool transpose_b, int bias_mode, int activation, dls_buf *c) {
+  if (m * n == 0) return DLS_OK;
+  const float *bias_ptr = bias_mode ? bias->ptr : nullptr;
+  if (k == 0) {
+    DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
+    return launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
+  }
+  if (mode == DLS_GEMM_FP32) {
+    int rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, c->ptr, (int)m, (int)n, (int)k, transpose_a, transpose_b);
+    if (!rc) rc = launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
+    return rc;
+  }
+  const void *pa, *pb;
+  long long lda, ldb;
+  bool a_mn, b_mn;
+  // a is stored [K][M] when transposed (contraction index = row index), else [M][K]
+  int rc = stage_operand(ctx, stream, mode, a, transpose_a ? k : m, transpose_a ? m : k, transpose_a, &pa, &lda, &a_mn);
+  // b is stored [N][K] when transposed, else [K][N] (contraction index = row index); the same buffer on both sides with
+  // two different interpretations must not evict the first staged copy
+  Block own;
+  if (!rc) rc = stage_operand(ctx, stream, mode, b, transpose_b ? n : k, transpose_b ? k : n, !transpose_b, &pb, &ldb, &b_mn,
+                              a == b ? &own : nullptr);
+  GemmEpilogue epi;
+  epi.bias = bias_ptr;
+  epi.bias_mode = bias_mode;
+  epi.act = activation;
+  if (!rc) rc = launch_gemm_tc(ctx, stream, mode, pa, a_mn, lda, pb, b_mn, ldb, c->ptr, (long long)n, (int)m, (int)n, (int)k, epi);
+  if (own.ptr) free_block(ctx, own);
+  return rc;
+}
+
+}  // namespace dls
+
 extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k, int transpose_a,
                              int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
                              dls_event **done) {
@@ -184,36 +222,7 @@ extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias
   dls_buf *c = nullptr;
   rc = new_buf(ctx, m * n, stream, &c);
   if (rc) return rc;
-  if (m * n != 0) {
-    if (mode == DLS_GEMM_FP32) {
-      if (k == 0) DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
-      else rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, c->ptr, (int)m, (int)n, (int)k, transpose_a != 0, transpose_b != 0);
-      if (!rc) rc = launch_bias_act(ctx, stream, c->ptr, m, n, o.bias_mode ? bias->ptr : nullptr, o.bias_mode, o.activation);
-    } else {
-      // K == 0 still runs the epilogue over a zero accumulator?  No MMA would ever be issued: handle on the slow path.
-      if (k == 0) {
-        DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
-        rc = launch_bias_act(ctx, stream, c->ptr, m, n, o.bias_mode ? bias->ptr : nullptr, o.bias_mode, o.activation);
-      } else {
-        const void *pa, *pb;
-        long long lda, ldb;
-        bool a_mn, b_mn;
-        // a is stored [K][M] when transposed (contraction index = row index), else [M][K]
-        rc = stage_operand(ctx, stream, mode, a, transpose_a ? k : m, transpose_a ? m : k, transpose_a != 0, &pa, &lda, &a_mn);
-        // b is stored [N][K] when transposed, else [K][N] (contraction index = row index)
-        // the same buffer on both sides with two different interpretations: the second copy must not evict the first
-        Block own;
-        if (!rc) rc = stage_operand(ctx, stream, mode, b, transpose_b ? n : k, transpose_b ? k : n, transpose_b == 0, &pb, &ldb, &b_mn,
-                                    a == b ? &own : nullptr);
-        GemmEpilogue epi;
-        epi.bias = o.bias_mode ? bias->ptr : nullptr;
-        epi.bias_mode = o.bias_mode;
-        epi.act = o.activation;
-        if (!rc) rc = launch_gemm_tc(ctx, stream, mode, pa, a_mn, lda, pb, b_mn, ldb, c->ptr, (long long)n, (int)m, (int)n, (int)k, epi);
-        if (own.ptr) free_block(ctx, own);
-      }
-    }
-  }
+  rc = run_matmul(ctx, stream, mode, a, b, bias, m, n, k, transpose_a != 0, transpose_b != 0, o.bias_mode, o.activation, c);
   if (!rc) rc = finish_output(ctx, stream, &c, 1, ins, 3, done);
   if (rc) {
     dls_buf_release(c);

@@ -2,6 +2,7 @@
 #include <string.h>
 
 #include "common.h"
+#include "gemm_tc.h"
 
 using namespace dls;
 
@@ -70,7 +71,15 @@ int dls_launch_tree(dls_ctx *ctx, const uint8_t *tree, size_t tree_len, dls_buf 
   dls_buf *o = nullptr;
   rc = new_buf(ctx, reduce ? 1 : (size_t)P.n_elems * P.n_roots, stream, &o);
   if (rc) return rc;
-  rc = launch_plan(ctx, stream, *cp, params, o, reduce);
+  // a tree that is nothing but one dense contraction (the unrolled matmuls of TensorsSpec:337-344 / :371-383) runs on the
+  // tcgen05 GEMM when the context asks for tensor-core contractions; in fp32 mode the folded device loop keeps the
+  // chain's exact left-fold rounding
+  const Plan::Contraction &ct = P.contraction;
+  if (ct.valid && !reduce && ctx->opts.gemm_mode != DLS_GEMM_FP32)
+    rc = run_matmul(ctx, stream, ctx->opts.gemm_mode, params[ct.param_a], params[ct.param_b], nullptr, (size_t)ct.m, (size_t)ct.n,
+                    (size_t)ct.k, ct.transpose_a, ct.transpose_b, 0, 0, o);
+  else
+    rc = launch_plan(ctx, stream, *cp, params, o, reduce);
   if (!rc) rc = finish_output(ctx, stream, &o, 1, params, n_params, done);
   if (rc) {
     dls_buf_release(o);

@@ -98,6 +98,7 @@ struct LeafInfo {
   long long ls[kMaxRank] = {0};  // per launch dim (G_STRIDED / G_SCALAR: zeros)
   GRow row[kMaxRank];
   std::vector<double> mat;        // G_GENERIC: literal-rounded matrix rows*(r+1)
+  bool mono_ok = false;           // every row is an integer row with <= 1 launch coordinate (row[] is filled in)
 };
 
 struct Lowering {
@@ -117,6 +118,8 @@ struct Lowering {
   int classify_leaf(Node &nd);
   int choose_kernel();
   int emit_all();
+  int compress_loops();
+  void detect_contraction();
 
   // ---- code emission state ----
   std::vector<int> slot_of;        // node -> permanent slot (shared sub-expressions), -1 if none
@@ -299,6 +302,7 @@ int Lowering::classify_leaf(Node &nd) {
   }
   if (q == 0) {  // KB:351-356 / KB:436-451 with an empty shape: `*p`, never checked
     L.mode = G_SCALAR;
+    L.mono_ok = true;
     leaves.push_back(L);
     return 0;
   }
@@ -314,6 +318,7 @@ int Lowering::classify_leaf(Node &nd) {
       L.ls[y] = pst[y];
     }
     L.mode = any_checked ? G_MONO : G_STRIDED;
+    L.mono_ok = true;
     leaves.push_back(L);
     return 0;
   }
@@ -366,6 +371,7 @@ int Lowering::classify_leaf(Node &nd) {
       all_mono = false;
     }
   }
+  L.mono_ok = all_int && all_mono;
   if (all_int && !any_checked) {
     L.mode = G_STRIDED;
     for (int y = 0; y < q; ++y) {
@@ -544,11 +550,238 @@ int Lowering::emit_all() {
 }
 
 
+// ---- folding host-unrolled chains back into device loops ------------------------------------------------------------------
+// After emission a chain `((t0 + t1) + t2) + ...` is a run of OP_MAC (t = leaf * leaf) or OP_ADD (t = leaf) instructions whose
+// leaves differ only in constant offsets.  A run of >= kLoopMinTerms compatible terms becomes one OP_LOOP.
+namespace {
+
+bool linear_mode(const LeafInfo &L) { return L.mode == G_SCALAR || L.mode == G_STRIDED; }
+
+bool linear_compatible(const LeafInfo &A, const LeafInfo &B) {
+  if (A.param != B.param || !linear_mode(A) || !linear_mode(B)) return false;
+  for (int d = 0; d < kMaxRank; ++d)
+    if (A.ls[d] != B.ls[d]) return false;
+  return true;
+}
+
+bool mono_compatible(const LeafInfo &A, const LeafInfo &B) {
+  if (A.param != B.param || !A.mono_ok || !B.mono_ok || A.rows != B.rows || A.rows > kLoopMonoRows || A.rows == 0) return false;
+  if (A.mode == G_GENERIC || B.mode == G_GENERIC) return false;
+  for (int y = 0; y < A.rows; ++y) {
+    const GRow &a = A.row[y], &b = B.row[y];
+    const long long ca = a.col >= 0 ? a.coef : 0, cb = b.col >= 0 ? b.coef : 0;
+    if (ca != cb || (ca != 0 && a.col != b.col) || a.extent != b.extent || a.stride != b.stride) return false;
+  }
+  return true;
+}
+
+}  // namespace
+
+int Lowering::compress_loops() {
+  std::vector<Instr> &code = plan->code;
+  std::vector<Instr> out;
+  out.reserve(code.size());
+  size_t i = 0;
+  while (i < code.size()) {
+    const Instr in = code[i];
+    const bool mac = in.op == OP_MAC && in.src == SRC_LEAF;
+    const bool add = in.op == OP_ADD && in.src == SRC_LEAF;
+    if (!mac && !add) {
+      out.push_back(in);
+      ++i;
+      continue;
+    }
+    size_t j = i;
+    while (j < code.size() && code[j].op == in.op && code[j].src == SRC_LEAF) ++j;
+    const int n_pos = mac ? 2 : 1;
+    auto leaf_id = [&](size_t t, int pos) -> int { return mac && pos == 0 ? (int)code[t].aux : (int)code[t].operand; };
+    size_t best = j - i;
+    int kind_of[2] = {LL_LINEAR, LL_LINEAR};
+    for (int pos = 0; pos < n_pos && best >= (size_t)kLoopMinTerms; ++pos) {
+      const LeafInfo &L0 = leaves[leaf_id(i, pos)];
+      size_t lin = 0, mono = 0;
+      while (lin < best && linear_compatible(L0, leaves[leaf_id(i + lin, pos)])) ++lin;
+      while (mono < best && mono_compatible(L0, leaves[leaf_id(i + mono, pos)])) ++mono;
+      kind_of[pos] = lin >= mono ? LL_LINEAR : LL_MONO;
+      best = std::min(best, std::max(lin, mono));
+    }
+    if (best < (size_t)kLoopMinTerms || best > 0x7fffffffu) {
+      out.push_back(in);
+      ++i;
+      continue;
+    }
+    // a leaf position may have been classed LINEAR on a longer prefix than the run finally taken: re-check the class
+    for (int pos = 0; pos < n_pos; ++pos) {
+      const LeafInfo &L0 = leaves[leaf_id(i, pos)];
+      bool lin = true;
+      for (size_t t = 0; t < best && lin; ++t) lin = linear_compatible(L0, leaves[leaf_id(i + t, pos)]);
+      kind_of[pos] = lin ? LL_LINEAR : LL_MONO;
+    }
+    GLoop G;
+    memset(&G, 0, sizeof(G));
+    G.kind = mac ? LOOP_MAC : LOOP_ADD;
+    G.count = (int32_t)best;
+    for (int pos = 0; pos < n_pos; ++pos) {
+      LeafInfo T = leaves[leaf_id(i, pos)];   // template = the first term's leaf
+      G.leaf_kind[pos] = kind_of[pos];
+      G.table[pos] = (long long)plan->lpool.size();
+      if (kind_of[pos] == LL_LINEAR) {
+        for (size_t t = 0; t < best; ++t) plan->lpool.push_back(leaves[leaf_id(i + t, pos)].base);
+        T.base = 0;
+        if (T.mode == G_SCALAR) T.mode = G_STRIDED;   // a rank-0 parameter: address = table[t] = 0
+      } else {
+        T.mode = G_MONO;
+        for (size_t t = 0; t < best; ++t) {
+          const LeafInfo &Lt = leaves[leaf_id(i + t, pos)];
+          for (int y = 0; y < T.rows; ++y) {
+            plan->lpool.push_back(Lt.row[y].off);
+            if (Lt.row[y].checked) T.row[y].checked = 1;   // checking a row that cannot fail is harmless
+          }
+        }
+        for (int y = 0; y < T.rows; ++y) {
+          T.row[y].off = 0;
+          if (T.row[y].col < 0) T.row[y].coef = 0;
+        }
+      }
+      leaves.push_back(T);
+      G.leaf[pos] = (int32_t)leaves.size() - 1;
+    }
+    Instr L;
+    L.op = OP_LOOP;
+    L.src = SRC_NONE;
+    L.aux = 0;
+    L.operand = (uint32_t)plan->loops.size();
+    plan->loops.push_back(G);
+    out.push_back(L);
+    i += best;
+  }
+  if (plan->loops.empty()) return 0;
+  code.swap(out);
+  // drop the leaves only the folded terms referenced, renumber the rest
+  std::vector<int> remap(leaves.size(), -1);
+  std::vector<LeafInfo> kept;
+  auto use = [&](int l) -> int {
+    if (remap[l] < 0) {
+      remap[l] = (int)kept.size();
+      kept.push_back(leaves[l]);
+    }
+    return remap[l];
+  };
+  for (Instr &in : code) {
+    if (in.op == OP_MAC || in.op == OP_MSUB) in.aux = (uint16_t)use(in.aux);
+    if (in.src == SRC_LEAF) in.operand = (uint32_t)use((int)in.operand);
+  }
+  for (GLoop &G : plan->loops)
+    for (int pos = 0; pos < (G.kind == LOOP_MAC ? 2 : 1); ++pos) G.leaf[pos] = use(G.leaf[pos]);
+  leaves.swap(kept);
+  return 0;
+}
+
+// A launch that is nothing but out[M, N] = sum_t A[.., t] * B[t, ..] over dense row-major parameters: the two matmul
+// formulations of the reference (TensorsSpec:337-344 single root over [i, k]; :371-383 one root per output column).
+void Lowering::detect_contraction() {
+  Plan &P = *plan;
+  const int R = P.n_roots;
+  if (P.loops.size() != (size_t)R) return;
+  const size_t per_root = R == 1 ? 3 : 4;             // LOAD, MUL, LOOP [, STORE]
+  if (P.code.size() != per_root * R + 1) return;
+  long long K = 0, a0 = 0, sa = 0, b0 = 0, sb = 0, nb = 0;
+  int la = -1, lb = -1;
+  for (int c = 0; c < R; ++c) {
+    const Instr *I = P.code.data() + per_root * c;
+    if (I[0].op != OP_LOAD || I[0].src != SRC_LEAF || I[1].op != OP_MUL || I[1].src != SRC_LEAF || I[2].op != OP_LOOP) return;
+    if (R > 1 && (I[3].op != OP_STORE || (int)I[3].operand != c)) return;
+    const GLoop &G = P.loops[I[2].operand];
+    if (G.kind != LOOP_MAC || G.leaf_kind[0] != LL_LINEAR || G.leaf_kind[1] != LL_LINEAR) return;
+    // the first term sits outside the loop as LOAD x; MUL y -- either order of the factors
+    const LeafInfo *F0 = &leaves[I[0].operand], *F1 = &leaves[I[1].operand];
+    const LeafInfo &TA = leaves[G.leaf[0]], &TB = leaves[G.leaf[1]];
+    if (!linear_compatible(*F0, TA)) std::swap(F0, F1);
+    if (!linear_compatible(*F0, TA) || !linear_compatible(*F1, TB)) return;
+    const long long *ta = P.lpool.data() + G.table[0], *tb = P.lpool.data() + G.table[1];
+    const long long k = (long long)G.count + 1;
+    const long long sa_c = ta[0] - F0->base, sb_c = tb[0] - F1->base;
+    for (long long t = 1; t < G.count; ++t)
+      if (ta[t] - ta[t - 1] != sa_c || tb[t] - tb[t - 1] != sb_c) return;
+    if (c == 0) {
+      K = k;
+      a0 = F0->base;
+      sa = sa_c;
+      b0 = F1->base;
+      sb = sb_c;
+      la = G.leaf[0];
+      lb = G.leaf[1];
+    } else {
+      if (k != K || sa_c != sa || sb_c != sb || F0->base != a0) return;
+      if (!linear_compatible(TA, leaves[la]) || !linear_compatible(TB, leaves[lb])) return;
+      if (c == 1) nb = F1->base - b0;
+      if (F1->base != b0 + nb * c) return;
+    }
+  }
+  const LeafInfo &A = leaves[la], &B = leaves[lb];
+  // launch dims: a prefix walks A (rows of the output), the rest walks B (columns); with several roots the root index is
+  // the column and every launch dim is a row dim
+  const int r = P.out_rank;
+  int split = r;
+  if (R == 1) {
+    split = 0;
+    while (split < r && (B.ls[split] == 0 || P.out_shape[split] == 1)) ++split;
+    for (int d = split; d < r; ++d)
+      if (A.ls[d] != 0 && P.out_shape[d] != 1) return;
+  } else {
+    for (int d = 0; d < r; ++d)
+      if (B.ls[d] != 0 && P.out_shape[d] != 1) return;
+  }
+  auto collapse = [&](const LeafInfo &L, int d0, int d1, long long *extent, long long *stride) -> bool {
+    long long ext = 1, st = 0;
+    bool have = false;
+    for (int d = d1 - 1; d >= d0; --d) {
+      if (P.out_shape[d] == 1) continue;
+      if (!have) {
+        st = L.ls[d];
+        have = true;
+      } else if (L.ls[d] != st * ext) {
+        return false;
+      }
+      ext *= P.out_shape[d];
+    }
+    *extent = ext;
+    *stride = have ? st : 0;
+    return true;
+  };
+  long long M, N, rs_a, cs_b;
+  if (!collapse(A, 0, split, &M, &rs_a)) return;
+  if (R == 1) {
+    if (!collapse(B, split, r, &N, &cs_b)) return;
+  } else {
+    N = R;
+    cs_b = nb;
+  }
+  if (M <= 0 || N <= 0 || a0 != 0 || b0 != 0) return;
+  const ParamInfo &PA = P.params[A.param], &PB = P.params[B.param];
+  if (PA.length() != M * K || PB.length() != K * N) return;
+  bool ta, tb;
+  if ((sa == 1 || K == 1) && (rs_a == K || M == 1)) ta = false;
+  else if ((rs_a == 1 || M == 1) && (sa == M || K == 1)) ta = true;
+  else return;
+  if ((cs_b == 1 || N == 1) && (sb == N || K == 1)) tb = false;
+  else if ((sb == 1 || K == 1) && (cs_b == K || N == 1)) tb = true;
+  else return;
+  P.contraction.valid = true;
+  P.contraction.param_a = A.param;
+  P.contraction.param_b = B.param;
+  P.contraction.m = M;
+  P.contraction.n = N;
+  P.contraction.k = K;
+  P.contraction.transpose_a = ta;
+  P.contraction.transpose_b = tb;
+}
+
 int Lowering::choose_kernel() {
   Plan &P = *plan;
   const int r = P.out_rank;
   bool vec_ok = P.n_roots == 1 && P.n_elems > 0 && (int)leaves.size() <= kInlineVLeaves &&
-                (int)P.code.size() <= kInlineCode && P.n_slots <= 6;
+                (int)P.code.size() <= kInlineCode && P.n_slots <= 6 && P.loops.empty();
   for (const LeafInfo &L : leaves)
     if (L.mode != G_SCALAR && L.mode != G_STRIDED) vec_ok = false;
   if (vec_ok) {
@@ -647,6 +880,14 @@ int lower_tree(const uint8_t *blob, size_t len, Plan *plan, std::string *err) {
   if (rc) return rc;
   rc = L.emit_all();
   if (rc) return rc;
+  rc = L.choose_kernel();
+  if (rc || plan->kind == PLAN_VEC) return rc;   // small contiguous programs stay on the 128-bit vector kernel
+  rc = L.compress_loops();
+  if (rc) return rc;
+  if (plan->loops.empty()) return 0;
+  plan->gleaves.clear();
+  plan->dpool.clear();
+  L.detect_contraction();
   return L.choose_kernel();
 }
 
@@ -664,12 +905,32 @@ std::string Plan::describe() const {
     o << "]";
   } else {
     o << " leaves=[";
-    for (const GLeaf &g : gleaves) o << mode_name[g.mode] << ":p" << g.param << ",";
+    if (gleaves.size() <= 16) {
+      for (const GLeaf &g : gleaves) o << mode_name[g.mode] << ":p" << g.param << ",";
+    } else {
+      int cnt[4] = {0, 0, 0, 0};
+      for (const GLeaf &g : gleaves) cnt[g.mode]++;
+      for (int m = 0; m < 4; ++m)
+        if (cnt[m]) o << cnt[m] << "x" << mode_name[m] << ",";
+    }
     o << "]";
   }
   int mac = 0;
   for (const Instr &i : code) mac += i.op == OP_MAC || i.op == OP_MSUB;
   o << " mac=" << mac;
+  if (!loops.empty()) {
+    o << " loops=[";
+    if (loops.size() > 8) o << loops.size() << " x ";
+    for (size_t li = 0; li < loops.size() && li < 8; ++li) {
+      const GLoop &g = loops[li];
+      o << (g.kind == LOOP_MAC ? "mac" : "add") << "x" << g.count << ":" << (g.leaf_kind[0] == LL_LINEAR ? "lin" : "mono")
+        << (g.kind == LOOP_MAC ? (g.leaf_kind[1] == LL_LINEAR ? "*lin" : "*mono") : "") << ",";
+    }
+    o << "]";
+  }
+  if (contraction.valid)
+    o << " contraction=" << contraction.m << "x" << contraction.n << "x" << contraction.k << (contraction.transpose_a ? "T" : "N")
+      << (contraction.transpose_b ? "T" : "N");
   return o.str();
 }
 

@@ -78,9 +78,19 @@ struct Plan {
   // PLAN_GATHER
   std::vector<GLeaf> gleaves;
   std::vector<double> dpool;
+  std::vector<GLoop> loops;       // OP_LOOP descriptors
+  std::vector<long long> lpool;   // their per-iteration offset tables
+  // set when the whole launch is ONE dense contraction out[M,N] = A[M,K] * B[K,N] (+ nothing else): the runtime routes
+  // it to the tcgen05 GEMM when the context's gemm_mode is a tensor-core mode (TensorsSpec:337-344 / :371-383 patterns)
+  struct Contraction {
+    bool valid = false;
+    int param_a = 0, param_b = 0;
+    long long m = 0, n = 0, k = 0;
+    bool transpose_a = false, transpose_b = false;
+  } contraction;
   // device-resident copy of code + leaves (uploaded by the runtime on first launch; owned by the plan cache)
   void *d_tables = nullptr;
-  size_t d_code_off = 0, d_leaf_off = 0, d_pool_off = 0, d_tables_bytes = 0;
+  size_t d_code_off = 0, d_leaf_off = 0, d_pool_off = 0, d_loop_off = 0, d_lpool_off = 0, d_tables_bytes = 0;
 
   std::string describe() const;
 };

@@ -38,6 +38,7 @@ enum Op : uint8_t {
   OP_MAC,    // acc = acc + (leaf[aux] * src)   two roundings
   OP_MSUB,   // acc = acc - (leaf[aux] * src)
   OP_STORE,  // out[L * n_roots + operand] = acc   (Concatenate roots, KB:632-652)
+  OP_LOOP,   // acc = (((acc + t_0) + t_1) + ...) over loops[operand]: a host-unrolled sum folded back into a device loop
   OP_COUNT_
 };
 
@@ -88,6 +89,29 @@ struct GLeaf {
   GRow row[kMaxRank];
   int32_t mat_off;    // G_GENERIC: index of rows*(rank+1) doubles in the constant pool
   int32_t pad_;
+};
+
+// ---- device loop over a host-unrolled chain (N2) ----------------------------------------------------------------------
+// TensorLayers.sumAs (TL:124-162) and every user-level matmul / convolution (TensorsSpec:144-210, :337-393) arrive as
+// `((t_0 + t_1) + t_2) + ...` with 10^2..10^6 terms that differ only in the constant column of their leaves' matrices.
+// The lowering folds such a run back into ONE loop instruction: the term template (one or two leaves) plus a table of
+// per-iteration offsets.  Evaluation order and roundings are exactly those of the unrolled chain (fmul, then fadd, term
+// by term), so the result is bit-identical to it.
+enum LoopKind : int32_t { LOOP_ADD = 0 /* acc + a_t */, LOOP_MAC = 1 /* acc + a_t * b_t */ };
+enum LoopLeafKind : int32_t {
+  LL_LINEAR = 0,  // scalar / strided leaves: address = sum_x g_x * ls_x + table[t]
+  LL_MONO = 1     // bounds-checked mono rows (<= kLoopMonoRows rows): index_y = g_col * coef + table[t * rows + y]
+};
+constexpr int kLoopMonoRows = 4;
+constexpr int kLoopMinTerms = 8;
+
+struct GLoop {
+  int32_t kind;          // LoopKind
+  int32_t count;
+  int32_t leaf[2];       // template leaves (gleaves index); leaf[1] unused for LOOP_ADD
+  int32_t leaf_kind[2];  // LoopLeafKind
+  int32_t pad_[2];
+  long long table[2];    // offsets into the loop pool (in long long units)
 };
 
 }  // namespace dls

@@ -490,6 +490,11 @@ class InlineTensor(Tensor):
             self._weak = weakref.ref(buf)
         return buf
 
+    def _see_through_closure(self):
+        """The expression a view of this tensor may be pushed into (trees.see_through), or None when the buffer
+        already exists (reading it is cheaper than recomputing)."""
+        return self.closure() if self._live() is None else None
+
 
 class FillTensor(InlineTensor):
     """Tensors:1266-1269."""
@@ -512,6 +517,9 @@ class TransformedTensor(InlineTensor):
         if self._node is None:
             self._node = Xform(self.checkpoint, self.matrix)
         return self._node
+
+    def _see_through_closure(self):
+        return None          # a view of a view already composes against the original checkpoint (Tensors:978-1003)
 
 
 class NonInlineTensor(Tensor):

@@ -144,7 +144,8 @@ def test_deep_left_fold_does_not_recurse(T):
     acc = a
     for _ in range(20000):
         acc = acc + a
-    assert "code=20002" in _plan(T, acc)
+    d = _plan(T, acc)                         # ... and the 20000 identical terms fold back into one device loop
+    assert "code=3 " in d and "loops=[addx20000:lin,]" in d
 
 
 def test_malformed_blobs_are_rejected(native):
