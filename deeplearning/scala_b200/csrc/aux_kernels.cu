@@ -105,6 +105,36 @@ __global__ void __launch_bounds__(kBlock) sum_axis_chunks_kernel(const float *__
   }
 }
 
+// few, short columns and a long k (inner <= 256): a block owns a slab of consecutive rows and reads it as ONE contiguous
+// run (thread t -> element t of the slab, so column = t % inner), keeps one partial per (row-lane, column), folds the
+// row-lanes through shared memory and writes partial[outer][block][column].  Launched twice: slabs -> gridDim.x partials,
+// then one block per outer index over those partials.
+__global__ void __launch_bounds__(kBlock) sum_axis_slab_kernel(const float *__restrict__ in, float *__restrict__ out, size_t k,
+                                                               size_t inner, size_t rows_per_block) {
+  __shared__ float part[kBlock];
+  const size_t o = blockIdx.y;
+  const int lanes = kBlock / (int)inner;                 // row-lanes per block (>= 1)
+  const int col = threadIdx.x % (int)inner, rl = threadIdx.x / (int)inner;
+  const size_t r0 = (size_t)blockIdx.x * rows_per_block, r1 = min(k, r0 + rows_per_block);
+  float a0 = 0.f, a1 = 0.f;
+  if (rl < lanes) {
+    const float *p = in + (o * k + r0) * inner + col;
+    size_t r = r0 + rl;
+    for (; r + lanes < r1; r += 2 * (size_t)lanes) {
+      a0 += __ldg(p + (r - r0) * inner);
+      a1 += __ldg(p + (r - r0 + lanes) * inner);
+    }
+    if (r < r1) a0 += __ldg(p + (r - r0) * inner);
+  }
+  part[threadIdx.x] = a0 + a1;
+  __syncthreads();
+  if (rl == 0) {
+    float s = part[col];
+    for (int l = 1; l < lanes; ++l) s += part[l * (int)inner + col];
+    out[(o * gridDim.x + blockIdx.x) * inner + col] = s;
+  }
+}
+
 int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, size_t k, size_t inner, float *out) {
   cudaStream_t st = ctx->streams[stream];
   if (outer * inner == 0) return DLS_OK;
@@ -117,6 +147,18 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
   if (inner == 1 && k >= 64) {
     size_t want = (outer + kBlock / 32 - 1) / (kBlock / 32);
     sum_axis_rows_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, out, outer, k);
+  } else if (inner <= kBlock && k >= 512 && outer * inner * 8 <= lanes_wanted && outer < 65536) {
+    size_t blocks = std::min<size_t>((size_t)ctx->sm_count * 4 / std::max<size_t>(1, std::min<size_t>(outer, 4)), (k + 63) / 64);
+    blocks = std::max<size_t>(1, blocks);
+    const size_t rows_per_block = (k + blocks - 1) / blocks;
+    blocks = (k + rows_per_block - 1) / rows_per_block;
+    Block scratch;
+    int rc = alloc_block(ctx, outer * blocks * inner * sizeof(float), stream, &scratch);
+    if (rc) return rc;
+    sum_axis_slab_kernel<<<dim3((unsigned)blocks, (unsigned)outer), kBlock, 0, st>>>(in, (float *)scratch.ptr, k, inner, rows_per_block);
+    sum_axis_slab_kernel<<<dim3(1, (unsigned)outer), kBlock, 0, st>>>((const float *)scratch.ptr, out, blocks, inner, blocks);
+    free_block(ctx, scratch);
+    ctx->stats.kernel_launches++;
   } else if (outer * inner * 8 <= lanes_wanted && k >= 256) {
     // two stages: enough chunks to fill the machine, at least 32 rows each
     size_t chunks = std::min(lanes_wanted / (outer * inner), (k + 31) / 32);

@@ -405,11 +405,167 @@ __global__ void __launch_bounds__(kBlock) ew_gather_kernel(const __grid_constant
 }
 
 
+// ---- N2 fast path: 32-bit affine gathers, V inner elements per lane -------------------------------------------------------
+struct G4Args {
+  float *out;
+  uint32_t n_tiles;                    // lanes of work: rows * ceil(inner / V)
+  int32_t rank;                        // launch rank (dims renumbered innermost-first)
+  int32_t n_roots, n_slots, reduce;
+  int32_t stage_roots;                 // n_roots > 1: collect a warp's outputs in shared memory, store them coalesced
+  FastDiv tpr;                         // tiles per row
+  FastDiv dims[kMaxRank];              // extents of dims 1 .. rank-1 (index 0 unused)
+  ReduceArgs red;
+  const float *params[kG4Params];
+  G4Leaf leaves[kG4Leaves];
+  Instr code[kG4Code];
+};
+
+template <int V>
+__device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int *g, float *v) {
+  const G4Leaf &L = A.leaves[li];
+  const float *p = A.params[L.param];
+  int addr = L.base;
+#pragma unroll
+  for (int d = 0; d < kMaxRank; ++d)
+    if (d < A.rank) addr += g[d] * L.ls[d];
+  const int step = L.ls[0];
+  unsigned valid = (1u << V) - 1u;
+  const int nc = L.n_checks;
+#pragma unroll
+  for (int c = 0; c < kG4Checks; ++c) {
+    if (c < nc) {
+      const G4Check C = L.chk[c];
+      if (C.col != 0) {
+        const int idx = g[C.col] * C.coef + C.off;
+        if ((unsigned)idx >= (unsigned)C.extent) valid = 0u;
+      } else {
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+          const int idx = (g[0] + e) * C.coef + C.off;
+          if ((unsigned)idx >= (unsigned)C.extent) valid &= ~(1u << e);
+        }
+      }
+    }
+  }
+  if (V == 4 && step == 1 && valid == 15u && (addr & 3) == 0) {
+    const float4 q = __ldg(reinterpret_cast<const float4 *>(p + addr));
+    v[0] = q.x;
+    v[1] = q.y;
+    v[2] = q.z;
+    v[3] = q.w;
+    return;
+  }
+#pragma unroll
+  for (int e = 0; e < V; ++e) v[e] = (valid >> e) & 1u ? __ldg(p + addr + e * step) : L.padding;
+}
+
+template <int V>
+__global__ void __launch_bounds__(kBlock, 3) ew_gather4_kernel(const __grid_constant__ G4Args A) {
+  extern __shared__ float g4_slots[];   // [slot][V][thread], then the root staging area [thread][V][root]
+  float *stage = g4_slots + (size_t)A.n_slots * V * kBlock;
+  float tsum = 0.f;
+  const uint32_t stride = gridDim.x * kBlock;
+  // with staged roots whole warps iterate together (the tail lanes of the last warp idle inside)
+  const uint32_t t_end = A.stage_roots ? ((A.n_tiles + 31u) & ~31u) : A.n_tiles;
+  for (uint32_t t = blockIdx.x * kBlock + threadIdx.x; t < t_end; t += stride) {
+    const bool live = t < A.n_tiles;
+    int g[kMaxRank];
+    uint32_t row = fast_div(t, A.tpr);
+    g[0] = (int)(t - row * A.tpr.d) * V;
+#pragma unroll
+    for (int d = 1; d < kMaxRank; ++d) {
+      if (d < A.rank) {
+        const uint32_t q = fast_div(row, A.dims[d]);
+        g[d] = (int)(row - q * A.dims[d].d);
+        row = q;
+      } else {
+        g[d] = 0;
+      }
+    }
+    float acc[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) acc[e] = 0.f;
+    for (int pc = 0; live; ++pc) {
+      const Instr in = A.code[pc];
+      const int op = in.op;
+      if (op == OP_END) break;
+      float s[V];
+      if (in.src == SRC_LEAF) {
+        g4_leaf<V>(A, in.operand, g, s);
+      } else if (in.src == SRC_LIT) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) s[e] = __uint_as_float(in.operand);
+      } else if (in.src == SRC_SLOT) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) s[e] = g4_slots[(in.operand * V + e) * kBlock + threadIdx.x];
+      }
+      if (op <= OP_RMOD) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[e] = apply_binary(op, acc[e], s[e]);
+      } else if (op <= OP_LOG) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[e] = apply_unary(op, acc[e]);
+      } else if (op == OP_SAVE) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) g4_slots[(in.operand * V + e) * kBlock + threadIdx.x] = acc[e];
+      } else if (op == OP_STORE) {
+        if (A.reduce) {
+#pragma unroll
+          for (int e = 0; e < V; ++e) tsum += acc[e];
+        } else if (A.stage_roots) {
+#pragma unroll
+          for (int e = 0; e < V; ++e) stage[(threadIdx.x * V + e) * A.n_roots + in.operand] = acc[e];
+        } else {
+#pragma unroll
+          for (int e = 0; e < V; ++e) A.out[(size_t)(t * V + e) * A.n_roots + in.operand] = acc[e];
+        }
+      } else {  // OP_MAC / OP_MSUB
+        float f[V];
+        g4_leaf<V>(A, in.aux, g, f);
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+          const float pr = __fmul_rn(f[e], s[e]);
+          acc[e] = op == OP_MAC ? __fadd_rn(acc[e], pr) : __fsub_rn(acc[e], pr);
+        }
+      }
+    }
+    if (A.n_roots == 1) {
+      if (!live) continue;
+      if (A.reduce) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) tsum += acc[e];
+      } else if (V == 4) {
+        reinterpret_cast<float4 *>(A.out)[t] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      } else {
+        A.out[t] = acc[0];
+      }
+    } else if (A.stage_roots) {
+      // the warp's 32 * V coordinates x n_roots outputs are one contiguous run of the output buffer
+      __syncwarp();
+      const uint32_t lane = threadIdx.x & 31u, t0 = t - lane;
+      const uint32_t lanes_live = min(32u, A.n_tiles - t0);
+      const uint32_t count = lanes_live * V * (uint32_t)A.n_roots;
+      const float *src = stage + (size_t)(threadIdx.x - lane) * V * A.n_roots;
+      float *dst = A.out + (size_t)t0 * V * A.n_roots;
+      if (V == 4) {
+        for (uint32_t i = lane * 4u; i < count; i += 128u)
+          *reinterpret_cast<float4 *>(dst + i) = *reinterpret_cast<const float4 *>(src + i);
+      } else {
+        for (uint32_t i = lane; i < count; i += 32u) dst[i] = src[i];
+      }
+      __syncwarp();
+    }
+  }
+  if (A.reduce) grid_sum_finish(tsum, A.red);
+}
+
 // ---- host side -------------------------------------------------------------------------------------------------------
 int query_ew_occupancy(dls_ctx *ctx) {
   int b = 0;
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
@@ -506,6 +662,51 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
     if (P.v_outer == 0) ew_vec_kernel<0><<<grid, kBlock, smem, st>>>(A);
     else if (P.v_outer == 1) ew_vec_kernel<1><<<grid, kBlock, smem, st>>>(A);
     else ew_vec_kernel<3><<<grid, kBlock, smem, st>>>(A);
+  } else if (P.g4_ok) {
+    static thread_local G4Args A;
+    auto mk_div = [](long long d) {
+      FastDiv f;
+      f.d = (uint32_t)d;
+      f.mul = 0;
+      f.shr = 0;
+      if (d > 1) {
+        int lg = 0;
+        while ((1ll << lg) < d) ++lg;
+        const int p = 31 + lg;
+        f.mul = (uint32_t)((((unsigned long long)1 << p) + (unsigned long long)d - 1) / (unsigned long long)d);
+        f.shr = (uint32_t)(p - 32);
+      }
+      return f;
+    };
+    const int V = P.g4_vec, r = P.out_rank;
+    const long long W = r ? P.out_shape[r - 1] : 1;
+    const long long tpr = (W + V - 1) / V;          // V == 4 only when W % 4 == 0
+    A.out = out->ptr;
+    A.n_tiles = (uint32_t)(P.n_elems / (W ? W : 1) * tpr);
+    A.rank = r;
+    A.n_roots = P.n_roots;
+    A.n_slots = P.n_slots;
+    A.reduce = reduce_sum ? 1 : 0;
+    A.tpr = mk_div(tpr);
+    for (int d = 0; d < kMaxRank; ++d) A.dims[d] = mk_div(d >= 1 && d < r ? P.out_shape[r - 1 - d] : 1);
+    A.red = red;
+    for (int i = 0; i < P.n_params; ++i) A.params[i] = params[i]->ptr;
+    memcpy(A.leaves, P.g4leaves.data(), P.g4leaves.size() * sizeof(G4Leaf));
+    memcpy(A.code, P.code.data(), P.code.size() * sizeof(Instr));
+    size_t smem = (size_t)P.n_slots * V * kBlock * sizeof(float);
+    const size_t stage_bytes = (size_t)kBlock * V * P.n_roots * sizeof(float);
+    A.stage_roots = P.n_roots > 1 && !reduce_sum && smem + stage_bytes <= 48 * 1024 ? 1 : 0;
+    if (A.stage_roots) smem += stage_bytes;
+    int per_sm = 0;
+    if (V == 4) DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4_kernel<4>, kBlock, smem));
+    else DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4_kernel<1>, kBlock, smem));
+    if (per_sm < 1) per_sm = 1;
+    long long want = ((long long)A.n_tiles + kBlock - 1) / kBlock;
+    long long cap = (long long)ctx->sm_count * per_sm;
+    if (reduce_sum && cap > kReduceMaxBlocks) cap = kReduceMaxBlocks;
+    const int grid = (int)std::max<long long>(1, std::min<long long>(want, cap));
+    if (V == 4) ew_gather4_kernel<4><<<grid, kBlock, smem, st>>>(A);
+    else ew_gather4_kernel<1><<<grid, kBlock, smem, st>>>(A);
   } else {
     DLS_CHECK(P.n_params <= kInlineParams, DLS_ERR_UNSUPPORTED, "more than 128 distinct parameters in one gather tree");
     int rc = upload_tables(P);

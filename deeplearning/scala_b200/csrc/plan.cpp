@@ -120,6 +120,7 @@ struct Lowering {
   int emit_all();
   int compress_loops();
   void detect_contraction();
+  void build_g4();
 
   // ---- code emission state ----
   std::vector<int> slot_of;        // node -> permanent slot (shared sub-expressions), -1 if none
@@ -870,6 +871,62 @@ int Lowering::choose_kernel() {
   return 0;
 }
 
+// The 32-bit affine form of a gather plan for the fast N2 kernel: launch dims renumbered innermost-first.
+void Lowering::build_g4() {
+  Plan &P = *plan;
+  P.g4_ok = false;
+  if (P.kind != PLAN_GATHER || !P.loops.empty() || leaves.empty() || (int)leaves.size() > kG4Leaves ||
+      (int)P.code.size() > kG4Code || P.n_params > kG4Params || P.n_elems <= 0 ||
+      P.n_elems * (long long)P.n_roots >= (1ll << 31) - (1ll << 24))
+    return;
+  for (const ParamInfo &pi : P.params)
+    if (pi.length() >= (1ll << 31)) return;
+  const int r = P.out_rank;
+  auto renum = [&](int d) { return r - 1 - d; };
+  const long long lim = (1ll << 31) - 1;
+  std::vector<G4Leaf> out;
+  for (const LeafInfo &L : leaves) {
+    G4Leaf G;
+    memset(&G, 0, sizeof(G));
+    G.param = L.param;
+    G.padding = L.padding;
+    long long base = 0, ls[kMaxRank] = {0};
+    if (L.mode == G_GENERIC) return;
+    if (L.mode == G_SCALAR || L.mode == G_STRIDED) {
+      base = L.base;
+      for (int d = 0; d < r; ++d) ls[renum(d)] = L.ls[d];
+    } else {  // G_MONO
+      for (int y = 0; y < L.rows; ++y) {
+        const GRow &R = L.row[y];
+        base += R.off * R.stride;
+        if (R.col >= 0) ls[renum(R.col)] += R.coef * R.stride;
+        if (R.checked) {
+          if (G.n_checks == kG4Checks) return;
+          const long long span = R.col >= 0 ? std::max<long long>(P.out_shape[R.col] - 1, 0) : 0;
+          const long long coef = R.col >= 0 ? R.coef : 0;
+          if (llabs(coef) * span + llabs(R.off) >= lim || R.extent >= lim) return;
+          G4Check &C = G.chk[G.n_checks++];
+          C.col = R.col >= 0 ? renum(R.col) : 0;
+          C.coef = (int32_t)coef;
+          C.off = (int32_t)R.off;
+          C.extent = (int32_t)R.extent;
+        }
+      }
+    }
+    // every address a VALID element can produce is inside the parameter (< 2^31); guard the intermediate sums too
+    long long reach = llabs(base);
+    for (int d = 0; d < r; ++d) reach += llabs(ls[renum(d)]) * std::max<long long>(P.out_shape[d] - 1, 0);
+    if (reach >= lim) return;
+    G.base = (int32_t)base;
+    for (int d = 0; d < kMaxRank; ++d) G.ls[d] = (int32_t)ls[d];
+    out.push_back(G);
+  }
+  P.g4leaves.swap(out);
+  const long long W = r ? P.out_shape[r - 1] : 1;
+  P.g4_vec = (r && W % 4 == 0) ? 4 : 1;
+  P.g4_ok = true;
+}
+
 }  // namespace
 
 int lower_tree(const uint8_t *blob, size_t len, Plan *plan, std::string *err) {
@@ -884,7 +941,10 @@ int lower_tree(const uint8_t *blob, size_t len, Plan *plan, std::string *err) {
   if (rc || plan->kind == PLAN_VEC) return rc;   // small contiguous programs stay on the 128-bit vector kernel
   rc = L.compress_loops();
   if (rc) return rc;
-  if (plan->loops.empty()) return 0;
+  if (plan->loops.empty()) {
+    L.build_g4();
+    return 0;
+  }
   plan->gleaves.clear();
   plan->dpool.clear();
   L.detect_contraction();
@@ -894,7 +954,7 @@ int lower_tree(const uint8_t *blob, size_t len, Plan *plan, std::string *err) {
 std::string Plan::describe() const {
   static const char *mode_name[] = {"scalar", "strided", "mono", "generic"};
   std::ostringstream o;
-  o << "kind=" << (kind == PLAN_VEC ? "vec" : "gather") << " elems=" << n_elems << " roots=" << n_roots
+  o << "kind=" << (kind == PLAN_VEC ? "vec" : g4_ok ? (g4_vec == 4 ? "gather4" : "gather1") : "gather") << " elems=" << n_elems << " roots=" << n_roots
     << " code=" << code.size() << " slots=" << n_slots;
   if (kind == PLAN_VEC) {
     o << " outer=" << v_outer << " dims=[";

@@ -78,6 +78,10 @@ struct Plan {
   // PLAN_GATHER
   std::vector<GLeaf> gleaves;
   std::vector<double> dpool;
+  // PLAN_GATHER fast path (gather4.cu): filled when every leaf fits the 32-bit affine + checks form
+  bool g4_ok = false;
+  int g4_vec = 1;                 // inner elements per lane (4 when the innermost extent is a multiple of 4)
+  std::vector<G4Leaf> g4leaves;
   std::vector<GLoop> loops;       // OP_LOOP descriptors
   std::vector<long long> lpool;   // their per-iteration offset tables
   // set when the whole launch is ONE dense contraction out[M,N] = A[M,K] * B[K,N] (+ nothing else): the runtime routes

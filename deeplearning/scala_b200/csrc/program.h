@@ -91,6 +91,24 @@ struct GLeaf {
   int32_t pad_;
 };
 
+// ---- N2 fast path (gather4.cu): every leaf is an affine address plus a few bounds checks, all in 32-bit ---------------
+// Launch dims are renumbered innermost-first (dim 0 = the fastest-varying output dim); a lane owns V consecutive inner
+// elements, so coordinates, outer-row checks and the leaf base address are computed once per V elements and contiguous
+// leaves are read with one 128-bit load.
+constexpr int kG4Leaves = 16;
+constexpr int kG4Code = 128;
+constexpr int kG4Checks = 4;
+constexpr int kG4Params = 16;
+struct G4Check {
+  int32_t col, coef, off, extent;   // 0 <= g[col] * coef + off < extent, else the leaf reads its padding
+};
+struct G4Leaf {
+  int32_t param, base, n_checks;
+  float padding;
+  int32_t ls[kMaxRank];             // element stride per (renumbered) launch dim
+  G4Check chk[kG4Checks];
+};
+
 // ---- device loop over a host-unrolled chain (N2) ----------------------------------------------------------------------
 // TensorLayers.sumAs (TL:124-162) and every user-level matmul / convolution (TensorsSpec:144-210, :337-393) arrive as
 // `((t_0 + t_1) + t_2) + ...` with 10^2..10^6 terms that differ only in the constant column of their leaves' matrices.
