@@ -9,7 +9,8 @@
 
 namespace dls {
 
-constexpr int kVecUnroll = 2;          // float4 tiles per thread per trip: 2 x 16 B x n_leaves in flight per lane
+// float4 tiles per thread per trip (template parameter U of ew_vec_kernel): U x 16 B x n_leaves in flight per lane, and
+// the interpreter's fetch / decode / dispatch cost per program instruction is shared by 4 * U elements
 constexpr int kInlineParams = 128;
 
 struct VLeafDev {
@@ -18,6 +19,9 @@ struct VLeafDev {
   uint32_t flags;                      // bit 0: contiguous along the inner dim (128-bit loads), else broadcast along it
                                        // bit 1: read-once stream (evict-first loads)
 };
+
+// leaf reference kinds of the vector kernel, patched into Instr.src / Instr.aux by launch_plan (a plan stores SRC_LEAF)
+enum VSrc : uint32_t { VSRC_DENSE = 4, VSRC_CONTIG = 5, VSRC_BCAST = 6 };
 
 struct FastDiv {                       // n / d for n < 2^31: umulhi(n, mul) >> shr   (d == 1: mul == 0)
   uint32_t d, mul, shr;
@@ -90,7 +94,7 @@ __device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f) {
 }
 
 #define DLS_EACH(EXPR)                                                                       \
-  _Pragma("unroll") for (int u = 0; u < kVecUnroll; ++u) {                                   \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) {                                   \
     float4 r_;                                                                               \
     { const float a = acc[u].x, b = s[u].x; (void)a; (void)b; r_.x = (EXPR); }               \
     { const float a = acc[u].y, b = s[u].y; (void)a; (void)b; r_.y = (EXPR); }               \
@@ -100,7 +104,7 @@ __device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f) {
   }
 
 #define DLS_EACH1(EXPR)                                                                      \
-  _Pragma("unroll") for (int u = 0; u < kVecUnroll; ++u) {                                   \
+  _Pragma("unroll") for (int u = 0; u < U; ++u) {                                   \
     float4 r_;                                                                               \
     { const float a = acc[u].x; r_.x = (EXPR); }                                             \
     { const float a = acc[u].y; r_.y = (EXPR); }                                             \
@@ -110,18 +114,18 @@ __device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f) {
   }
 
 // OUTER = number of collapsed outer dims the launch has: 0 (flat), 1 (rows x inner) or 3 (up to three outer dims).
-// Every lane owns kVecUnroll float4 tiles per trip, one grid stride apart (coalesced 128-bit accesses); tiles past the
+// Every lane owns U float4 tiles per trip, one grid stride apart (coalesced 128-bit accesses); tiles past the
 // end are clamped to the last tile (recomputed, never stored) so that no load needs a predicate.
-template <int OUTER>
-__global__ void __launch_bounds__(kBlock) ew_vec_kernel(const __grid_constant__ VecArgs A) {
+template <int OUTER, int U>
+__global__ void __launch_bounds__(kBlock, U == 4 ? 3 : 1) ew_vec_kernel(const __grid_constant__ VecArgs A) {
   extern __shared__ float4 slot_mem[];  // [slot][unroll][thread]
   const uint32_t total = A.total_tiles;
   const uint32_t nthreads = gridDim.x * kBlock;
   float tsum = 0.f;
-  for (uint32_t t0 = blockIdx.x * kBlock + threadIdx.x; t0 < total; t0 += nthreads * kVecUnroll) {
-    uint32_t tile[kVecUnroll], c4[kVecUnroll], r0[kVecUnroll], r1[kVecUnroll], r2[kVecUnroll];
+  for (uint32_t t0 = blockIdx.x * kBlock + threadIdx.x; t0 < total; t0 += nthreads * U) {
+    uint32_t tile[U], c4[U], r0[U], r1[U], r2[U];
 #pragma unroll
-    for (int u = 0; u < kVecUnroll; ++u) {
+    for (int u = 0; u < U; ++u) {
       const uint32_t t = min(t0 + (uint32_t)u * nthreads, total - 1);
       tile[u] = t;
       r0[u] = r1[u] = r2[u] = 0;
@@ -141,21 +145,45 @@ __global__ void __launch_bounds__(kBlock) ew_vec_kernel(const __grid_constant__ 
         }
       }
     }
-    float4 acc[kVecUnroll];
+    float4 acc[U];
 
-    // element offsets are 32-bit (the host only picks this kernel when every leaf spans < 2^32 floats): one IMAD for
-    // the offset, one IMAD.WIDE for the address, one LDG.128
-    auto fetch_leaf = [&](uint32_t li, float4 *dst) {
-      const VLeafDev &L = A.leaves[li];
-      const bool contiguous = (L.flags & 1u) != 0;
+    // element offsets are 32-bit (the host only picks this kernel when every leaf spans < 2^32 floats).  The launch
+    // code classifies every leaf reference (VSRC_*), so each addressing mode is its own grid-uniform branch:
+    //   dense  -- same layout as the output: offset = tile * 4, one IMAD.WIDE + LDG.128 per tile
+    //   contig -- contiguous along the inner dim, own outer strides
+    //   bcast  -- constant along the inner dim: one scalar load per tile, splat
+    auto fetch_dense = [&](uint32_t li, float4 *dst) {
+      const float4 *p = reinterpret_cast<const float4 *>(A.leaves[li].ptr);
 #pragma unroll
-      for (int u = 0; u < kVecUnroll; ++u) {
-        uint32_t off = contiguous ? c4[u] * 4u : 0u;
+      for (int u = 0; u < U; ++u) dst[u] = __ldg(p + tile[u]);
+    };
+    auto fetch_contig = [&](uint32_t li, float4 *dst) {
+      const VLeafDev &L = A.leaves[li];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        uint32_t off = c4[u] * 4u;
         if (OUTER >= 1) off += r0[u] * L.ls[0];
         if (OUTER == 3) off += r1[u] * L.ls[1] + r2[u] * L.ls[2];
-        const float *p = L.ptr + off;
-        if (contiguous) dst[u] = __ldg(reinterpret_cast<const float4 *>(p));
-        else dst[u] = splat(__ldg(p));
+        dst[u] = __ldg(reinterpret_cast<const float4 *>(L.ptr + off));
+      }
+    };
+    auto fetch_bcast = [&](uint32_t li, float4 *dst) {
+      const VLeafDev &L = A.leaves[li];
+      __syncwarp();  // control flow is grid-uniform, so this is free; it keeps ptxas from if-converting this arm into
+                     // the dense one (both arms' loads would then issue, predicated, on every fetch)
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        uint32_t off = 0u;
+        if (OUTER >= 1) off += r0[u] * L.ls[0];
+        if (OUTER == 3) off += r1[u] * L.ls[1] + r2[u] * L.ls[2];
+        dst[u] = splat(__ldg(L.ptr + off));
+      }
+    };
+    auto fetch_leaf = [&](uint32_t kind, uint32_t li, float4 *dst) {
+      switch (kind) {
+        case VSRC_DENSE: fetch_dense(li, dst); break;
+        case VSRC_CONTIG: fetch_contig(li, dst); break;
+        default: fetch_bcast(li, dst); break;
       }
     };
 
@@ -182,31 +210,31 @@ __global__ void __launch_bounds__(kBlock) ew_vec_kernel(const __grid_constant__ 
       }
       if (op == OP_SAVE) {
 #pragma unroll
-        for (int u = 0; u < kVecUnroll; ++u) slot_mem[(in.operand * kVecUnroll + u) * kBlock + threadIdx.x] = acc[u];
+        for (int u = 0; u < U; ++u) slot_mem[(in.operand * U + u) * kBlock + threadIdx.x] = acc[u];
         continue;
       }
-      float4 s[kVecUnroll];
-      if (in.src == SRC_LEAF) {
-        fetch_leaf(in.operand, s);
+      float4 s[U];
+      if (in.src >= VSRC_DENSE) {
+        fetch_leaf(in.src, in.operand, s);
       } else if (in.src == SRC_LIT) {
 #pragma unroll
-        for (int u = 0; u < kVecUnroll; ++u) s[u] = splat(__uint_as_float(in.operand));
+        for (int u = 0; u < U; ++u) s[u] = splat(__uint_as_float(in.operand));
       } else {
 #pragma unroll
-        for (int u = 0; u < kVecUnroll; ++u) s[u] = slot_mem[(in.operand * kVecUnroll + u) * kBlock + threadIdx.x];
+        for (int u = 0; u < U; ++u) s[u] = slot_mem[(in.operand * U + u) * kBlock + threadIdx.x];
       }
-      if (op >= OP_MAC) {  // OP_MAC / OP_MSUB: acc +- leaf[aux] * src, two roundings
-        float4 f[kVecUnroll];
-        fetch_leaf(in.aux, f);
+      if (op >= OP_MAC) {  // OP_MAC / OP_MSUB: acc +- leaf[aux] * src, two roundings; aux = kind << 12 | leaf
+        float4 f[U];
+        fetch_leaf(in.aux >> 12, in.aux & 0xfffu, f);
 #pragma unroll
-        for (int u = 0; u < kVecUnroll; ++u)
+        for (int u = 0; u < U; ++u)
           s[u] = make_float4(__fmul_rn(f[u].x, s[u].x), __fmul_rn(f[u].y, s[u].y), __fmul_rn(f[u].z, s[u].z),
                              __fmul_rn(f[u].w, s[u].w));
         if (op == OP_MAC) { DLS_EACH(__fadd_rn(a, b)) } else { DLS_EACH(__fsub_rn(a, b)) }
         continue;
       }
       switch (op) {  // grid-uniform: one branch per instruction, then straight-line lanes
-        case OP_LOAD: DLS_EACH(b) break;
+        case OP_LOAD: DLS_EACH(__fadd_rn(b, -0.0f)) break;  // x + (-0) == x bit for bit; keeps src out of acc's registers
         case OP_ADD: DLS_EACH(__fadd_rn(a, b)) break;
         case OP_SUB: DLS_EACH(__fsub_rn(a, b)) break;
         case OP_MUL: DLS_EACH(__fmul_rn(a, b)) break;
@@ -220,16 +248,20 @@ __global__ void __launch_bounds__(kBlock) ew_vec_kernel(const __grid_constant__ 
       }
     }
 
+    if (A.reduce && t0 + (uint32_t)(U - 1) * nthreads < total - 1) {
+      // every tile of the trip is live and full: pairwise sum per tile
 #pragma unroll
-    for (int u = 0; u < kVecUnroll; ++u) {
+      for (int u = 0; u < U; ++u) tsum += (acc[u].x + acc[u].y) + (acc[u].z + acc[u].w);
+      continue;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
       const bool live = t0 + (uint32_t)u * nthreads < total;   // clamped duplicates contribute nothing
       if (A.reduce) {
         const uint32_t left = tile[u] == total - 1 ? A.tail_valid : 4u;
-        float part = acc[u].x;
-        if (left > 1) part += acc[u].y;
-        if (left > 2) part += acc[u].z;
-        if (left > 3) part += acc[u].w;
-        if (live) tsum += part;
+        const float hi = (left > 2 ? acc[u].z : 0.f) + (left > 3 ? acc[u].w : 0.f);
+        const float lo = acc[u].x + (left > 1 ? acc[u].y : 0.f);
+        if (live) tsum += lo + hi;
       } else if (live) {
         reinterpret_cast<float4 *>(A.out)[tile[u]] = acc[u];
       }
@@ -566,10 +598,13 @@ int query_ew_occupancy(dls_ctx *ctx) {
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-  DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<1>, kBlock, 0));
+#define DLS_VEC_ATTR(O, UU) \
+  DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<O, UU>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  DLS_VEC_ATTR(0, 1) DLS_VEC_ATTR(0, 2) DLS_VEC_ATTR(0, 4)
+  DLS_VEC_ATTR(1, 1) DLS_VEC_ATTR(1, 2) DLS_VEC_ATTR(1, 4)
+  DLS_VEC_ATTR(3, 1) DLS_VEC_ATTR(3, 2) DLS_VEC_ATTR(3, 4)
+#undef DLS_VEC_ATTR
+  DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<1, 2>, kBlock, 0));
   ctx->vec_blocks_per_sm = b > 0 ? b : 1;
   DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_gather_kernel<true>, kBlock, 0));
   ctx->gather_blocks_per_sm = b > 0 ? b : 1;
@@ -647,21 +682,51 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
       A.leaves[l].flags = (V.inner ? 1u : 0u) | (V.streaming ? 2u : 0u);
     }
     memcpy(A.code, P.code.data(), P.code.size() * sizeof(Instr));
-    size_t smem = (size_t)P.n_slots * kVecUnroll * kBlock * sizeof(float4);
-    int per_sm = ctx->vec_blocks_per_sm;
-    if (smem) {
-      int b = 0;
-      DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, ew_vec_kernel<1>, kBlock, smem));
-      per_sm = b > 0 ? b : 1;
+    // leaf references carry their addressing mode, so that the kernel branches once per instruction, grid-uniformly
+    auto leaf_kind = [&](uint32_t li) -> uint32_t {
+      const VLeaf &V = P.vleaves[li];
+      return V.dense ? VSRC_DENSE : V.inner ? VSRC_CONTIG : VSRC_BCAST;
+    };
+    for (size_t i = 0; i < P.code.size(); ++i) {
+      Instr &in = A.code[i];
+      if (in.op == OP_MAC || in.op == OP_MSUB) in.aux = (uint16_t)(leaf_kind(in.aux) << 12 | in.aux);
+      if (in.src == SRC_LEAF) in.src = (uint8_t)leaf_kind(in.operand);
     }
-    long long want = (total_tiles + (long long)kBlock * kVecUnroll - 1) / ((long long)kBlock * kVecUnroll);
+    // Unroll: 4 tiles per lane once the launch fills the machine several times over (the interpreter's per-instruction
+    // cost is then shared by 16 elements), fewer for small launches (more CTAs) and slot-heavy programs (shared memory).
+    static const int forced_unroll = [] {
+      const char *e = getenv("DLS_VEC_UNROLL");
+      return e ? atoi(e) : 0;
+    }();
+    int U = 1;
+    const long long lanes = (long long)ctx->sm_count * kBlock;
+    if (total_tiles >= lanes * 4) U = 2;
+    if (total_tiles >= lanes * 32 && P.n_slots <= 3) U = 4;
+    if (forced_unroll == 1 || forced_unroll == 2 || (forced_unroll == 4 && P.n_slots <= 6)) U = forced_unroll;
+    size_t smem = (size_t)P.n_slots * U * kBlock * sizeof(float4);
+    int per_sm = 0;
+#define DLS_VEC_OCC(UU)                                                                                              \
+  DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_vec_kernel<1, UU>, kBlock, smem))
+    if (U == 4) DLS_VEC_OCC(4);
+    else if (U == 2) DLS_VEC_OCC(2);
+    else DLS_VEC_OCC(1);
+#undef DLS_VEC_OCC
+    if (per_sm < 1) per_sm = 1;
+    long long want = (total_tiles + (long long)kBlock * U - 1) / ((long long)kBlock * U);
     long long cap = (long long)ctx->sm_count * per_sm;
     if (reduce_sum && cap > kReduceMaxBlocks) cap = kReduceMaxBlocks;
     int grid = (int)std::min<long long>(want, cap);
     // a 3-outer launch with leading extents of 1 was collapsed on the host: v_outer is 0, 1, 2 or 3
-    if (P.v_outer == 0) ew_vec_kernel<0><<<grid, kBlock, smem, st>>>(A);
-    else if (P.v_outer == 1) ew_vec_kernel<1><<<grid, kBlock, smem, st>>>(A);
-    else ew_vec_kernel<3><<<grid, kBlock, smem, st>>>(A);
+#define DLS_VEC_GO(O)                                                          \
+  do {                                                                         \
+    if (U == 4) ew_vec_kernel<O, 4><<<grid, kBlock, smem, st>>>(A);            \
+    else if (U == 2) ew_vec_kernel<O, 2><<<grid, kBlock, smem, st>>>(A);       \
+    else ew_vec_kernel<O, 1><<<grid, kBlock, smem, st>>>(A);                   \
+  } while (0)
+    if (P.v_outer == 0) DLS_VEC_GO(0);
+    else if (P.v_outer == 1) DLS_VEC_GO(1);
+    else DLS_VEC_GO(3);
+#undef DLS_VEC_GO
   } else if (P.g4_ok) {
     static thread_local G4Args A;
     auto mk_div = [](long long d) {

@@ -844,6 +844,15 @@ int Lowering::choose_kernel() {
       P.v_outer = k > 0 ? k - 1 : 0;
       for (int j = 0; j < kMaxVecOuter; ++j) P.v_dims[j] = j < P.v_outer ? ext[j] : 1;
       P.v_inner = W;
+      for (VLeaf &V : P.vleaves) {  // dense: laid out exactly like the output, so a tile's offset is tile * 4
+        bool dense = V.inner == 1;
+        long long expect = W;
+        for (int j = P.v_outer - 1; j >= 0 && dense; --j) {
+          dense = V.ls[j] == expect;
+          expect *= P.v_dims[j];
+        }
+        V.dense = dense ? 1 : 0;
+      }
       return 0;
     }
     P.vleaves.clear();

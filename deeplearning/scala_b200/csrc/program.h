@@ -59,7 +59,7 @@ struct VLeaf {
   int32_t inner;                  // 1: contiguous along the inner dim (128-bit loads); 0: broadcast along it
   int32_t param;                  // index into the parameter pointer table
   int32_t streaming;              // 1: footprint == output size, read once (evict-first loads)
-  int32_t pad_;
+  int32_t dense;                  // 1: same row-major layout as the (collapsed) output: element offset = 4 * tile index
 };
 
 // ---- gather kernel (N2) leaf ---------------------------------------------------------------------------------------
