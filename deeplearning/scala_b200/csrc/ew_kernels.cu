@@ -467,7 +467,13 @@ __device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int 
   for (int c = 0; c < kG4Checks; ++c) {
     if (c < nc) {
       const G4Check C = L.chk[c];
-      if (C.col != 0) {
+      if (C.shift) {  // dyadic row: (int)(g * coef / 2^shift + off / 2^shift), truncation toward zero (KB:386)
+        // along the innermost dim (col 0) the host launches V == 1, so g[0] is the element's own coordinate
+        const int n = g[C.col] * C.coef + C.off;
+        const int idx = n >= 0 ? n >> C.shift : -((-n) >> C.shift);
+        if ((unsigned)idx >= (unsigned)C.extent) valid = 0u;
+        addr += idx * C.stride;
+      } else if (C.col != 0) {
         const int idx = g[C.col] * C.coef + C.off;
         if ((unsigned)idx >= (unsigned)C.extent) valid = 0u;
       } else {

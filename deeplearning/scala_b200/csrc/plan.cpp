@@ -894,14 +894,61 @@ void Lowering::build_g4() {
   auto renum = [&](int d) { return r - 1 - d; };
   const long long lim = (1ll << 31) - 1;
   std::vector<G4Leaf> out;
+  bool inner_scaled = false;           // a dyadic row along the innermost launch dim: one element per lane
   for (const LeafInfo &L : leaves) {
     G4Leaf G;
     memset(&G, 0, sizeof(G));
     G.param = L.param;
     G.padding = L.padding;
+    long long scaled_reach = 0;
     long long base = 0, ls[kMaxRank] = {0};
-    if (L.mode == G_GENERIC) return;
-    if (L.mode == G_SCALAR || L.mode == G_STRIDED) {
+    if (L.mode == G_GENERIC) {
+      // rows are integer single-term (as in G_MONO) or single-term with coefficient and offset multiples of 1/8:
+      // the double expression of KB:363-390 is then exact, and so is the integer form used by the kernel
+      const int cols = r + 1;
+      for (int y = 0; y < L.rows; ++y) {
+        const double *row = L.mat.data() + (size_t)y * cols;
+        int nz = 0, col = -1;
+        for (int x = 0; x < r; ++x)
+          if (row[x] != 0.0) {
+            ++nz;
+            col = x;
+          }
+        if (nz > 1) return;
+        const double c8 = nz ? row[col] * 8.0 : 0.0, o8 = row[r] * 8.0;
+        if (c8 != std::floor(c8) || o8 != std::floor(o8) || std::fabs(c8) >= 1e6 || std::fabs(o8) >= 1e9) return;
+        const GRow &R = L.row[y];
+        const long long span = nz ? std::max<long long>(P.out_shape[col] - 1, 0) : 0;
+        const bool integral = std::fmod(c8, 8.0) == 0.0 && std::fmod(o8, 8.0) == 0.0;
+        if (integral) {
+          const long long coef = (long long)(c8 / 8.0), off = (long long)(o8 / 8.0);
+          base += off * R.stride;
+          if (nz) ls[renum(col)] += coef * R.stride;
+          if (R.checked) {
+            if (G.n_checks == kG4Checks) return;
+            if (llabs(coef) * span + llabs(off) >= lim || R.extent >= lim) return;
+            G4Check &C = G.chk[G.n_checks++];
+            C.col = nz ? renum(col) : 0;
+            C.coef = (int32_t)coef;
+            C.off = (int32_t)off;
+            C.extent = (int32_t)R.extent;
+          }
+        } else {
+          if (G.n_checks == kG4Checks) return;
+          if (std::fabs(c8) * (double)span + std::fabs(o8) >= (double)lim || R.extent >= lim || R.stride >= lim) return;
+          G4Check &C = G.chk[G.n_checks++];
+          C.col = nz ? renum(col) : 0;
+          C.coef = (int32_t)c8;
+          C.off = (int32_t)o8;
+          C.extent = (int32_t)R.extent;      // always bounds checked (classify_leaf marks non-integer rows checked)
+          C.shift = 3;
+          C.stride = (int32_t)R.stride;
+          if (nz && renum(col) == 0) inner_scaled = true;
+          // farthest address this row can add, for the reach guard below
+          scaled_reach += (R.extent - 1) * R.stride;
+        }
+      }
+    } else if (L.mode == G_SCALAR || L.mode == G_STRIDED) {
       base = L.base;
       for (int d = 0; d < r; ++d) ls[renum(d)] = L.ls[d];
     } else {  // G_MONO
@@ -923,7 +970,7 @@ void Lowering::build_g4() {
       }
     }
     // every address a VALID element can produce is inside the parameter (< 2^31); guard the intermediate sums too
-    long long reach = llabs(base);
+    long long reach = llabs(base) + scaled_reach;
     for (int d = 0; d < r; ++d) reach += llabs(ls[renum(d)]) * std::max<long long>(P.out_shape[d] - 1, 0);
     if (reach >= lim) return;
     G.base = (int32_t)base;
@@ -932,7 +979,7 @@ void Lowering::build_g4() {
   }
   P.g4leaves.swap(out);
   const long long W = r ? P.out_shape[r - 1] : 1;
-  P.g4_vec = (r && W % 4 == 0) ? 4 : 1;
+  P.g4_vec = (r && W % 4 == 0 && !inner_scaled) ? 4 : 1;
   P.g4_ok = true;
 }
 

@@ -101,6 +101,10 @@ constexpr int kG4Checks = 4;
 constexpr int kG4Params = 16;
 struct G4Check {
   int32_t col, coef, off, extent;   // 0 <= g[col] * coef + off < extent, else the leaf reads its padding
+  // shift > 0: a row with a dyadic-rational coefficient (`scale` up by 2, 4, 8: KB:363-390 evaluates
+  // `(int)(g * 0.5 + off)` in double, exact for multiples of 1/8): index = trunc_toward_zero((g * coef + off) / 2^shift)
+  // with coef and off pre-multiplied by 2^shift; the row's address term index * stride is added here, not through ls[]
+  int32_t shift, stride;
 };
 struct G4Leaf {
   int32_t param, base, n_checks;

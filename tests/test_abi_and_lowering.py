@@ -127,6 +127,15 @@ def test_views_lower_to_the_gather_kernel_with_the_cheapest_leaf_mode(T):
     assert "kind=gather" in _plan(T, s + T.scalar(1.0))                        # stride-16 walk
 
 
+def test_dyadic_scale_rows_take_the_32_bit_gather_path(T):
+    x = T.random([8, 12, 16], 1)
+    assert "kind=gather4 " in _plan(T, x.scale([16, 24, 16]))                  # 0.5 on two outer dims, 128-bit inner loads
+    assert "kind=gather1 " in _plan(T, x.scale([8, 12, 32]))                   # 0.5 along the inner dim: one element per lane
+    assert "kind=gather4 " in _plan(T, x.scale([64, 12, 16]))                  # 0.125
+    assert "kind=gather " in _plan(T, x.scale([24, 12, 16]))                   # 1/3 -> "0.333": stays on double arithmetic
+    assert "kind=gather4 " in _plan(T, x.translate([1, 0, 0]).scale([16, 12, 16]))   # (g * 0.5 - 1), negative numerators
+
+
 def test_shared_subtrees_get_slots_and_macs_are_fused(T):
     a, b, c = (T.random([64, 64], s) for s in (1, 2, 3))
     t2 = a + b

@@ -191,6 +191,31 @@ def test_scale_truncating_resample_bit_exact(backends, new_shape):
     assert_bits(want, got)
 
 
+@pytest.mark.parametrize("case", ["up2_outer", "up2_inner", "up8", "up4_after_translate", "up2_negative_offsets", "translate_after_scale", "mixed"])
+def test_dyadic_scale_rows_bit_exact(backends, case):
+    """Coefficients that are multiples of 1/8 run on the 32-bit gather path in integer arithmetic; the result must be
+    the `(int)(double)` truncation of KB:386, including the (-1, 0) -> 0 quirk for negative numerators."""
+    x = rnd(29, 4, 6, 8)
+
+    def build(M):
+        t = M.tensor(x, padding=-7.0)
+        if case == "up2_outer":
+            return t.scale([8, 12, 8])
+        if case == "up2_inner":
+            return t.scale([4, 6, 16])
+        if case == "up8":
+            return t.scale([32, 6, 8])
+        if case == "up4_after_translate":
+            return t.translate([1, -2, 0]).scale([16, 6, 8])
+        if case == "up2_negative_offsets":
+            return t.translate([3, 1, 2], [6, 8, 12]).scale([12, 16, 12])
+        if case == "translate_after_scale":                  # index = (int)(g * 0.5 - 0.5): g = 0 reads element 0, not padding
+            return t.scale([8, 12, 8]).translate([1, 3, 0])
+        return (t.scale([8, 12, 8]) * M.tensor(rnd(30, 8, 12, 8))).scale([16, 12, 8])
+    want, got, _ = both(backends, build)
+    assert_bits(want, got)
+
+
 def test_split_join_permute_compositions(backends):
     x = rnd(24, 4, 6, 8)
 
