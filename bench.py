@@ -200,6 +200,7 @@ def main():
                     help="c2 (default) = BASELINE configs[1]; c1/c3/c4/c5 = the training configs (samples/s)")
     ap.add_argument("--gemm-mode", default="bf16", choices=["fp32", "tf32", "bf16"], help="contraction precision of the training legs")
     ap.add_argument("--no-train", action="store_true", help="skip the short training legs appended to the C2 line")
+    ap.add_argument("--eager", action="store_true", help="training legs: time only the eager path (no captured step)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -397,7 +398,7 @@ def train_once(workload, args, rank, world, local, dist, steps, warmup, e2e_step
         if dist is not None:
             dist.barrier()
         be.synchronize()
-    r = bench_train.run(workload, be, steps, warmup, e2e_steps, exchange, rank, world, barrier)
+    r = bench_train.run(workload, be, steps, warmup, e2e_steps, exchange, rank, world, barrier, compiled=not args.eager)
     times = [r["ms_total"], r["e2e_ms_per_step"]]
     if dist is not None:
         import torch
@@ -422,7 +423,7 @@ def train_legs(args, rank, world, local, dist):
         try:
             r = train_once(workload, args, rank, world, local, dist, steps, 3, 3)
             legs[workload] = {k: r[k] for k in ("workload", "samples_per_s", "e2e_samples_per_s", "ms_per_step", "tflops",
-                                                "launches_per_step", "gemm_mode", "last_loss")}
+                                                "launches_per_step", "gemm_mode", "last_loss", "mode", "eager")}
         except Exception as exc:                      # a training leg must never take the headline line down
             legs[workload] = {"error": "%s: %s" % (type(exc).__name__, exc)}
     return legs
@@ -522,6 +523,7 @@ def main_train(args, rank, world, local):
                         "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
                         "note": "whole-step FLOP / whole-step time (includes elementwise, staging and host launch gaps)"},
            "launches_per_step": r["launches_per_step"], "driver_allocs_in_timed_region": r["driver_allocs_in_timed_region"],
+           "mode": r["mode"], "eager": r["eager"], "captured": r.get("captured"),
            "loss": {"first": r["first_loss"], "last": r["last_loss"]}}
     if rank == 0:
         print(json.dumps(out))

@@ -55,7 +55,10 @@ def build(workload, be, exchange=None, rank=0, world=1, gemm_mode=None):
     return model, x, t, batch, flop, desc
 
 
-def run(workload, be, steps, warmup, e2e_steps=5, exchange=None, rank=0, world=1, barrier=None):
+def run(workload, be, steps, warmup, e2e_steps=5, exchange=None, rank=0, world=1, barrier=None, compiled=True):
+    """Times the step twice: eagerly (one host dispatch per launch, `model.step`) and, with `compiled`, as a captured step
+    (`model.compile`: the same user code recorded once into a CUDA graph, one driver call per step).  The headline
+    numbers (`ms_total`, `e2e_ms_per_step`) are the captured step's when it is available, else the eager ones."""
     import deeplearning.scala_b200.tensors as B
     from deeplearning.scala_b200 import _native as N
     model, x, t, batch, flop, desc = build(workload, be, exchange, rank, world)
@@ -72,7 +75,7 @@ def run(workload, be, steps, warmup, e2e_steps=5, exchange=None, rank=0, world=1
         losses.append(model.step(xd, td))
     e1 = be.record_event()
     barrier()
-    ms = B.elapsed_ms(e0, e1)
+    eager_ms = B.elapsed_ms(e0, e1)
     st1 = be.stats()
     # e2e: the step a user makes -- host batch (pinned) -> Tensor.apply -> train -> loss on the host
     px, hx = pinned_like(N, x)
@@ -83,14 +86,51 @@ def run(workload, be, steps, warmup, e2e_steps=5, exchange=None, rank=0, world=1
     for _ in range(e2e_steps):
         losses.append(model.step(be.tensor(hx), be.tensor(ht) if t is not None else None))
     be.synchronize()
-    e2e_s = time.perf_counter() - t0
+    eager_e2e_s = time.perf_counter() - t0
+    out = {"workload": desc, "batch_per_gpu": batch, "flop_per_step_per_gpu": flop,
+           "eager": {"ms_per_step": eager_ms / steps, "e2e_ms_per_step": eager_e2e_s * 1e3 / e2e_steps,
+                     "launches_per_step": (st1["kernel_launches"] - st0["kernel_launches"]) / steps},
+           "driver_allocs_in_timed_region": st1["driver_allocs"] - st0["driver_allocs"],
+           "h2d_bytes_per_step": int(x.nbytes + (t.nbytes if t is not None else 0)), "d2h_bytes_per_step": 4,
+           "steps": steps, "e2e_steps": e2e_steps, "mode": "eager"}
+    ms, e2e_s, launches = eager_ms, eager_e2e_s, out["eager"]["launches_per_step"]
+    if compiled:
+        step = model.compile(xd, td)                           # one eager step, then the recording
+        for _ in range(warmup):
+            step.launch()
+        losses.append(step.loss())
+        barrier()
+        st0 = be.stats()
+        e0 = be.record_event()
+        for _ in range(steps):
+            step.launch()
+        e1 = be.record_event()
+        barrier()
+        ms = B.elapsed_ms(e0, e1)
+        st1 = be.stats()
+        losses.append(step.loss())
+        # e2e: pinned host batch written into the step's input buffers, one replay, the scalar loss read back
+        step(hx, ht)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            losses.append(step(hx, ht))
+        be.synchronize()
+        e2e_s = time.perf_counter() - t0
+        info = step.graph.info()
+        launches = (st1["kernel_launches"] - st0["kernel_launches"]) / steps
+        out["captured"] = {"ms_per_step": ms / steps, "e2e_ms_per_step": e2e_s * 1e3 / e2e_steps, "launches_per_step": launches,
+                           "graph_nodes": info["nodes"], "arena_bytes": info["arena_bytes"]}
+        out["driver_allocs_in_timed_region"] += st1["driver_allocs"] - st0["driver_allocs"]
+        if ms <= eager_ms:
+            out["mode"] = "captured step (CUDA graph replay of the recorded loss.train)"
+        else:                                                  # device-bound steps gain nothing from the recording and pay
+            ms, e2e_s, launches = eager_ms, eager_e2e_s, out["eager"]["launches_per_step"]    # the weight copy-back
+        del step
     N.lib.dls_host_free(px)
     if pt is not None:
         N.lib.dls_host_free(pt)
     n_params = int(sum(np.prod(w.data.shape) for w in model.weights))
-    return {"workload": desc, "batch_per_gpu": batch, "ms_per_step": ms / steps, "ms_total": ms,
-            "e2e_ms_per_step": e2e_s * 1e3 / e2e_steps, "flop_per_step_per_gpu": flop, "parameters": n_params,
-            "launches_per_step": (st1["kernel_launches"] - st0["kernel_launches"]) / steps,
-            "driver_allocs_in_timed_region": st1["driver_allocs"] - st0["driver_allocs"],
-            "h2d_bytes_per_step": int(x.nbytes + (t.nbytes if t is not None else 0)), "d2h_bytes_per_step": 4,
-            "first_loss": losses[0], "last_loss": losses[-1], "steps": steps, "e2e_steps": e2e_steps}
+    out.update({"ms_per_step": ms / steps, "ms_total": ms, "e2e_ms_per_step": e2e_s * 1e3 / e2e_steps, "parameters": n_params,
+                "launches_per_step": launches, "first_loss": losses[0], "last_loss": losses[-1]})
+    return out

@@ -93,6 +93,14 @@ _SIG = {
     "dls_comm_init": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_int]),
     "dls_allreduce_sum": (C.c_int, [_P, _P, C.c_size_t, _PP, C.c_int, _PP]),
     "dls_comm_destroy": (C.c_int, [_P]),
+    "dls_graph_begin": (C.c_int, [_P]),
+    "dls_graph_end": (C.c_int, [_P, _PP]),
+    "dls_graph_abort": (C.c_int, [_P]),
+    "dls_graph_launch": (C.c_int, [_P]),
+    "dls_graph_info": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "dls_graph_retain": (None, [_P]),
+    "dls_graph_release": (None, [_P]),
+    "dls_buf_copy": (C.c_int, [_P, _P, _P, C.c_size_t]),
 }
 EXPORTS = tuple(_SIG)
 for _name, (_res, _args) in _SIG.items():

@@ -40,7 +40,15 @@ struct Block {
   void *ptr = nullptr;
   size_t bytes = 0;
   uint32_t stream_mask = 0;                 // pool streams that touched the block before it was freed
+  int pool = 0;                             // 0: the context's allocator; > 0: private arena of a captured step (graph.cu)
   cudaEvent_t free_events[kMaxStreams] = {};  // only for streams in stream_mask when more than one stream exists
+};
+
+// Private arena of one captured step: every block allocated between dls_graph_begin and dls_graph_end comes from here
+// and returns here when freed, so the addresses baked into the graph's kernel nodes are never handed to eager work.
+struct GraphPool {
+  std::multimap<size_t, Block> free_blocks;
+  uint64_t bytes = 0;
 };
 
 struct CachedPlan {
@@ -71,6 +79,15 @@ struct dls_buf {
   long long shadow_rows[2] = {0, 0}, shadow_cols[2] = {0, 0};
 };
 
+struct dls_graph {
+  std::atomic<int> rc{1};
+  dls_ctx *ctx = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int pool = 0;
+  uint64_t kernel_nodes = 0, nodes = 0;
+};
+
 struct dls_ctx {
   int device = 0;
   int sm_count = 148;
@@ -94,6 +111,11 @@ struct dls_ctx {
   // occupancy-derived grid sizes, filled at create time
   int vec_blocks_per_sm = 4;
   int gather_blocks_per_sm = 4;
+
+  // captured steps (graph.cu)
+  int capture_pool = 0;                       // arena id while a capture is open, else 0
+  int next_pool = 1;
+  std::map<int, dls::GraphPool> pools;
 
   void *nccl_comm = nullptr;
   int comm_rank = 0, comm_world = 1;

@@ -130,7 +130,9 @@ int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long ro
   const long long p = mode == DLS_GEMM_BF16 ? ((cols + 7) & ~7LL) : transposed ? ((rows + 3) & ~3LL) : ((cols + 3) & ~3LL);
   // slot 1 holds either the transposed or the re-pitched fp32 copy; the sign of shadow_rows tells which
   const long long tag_rows = transposed ? -rows : rows;
-  if (!(sh.ptr && tag_r == tag_rows && tag_c == cols)) {
+  // a staged copy made outside the capture that is open now (or inside one that has ended) holds data the graph being
+  // recorded will not reproduce on replay: only copies staged in the current arena count as fresh
+  if (!(sh.ptr && tag_r == tag_rows && tag_c == cols && sh.pool == ctx->capture_pool)) {
     if (sh.ptr) free_block(ctx, sh);
     int rc;
     if (mode == DLS_GEMM_BF16) {

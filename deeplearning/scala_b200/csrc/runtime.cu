@@ -37,6 +37,27 @@ static size_t size_class(size_t bytes) {
 
 int alloc_block(dls_ctx *ctx, size_t bytes, int stream, Block *out) {
   const size_t want = size_class(bytes + 16);  // 16 B slack: ragged 128-bit tail accesses stay inside the block
+  if (ctx->capture_pool) {  // inside dls_graph_begin .. dls_graph_end: private arena, single stream, no events
+    GraphPool &gp = ctx->pools[ctx->capture_pool];
+    auto it = gp.free_blocks.lower_bound(want);
+    if (it != gp.free_blocks.end() && it->first <= want + want / 8) {
+      *out = it->second;
+      gp.free_blocks.erase(it);
+      ctx->stats.bytes_in_use += out->bytes;
+      return DLS_OK;
+    }
+    Block b;
+    b.bytes = want;
+    b.pool = ctx->capture_pool;
+    b.stream_mask = 1u << stream;
+    cudaError_t e = cudaMalloc(&b.ptr, want);   // legal while capturing in relaxed mode; not a graph node
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc (captured step arena)", __FILE__, __LINE__);
+    ctx->stats.driver_allocs++;
+    ctx->stats.bytes_in_use += want;
+    gp.bytes += want;
+    *out = b;
+    return DLS_OK;
+  }
   auto it = ctx->free_blocks.lower_bound(want);
   if (it != ctx->free_blocks.end() && it->first <= want + want / 8) {
     Block b = it->second;
@@ -72,6 +93,13 @@ int alloc_block(dls_ctx *ctx, size_t bytes, int stream, Block *out) {
 void free_block(dls_ctx *ctx, Block &blk) {
   if (!blk.ptr) return;
   ctx->stats.bytes_in_use -= blk.bytes;
+  if (blk.pool) {  // arena block: parked for the graph that owns the arena; returned to the driver once that graph is gone
+    auto it = ctx->pools.find(blk.pool);
+    if (it != ctx->pools.end()) it->second.free_blocks.emplace(blk.bytes, blk);
+    else cudaFree(blk.ptr);
+    blk.ptr = nullptr;
+    return;
+  }
   if (ctx->n_streams > 1) {
     for (int s = 0; s < ctx->n_streams; ++s) {
       if (!(blk.stream_mask & (1u << s))) continue;
@@ -143,6 +171,7 @@ int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_writt
     }
   }
   if (done) {
+    DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "completion events cannot be requested inside a captured step");
     dls_event *e = new dls_event();
     e->ctx = ctx;
     cudaError_t err = cudaEventCreate(&e->ev);
@@ -213,6 +242,7 @@ int dls_ctx_create(const dls_ctx_opts *opts, dls_ctx **out) {
 
 int dls_ctx_sync(dls_ctx *ctx) {
   DLS_CHECK(ctx, DLS_ERR_INVALID, "dls_ctx_sync: ctx is NULL");
+  DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_ctx_sync: a capture is open on this context");
   DLS_CUDA(cudaSetDevice(ctx->device));
   for (cudaStream_t s : ctx->streams) DLS_CUDA(cudaStreamSynchronize(s));
   return DLS_OK;
@@ -237,7 +267,11 @@ void dls_ctx_destroy(dls_ctx *ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   dls_comm_destroy(ctx);
+  dls_graph_abort(ctx);
   dls_ctx_trim(ctx);
+  for (auto &kv : ctx->pools)
+    for (auto &fb : kv.second.free_blocks) cudaFree(fb.second.ptr);
+  ctx->pools.clear();
   for (auto &kv : ctx->plans)
     if (kv.second->plan.d_tables) cudaFree(kv.second->plan.d_tables);
   ctx->plans.clear();
@@ -272,6 +306,7 @@ int dls_buf_alloc(dls_ctx *ctx, size_t n_floats, dls_buf **out) {
 int dls_buf_from_host(dls_ctx *ctx, const float *src, size_t n_floats, dls_buf **out, dls_event **done) {
   DLS_CHECK(ctx && out && (src || n_floats == 0), DLS_ERR_INVALID, "dls_buf_from_host: NULL argument");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_buf_from_host: host transfers cannot be recorded into a captured step");
   DLS_CUDA(cudaSetDevice(ctx->device));
   int stream = pick_stream(ctx);
   dls_buf *b = nullptr;
@@ -320,6 +355,7 @@ int dls_buf_read(dls_ctx *ctx, dls_buf *buf, size_t offset, float *dst, size_t n
   DLS_CHECK(ctx && buf && (dst || n_floats == 0), DLS_ERR_INVALID, "dls_buf_read: NULL argument");
   DLS_CHECK(offset + n_floats <= buf->n, DLS_ERR_INVALID, "dls_buf_read: range exceeds the buffer");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_buf_read: host transfers cannot be recorded into a captured step");
   DLS_CUDA(cudaSetDevice(ctx->device));
   int stream = buf->last_stream;
   int rc = wait_inputs(ctx, stream, nullptr, 0, deps, n_deps);
@@ -337,6 +373,7 @@ int dls_buf_write(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, s
   DLS_CHECK(ctx && buf && (src || n_floats == 0), DLS_ERR_INVALID, "dls_buf_write: NULL argument");
   DLS_CHECK(offset + n_floats <= buf->n, DLS_ERR_INVALID, "dls_buf_write: range exceeds the buffer");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_buf_write: host transfers cannot be recorded into a captured step");
   DLS_CUDA(cudaSetDevice(ctx->device));
   int stream = buf->last_stream;
   if (n_floats) {

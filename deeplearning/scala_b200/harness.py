@@ -74,8 +74,63 @@ class Trainer:
             raise self.P.handled_exceptions.pop(0)
         return out
 
+    def loss_layer(self, x: T.Tensor, target: Optional[T.Tensor] = None):
+        raise NotImplementedError
+
+    def step(self, x: T.Tensor, target: Optional[T.Tensor] = None) -> float:
+        return self.run(self.loss_layer(x, target))
+
+    def compile(self, x: T.Tensor, target: Optional[T.Tensor] = None) -> "CompiledStep":
+        """Record one whole training step on the fixed input buffers `x` / `target` (see CompiledStep)."""
+        return CompiledStep(self, x, target)
+
     def parameters(self) -> List[np.ndarray]:
         return [w.data.flat_array().reshape(w.data.shape) for w in self.weights]
+
+
+class CompiledStep:
+    """One training step (forward, backward, every weight update, the scalar loss) recorded into a CUDA graph
+    (`Backend.capture`, csrc/graph.cu) and replayed with one driver call per step.  The user-level code is unchanged:
+    the same `loss.train` runs once while recording.  The reference swaps each weight for a freshly allocated buffer
+    (TW:63-72); inside the recording the new value is copied back into the weight's home buffer at the end of the step,
+    so every replay reads the weights the previous one wrote.  `x` / `target` are device tensors whose buffers stay the
+    step's inputs: refresh them with `write_inputs` between replays."""
+
+    def __init__(self, trainer: "Trainer", x: T.Tensor, target: Optional[T.Tensor]):
+        be = trainer.backend
+        self.trainer, self.backend = trainer, be
+        self.x = x.do_cache()
+        self.target = target.do_cache() if target is not None else None
+        trainer.step(self.x, self.target)                    # eager once: every plan is built, operands are staged
+        homes = [(w, w.data._buffer(), list(w.data.shape), w.data.padding) for w in trainer.weights]
+        with be.capture() as graph:
+            loss = trainer.loss_layer(self.x, self.target).train().map(lambda data: data.sum().do_cache()).run()
+            for w, home, shape, padding in homes:
+                if w.data._buffer() is not home:
+                    be.copy(home, w.data._buffer(), w.data.size)
+                    w.data.release()
+                    w.data = T.CachedTensor(be, home, shape, padding)
+        if trainer.P.handled_exceptions:
+            raise trainer.P.handled_exceptions.pop(0)
+        self.graph, self._loss = graph, loss
+
+    def write_inputs(self, x_host: np.ndarray, target_host: Optional[np.ndarray] = None):
+        self.backend.write(self.x._buffer(), x_host)
+        if target_host is not None:
+            self.backend.write(self.target._buffer(), target_host)
+
+    def launch(self):
+        self.graph.launch()
+
+    def loss(self) -> float:
+        """Scalar loss of the most recent replay (4-byte D2H, waits for the replay)."""
+        return float(self._loss.flat_array()[0])
+
+    def __call__(self, x_host: Optional[np.ndarray] = None, target_host: Optional[np.ndarray] = None) -> float:
+        if x_host is not None:
+            self.write_inputs(x_host, target_host)
+        self.launch()
+        return self.loss()
 
 
 class Mlp(Trainer):
@@ -102,9 +157,9 @@ class Mlp(Trainer):
             h = self.L.linear(w, h, b, "row" if b is not None else "none", act)
         return h
 
-    def step(self, x: T.Tensor, target: Optional[T.Tensor] = None) -> float:
+    def loss_layer(self, x: T.Tensor, target: Optional[T.Tensor] = None):
         out = self.forward(x)
-        return self.run(self.L.squared_error(out, target) if target is not None else out)
+        return self.L.squared_error(out, target) if target is not None else out
 
 
 class Cnn(Trainer):
@@ -137,8 +192,8 @@ class Cnn(Trainer):
         h = L.linear(h, self.fc1[0], self.fc1[1], "col", "relu")
         return L.linear(h, self.fc2[0], self.fc2[1], "col", "none")
 
-    def step(self, x: T.Tensor, target: T.Tensor) -> float:
-        return self.run(self.L.squared_error(self.forward(x), target))
+    def loss_layer(self, x: T.Tensor, target: Optional[T.Tensor] = None):
+        return self.L.squared_error(self.forward(x), target)
 
 
 def one_hot(labels: np.ndarray, classes: int, feature_major: bool) -> np.ndarray:

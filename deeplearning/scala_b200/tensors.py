@@ -67,6 +67,48 @@ def elapsed_ms(start: Event, end: Event) -> float:
     return ms.value
 
 
+class CapturedStep:
+    """Owns one reference to a `dls_graph`: everything the backend launched inside `with backend.capture() as step:`
+    (csrc/graph.cu).  `step.launch()` replays it with one driver call."""
+    __slots__ = ("backend", "handle")
+
+    def __init__(self, backend):
+        self.backend, self.handle = backend, None
+
+    def launch(self):
+        if not self.handle:
+            raise RuntimeError("the capture did not complete")
+        N.check(N.lib.dls_graph_launch(self.handle))
+
+    def info(self) -> dict:
+        k, n, b = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        N.check(N.lib.dls_graph_info(self.handle, C.byref(k), C.byref(n), C.byref(b)))
+        return {"kernel_nodes": k.value, "nodes": n.value, "arena_bytes": b.value}
+
+    def __del__(self):
+        h, self.handle = self.handle, None
+        if h and N is not None and self.backend._ctx:
+            N.lib.dls_graph_release(h)
+
+
+class _Capture:
+    def __init__(self, backend):
+        self.backend, self.step = backend, CapturedStep(backend)
+
+    def __enter__(self) -> CapturedStep:
+        N.check(N.lib.dls_graph_begin(self.backend.ctx))
+        return self.step
+
+    def __exit__(self, exc_type, exc, tb):
+        if exc_type is not None:
+            N.lib.dls_graph_abort(self.backend.ctx)
+            return False
+        h = C.c_void_p()
+        N.check(N.lib.dls_graph_end(self.backend.ctx, C.byref(h)))
+        self.step.handle = h
+        return False
+
+
 class Backend:
     """One instance of the `Tensors` trait: context, stream pool, allocator, plan cache (Tensors:199, OpenCL:1139)."""
 
@@ -120,6 +162,20 @@ class Backend:
         # the source array may be freed by the caller: the copy above is enqueued from pageable memory, which the CUDA
         # runtime stages synchronously, so no extra wait is needed here
         return DeviceBuffer(self, h, flat.size)
+
+    def capture(self) -> _Capture:
+        """`with backend.capture() as step:` records every launch made inside instead of executing it (one CUDA graph);
+        `step.launch()` replays the recording.  Inputs must already be on the device; nothing may be read back inside."""
+        return _Capture(self)
+
+    def copy(self, dst: DeviceBuffer, src: DeviceBuffer, n: Optional[int] = None):
+        """Stream-ordered device-to-device copy (recordable)."""
+        N.check(N.lib.dls_buf_copy(self.ctx, dst.handle, src.handle, min(dst.length, src.length) if n is None else n))
+
+    def write(self, buf: DeviceBuffer, flat: np.ndarray, offset: int = 0):
+        """Refresh an existing device buffer from host memory (asynchronous when `flat` is pinned)."""
+        flat = np.ascontiguousarray(flat, dtype=F32).reshape(-1)
+        N.check(N.lib.dls_buf_write(self.ctx, buf.handle, offset, flat.ctypes.data_as(C.c_void_p), flat.size, None))
 
     def download(self, buf: DeviceBuffer, n: Optional[int] = None, offset: int = 0) -> np.ndarray:
         n = buf.length - offset if n is None else n

@@ -179,6 +179,24 @@ int dls_allreduce_sum(dls_ctx *ctx, dls_buf *buf, size_t n_floats, dls_event *co
                       dls_event **done);
 int dls_comm_destroy(dls_ctx *ctx);
 
+/* ---- captured steps (new functionality).  The reference dispatches every tensor materialisation separately:
+ * clSetKernelArg + clEnqueueNDRangeKernel per launch (Tensors:1203-1251, OpenCL:826) and one clCreateBuffer per output
+ * (Tensors:1217).  Between dls_graph_begin and dls_graph_end every launch of this library is RECORDED instead of
+ * executed (CUDA stream capture); dls_graph_launch replays the whole step with one driver call.  Buffers allocated
+ * while recording come from an arena owned by the graph; host transfers, completion events and dls_ctx_sync are
+ * rejected while a capture is open; single-stream contexts only.  See csrc/graph.cu for the full contract. */
+typedef struct dls_graph dls_graph;
+int dls_graph_begin(dls_ctx *ctx);
+int dls_graph_end(dls_ctx *ctx, dls_graph **out);
+int dls_graph_abort(dls_ctx *ctx);                /* drop an open capture (error paths); no-op when none is open */
+int dls_graph_launch(dls_graph *graph);           /* asynchronous, on the context's stream */
+int dls_graph_info(const dls_graph *graph, uint64_t *kernel_nodes, uint64_t *nodes, uint64_t *arena_bytes);
+void dls_graph_retain(dls_graph *graph);
+void dls_graph_release(dls_graph *graph);
+/* device-to-device copy of the first n_floats (stream ordered, recordable): a captured step uses it to write a swapped
+ * weight (TW:63-72) back into the buffer the next replay reads */
+int dls_buf_copy(dls_ctx *ctx, dls_buf *dst, dls_buf *src, size_t n_floats);
+
 #ifdef __cplusplus
 }
 #endif
