@@ -40,7 +40,7 @@ def build(workload, be, exchange=None, rank=0, world=1, gemm_mode=None):
         desc = "C4: wide MLP 4 x (4096x4096) tanh, batch 8192, loss = sum(out), 11 GEMMs of 8192x4096x4096 per step"
     elif workload in ("c3", "c5"):
         batch = 256
-        model = H.Cnn(image=32, channels=(3, 32, 64, 128), hidden=256, classes=10, backend=be, learning_rate=1e-3, exchange=exchange)
+        model = H.Cnn(image=32, channels=(3, 32, 64, 128), hidden=256, classes=10, backend=be, learning_rate=1e-3 / world, exchange=exchange)
         x = rng.rand(batch, 32, 32, 3).astype(np.float32)
         t = H.one_hot(rng.randint(0, 10, size=batch), 10, feature_major=False)
         conv = [(32 * 32, 3, 32), (16 * 16, 32, 64), (8 * 8, 64, 128)]

@@ -17,6 +17,7 @@ typedef int (*fn_comm_init_rank)(nccl_comm_t *, int, nccl_unique_id, int);
 typedef int (*fn_all_reduce)(const void *, void *, size_t, int, int, nccl_comm_t, cudaStream_t);
 typedef int (*fn_comm_destroy)(nccl_comm_t);
 typedef const char *(*fn_get_error_string)(int);
+typedef int (*fn_group)(void);
 
 struct NcclApi {
   void *handle = nullptr;
@@ -25,6 +26,7 @@ struct NcclApi {
   fn_all_reduce all_reduce = nullptr;
   fn_comm_destroy comm_destroy = nullptr;
   fn_get_error_string get_error_string = nullptr;
+  fn_group group_start = nullptr, group_end = nullptr;
 };
 
 NcclApi g_nccl;
@@ -50,6 +52,8 @@ int load_nccl() {
   g_nccl.all_reduce = (fn_all_reduce)dlsym(h, "ncclAllReduce");
   g_nccl.comm_destroy = (fn_comm_destroy)dlsym(h, "ncclCommDestroy");
   g_nccl.get_error_string = (fn_get_error_string)dlsym(h, "ncclGetErrorString");
+  g_nccl.group_start = (fn_group)dlsym(h, "ncclGroupStart");
+  g_nccl.group_end = (fn_group)dlsym(h, "ncclGroupEnd");
   if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.all_reduce || !g_nccl.comm_destroy) {
     dls::set_error("libnccl is missing a required symbol");
     dlclose(h);
@@ -105,7 +109,9 @@ int dls_allreduce_sum(dls_ctx *ctx, dls_buf *buf, size_t n_floats, dls_event *co
   DLS_CHECK(ctx->nccl_comm, DLS_ERR_COMM, "dls_allreduce_sum: dls_comm_init has not been called on this context");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   DLS_CUDA(cudaSetDevice(ctx->device));
-  const int stream = buf->last_stream;  // in order behind the kernels that produced the gradients
+  if (ctx->n_streams == 1 && !done && n_deps == 0) return dls_allreduce_sum_many(ctx, &buf, &n_floats, 1);
+  // multi-stream contexts order everything with per-buffer events already: run in line on the producing stream
+  const int stream = buf->last_stream;
   int rc = dls::wait_inputs(ctx, stream, &buf, 1, deps, n_deps);
   if (rc) return rc;
   int e = g_nccl.all_reduce(buf->ptr, buf->ptr, n_floats, /*ncclFloat32*/ 7, /*ncclSum*/ 0, ctx->nccl_comm, ctx->streams[stream]);
@@ -113,8 +119,63 @@ int dls_allreduce_sum(dls_ctx *ctx, dls_buf *buf, size_t n_floats, dls_event *co
   return dls::finish_output(ctx, stream, &buf, 1, nullptr, 0, done);
 }
 
+// One bucket of gradients: every buffer is SUM-all-reduced in place by ONE grouped NCCL launch on the exchange stream.
+// The exchange stream is forked from the compute stream with an event recorded here; the compute stream carries on
+// with the rest of the backward pass and only waits (join_exchange, via wait_inputs) when a launch touches one of the
+// buffers again -- normally the weight update at the end of the step.  Every rank issues its buckets in program order
+// on one stream, so the order matches across ranks.  All of it is recordable: inside a captured step the fork and the
+// joins become graph edges.
+int dls_allreduce_sum_many(dls_ctx *ctx, dls_buf *const *bufs, const size_t *n_floats, int n_bufs) {
+  DLS_CHECK(ctx && (n_bufs == 0 || (bufs && n_floats)) && n_bufs >= 0, DLS_ERR_INVALID, "dls_allreduce_sum_many: bad argument");
+  DLS_CHECK(ctx->nccl_comm, DLS_ERR_COMM, "dls_allreduce_sum_many: dls_comm_init has not been called on this context");
+  DLS_CHECK(ctx->n_streams == 1, DLS_ERR_UNSUPPORTED, "dls_allreduce_sum_many: single-stream contexts only");
+  for (int i = 0; i < n_bufs; ++i)
+    DLS_CHECK(bufs[i] && n_floats[i] <= bufs[i]->n, DLS_ERR_INVALID, "dls_allreduce_sum_many: NULL buffer or length exceeds it");
+  if (n_bufs == 0) return DLS_OK;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CUDA(cudaSetDevice(ctx->device));
+  int rc = dls::wait_inputs(ctx, 0, bufs, n_bufs, nullptr, 0);   // joins an exchange still pending on any of them
+  if (rc) return rc;
+  if (!ctx->comm_stream) DLS_CUDA(cudaStreamCreateWithFlags(&ctx->comm_stream, cudaStreamNonBlocking));
+  cudaEvent_t fork = nullptr;
+  DLS_CUDA(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
+  cudaError_t ce = cudaEventRecord(fork, ctx->streams[0]);
+  if (ce == cudaSuccess) ce = cudaStreamWaitEvent(ctx->comm_stream, fork, 0);
+  cudaEventDestroy(fork);
+  if (ce != cudaSuccess) return dls::cuda_fail(ce, "fork onto the exchange stream", __FILE__, __LINE__);
+  const bool group = n_bufs > 1 && g_nccl.group_start && g_nccl.group_end;
+  int e = group ? g_nccl.group_start() : 0;
+  if (e) return nccl_fail(e, "ncclGroupStart");
+  for (int i = 0; i < n_bufs && !e; ++i)
+    e = g_nccl.all_reduce(bufs[i]->ptr, bufs[i]->ptr, n_floats[i], /*ncclFloat32*/ 7, /*ncclSum*/ 0, ctx->nccl_comm, ctx->comm_stream);
+  if (group) {
+    int e2 = g_nccl.group_end();
+    if (!e) e = e2;
+  }
+  if (e) return nccl_fail(e, "ncclAllReduce");
+  for (int i = 0; i < n_bufs; ++i) {
+    dls_buf *b = bufs[i];
+    if (b->comm_ready) continue;   // the same buffer twice in one bucket
+    cudaEvent_t joined = nullptr;
+    DLS_CUDA(cudaEventCreateWithFlags(&joined, cudaEventDisableTiming));
+    ce = cudaEventRecord(joined, ctx->comm_stream);
+    if (ce != cudaSuccess) {
+      cudaEventDestroy(joined);
+      return dls::cuda_fail(ce, "cudaEventRecord(exchange)", __FILE__, __LINE__);
+    }
+    b->comm_ready = joined;
+    ctx->comm_pending.push_back(b);
+  }
+  return dls::finish_output(ctx, 0, bufs, n_bufs, nullptr, 0, nullptr);
+}
+
 int dls_comm_destroy(dls_ctx *ctx) {
   if (!ctx || !ctx->nccl_comm) return DLS_OK;
+  if (ctx->comm_stream) {
+    cudaStreamSynchronize(ctx->comm_stream);
+    cudaStreamDestroy(ctx->comm_stream);
+    ctx->comm_stream = nullptr;
+  }
   if (g_nccl.comm_destroy) g_nccl.comm_destroy(ctx->nccl_comm);
   ctx->nccl_comm = nullptr;
   ctx->comm_world = 1;

@@ -72,6 +72,7 @@ struct dls_buf {
   dls::Block block;
   int last_stream = 0;     // stream of the most recent writer
   cudaEvent_t ready = nullptr;  // recorded after the most recent writer (multi-stream contexts only)
+  cudaEvent_t comm_ready = nullptr;  // an all-reduce of this buffer is in flight on the exchange stream (comm.cpp)
   // tensor-core operand shadows (matmul.cu): a bf16 copy and a transposed fp32 copy of this buffer for a given
   // [rows, cols] interpretation, kept until the buffer is written again or released, so a tensor that feeds several
   // contractions (an activation in forward and in the weight-gradient GEMM) is staged once.
@@ -117,6 +118,10 @@ struct dls_ctx {
   int next_pool = 1;
   std::map<int, dls::GraphPool> pools;
 
+  // data-parallel exchange: collectives run on their own stream, forked from / joined to the compute stream with
+  // events, so that an all-reduce overlaps the backward kernels launched after it (comm.cpp)
+  cudaStream_t comm_stream = nullptr;
+  std::vector<dls_buf *> comm_pending;        // buffers whose comm_ready has not been waited for yet
   void *nccl_comm = nullptr;
   int comm_rank = 0, comm_world = 1;
 };
@@ -128,6 +133,8 @@ int pick_stream(dls_ctx *ctx);
 int alloc_block(dls_ctx *ctx, size_t bytes, int stream, Block *out);
 void free_block(dls_ctx *ctx, Block &blk);
 int new_buf(dls_ctx *ctx, size_t n_floats, int stream, dls_buf **out);
+int join_exchange(dls_ctx *ctx, int stream, dls_buf *buf);   // make `stream` wait for buf's pending all-reduce
+int join_all_exchanges(dls_ctx *ctx, int stream);
 int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_event *const *deps, int n_deps);
 int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_written, dls_buf *const *read, int n_read,
                   dls_event **done);

@@ -50,6 +50,7 @@ int dls_graph_end(dls_ctx *ctx, dls_graph **out) {
   DLS_CHECK(ctx->capture_pool != 0, DLS_ERR_INVALID, "dls_graph_end: no capture is open on this context");
   DLS_CUDA(cudaSetDevice(ctx->device));
   const int pool = ctx->capture_pool;
+  join_all_exchanges(ctx, 0);   // work forked onto the exchange stream must rejoin the origin stream before the end
   ctx->capture_pool = 0;
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(ctx->streams[0], &graph);
@@ -147,7 +148,8 @@ int dls_buf_copy(dls_ctx *ctx, dls_buf *dst, dls_buf *src, size_t n_floats) {
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   DLS_CUDA(cudaSetDevice(ctx->device));
   const int stream = ctx->n_streams == 1 ? 0 : dst->last_stream;
-  int rc = wait_inputs(ctx, stream, &src, 1, nullptr, 0);
+  dls_buf *both[2] = {src, dst};
+  int rc = wait_inputs(ctx, stream, both, 2, nullptr, 0);
   if (rc) return rc;
   if (n_floats && dst->ptr != src->ptr)
     DLS_CUDA(cudaMemcpyAsync(dst->ptr, src->ptr, n_floats * sizeof(float), cudaMemcpyDeviceToDevice, ctx->streams[stream]));

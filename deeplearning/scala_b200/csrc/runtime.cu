@@ -140,8 +140,36 @@ int new_buf(dls_ctx *ctx, size_t n_floats, int stream, dls_buf **out) {
 
 // Make `stream` wait for the producers of every input buffer and for the explicit dependencies
 // (replaces the `waitingEvents` list handed to clEnqueueNDRangeKernel, Tensors:1235, OpenCL:826).
+int join_exchange(dls_ctx *ctx, int stream, dls_buf *b) {
+  if (!b || !b->comm_ready) return DLS_OK;
+  cudaEvent_t ev = b->comm_ready;
+  b->comm_ready = nullptr;
+  for (size_t i = 0; i < ctx->comm_pending.size(); ++i)
+    if (ctx->comm_pending[i] == b) {
+      ctx->comm_pending.erase(ctx->comm_pending.begin() + i);
+      break;
+    }
+  cudaError_t e = cudaStreamWaitEvent(ctx->streams[stream], ev, 0);
+  cudaEventDestroy(ev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaStreamWaitEvent(exchange)", __FILE__, __LINE__);
+  return DLS_OK;
+}
+
+int join_all_exchanges(dls_ctx *ctx, int stream) {
+  while (!ctx->comm_pending.empty()) {
+    int rc = join_exchange(ctx, stream, ctx->comm_pending.back());
+    if (rc) return rc;
+  }
+  return DLS_OK;
+}
+
 int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_event *const *deps, int n_deps) {
   cudaStream_t st = ctx->streams[stream];
+  for (int i = 0; i < n_bufs; ++i)
+    if (bufs[i] && bufs[i]->comm_ready) {
+      int rc = join_exchange(ctx, stream, bufs[i]);
+      if (rc) return rc;
+    }
   if (ctx->n_streams > 1) {
     for (int i = 0; i < n_bufs; ++i) {
       dls_buf *b = bufs[i];
@@ -244,6 +272,7 @@ int dls_ctx_sync(dls_ctx *ctx) {
   DLS_CHECK(ctx, DLS_ERR_INVALID, "dls_ctx_sync: ctx is NULL");
   DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_ctx_sync: a capture is open on this context");
   DLS_CUDA(cudaSetDevice(ctx->device));
+  if (ctx->comm_stream) DLS_CUDA(cudaStreamSynchronize(ctx->comm_stream));
   for (cudaStream_t s : ctx->streams) DLS_CUDA(cudaStreamSynchronize(s));
   return DLS_OK;
 }
@@ -339,6 +368,7 @@ void dls_buf_release(dls_buf *buf) {
   dls_ctx *ctx = buf->ctx;
   {
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+    if (buf->comm_ready) join_exchange(ctx, buf->last_stream, buf);   // the block may be reused right away
     if (buf->ready) cudaEventDestroy(buf->ready);
     for (int k = 0; k < 2; ++k) free_block(ctx, buf->shadow[k]);
     free_block(ctx, buf->block);
@@ -358,7 +388,7 @@ int dls_buf_read(dls_ctx *ctx, dls_buf *buf, size_t offset, float *dst, size_t n
   DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_buf_read: host transfers cannot be recorded into a captured step");
   DLS_CUDA(cudaSetDevice(ctx->device));
   int stream = buf->last_stream;
-  int rc = wait_inputs(ctx, stream, nullptr, 0, deps, n_deps);
+  int rc = wait_inputs(ctx, stream, &buf, 1, deps, n_deps);
   if (rc) return rc;
   if (n_floats) {
     DLS_CUDA(cudaMemcpyAsync(dst, buf->ptr + offset, n_floats * sizeof(float), cudaMemcpyDeviceToHost, ctx->streams[stream]));
@@ -376,6 +406,8 @@ int dls_buf_write(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, s
   DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_buf_write: host transfers cannot be recorded into a captured step");
   DLS_CUDA(cudaSetDevice(ctx->device));
   int stream = buf->last_stream;
+  int rc = join_exchange(ctx, stream, buf);
+  if (rc) return rc;
   if (n_floats) {
     DLS_CUDA(cudaMemcpyAsync(buf->ptr + offset, src, n_floats * sizeof(float), cudaMemcpyHostToDevice, ctx->streams[stream]));
     ctx->stats.h2d_bytes += n_floats * sizeof(float);

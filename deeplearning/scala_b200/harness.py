@@ -26,6 +26,7 @@ class Exchange:
         self.backend, self.rank, self.world_size = backend, rank, world_size
         self._N, self._C = N, C
         N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
+        self._pending, self._pending_bytes = [], 0
 
     @staticmethod
     def unique_id() -> bytes:
@@ -35,11 +36,28 @@ class Exchange:
         N.check(N.lib.dls_comm_unique_id(buf))
         return buf.raw
 
+    bucket_bytes = 1 << 20      # gradients are collected until this much is pending, then exchanged by ONE grouped launch
+
     def allreduce(self, tensor: T.Tensor) -> T.Tensor:
-        N = self._N
-        cached = tensor.do_cache()                     # materialise the local partial gradient
-        N.check(N.lib.dls_allreduce_sum(self.backend.ctx, cached._buffer().handle, cached.size, None, 0, None))
+        """Materialise the local partial gradient and queue it; the bucket goes out once `bucket_bytes` are pending or
+        at `flush` (end of the step).  Small gradients (biases, early convolutions) then share one NCCL launch instead
+        of paying its latency each, and the big ones leave as soon as they exist and overlap the rest of backward."""
+        cached = tensor.do_cache()
+        self._pending.append(cached)
+        self._pending_bytes += cached.size * 4
+        if self._pending_bytes >= self.bucket_bytes:
+            self.flush()
         return cached
+
+    def flush(self):
+        pending, self._pending, self._pending_bytes = self._pending, [], 0
+        if not pending:
+            return
+        C, N = self._C, self._N
+        bufs = [t._buffer() for t in pending]
+        handles = (C.c_void_p * len(bufs))(*[b.handle for b in bufs])
+        counts = (C.c_size_t * len(bufs))(*[t.size for t in pending])
+        N.check(N.lib.dls_allreduce_sum_many(self.backend.ctx, handles, counts, len(bufs)))
 
 
 class Trainer:
@@ -54,7 +72,7 @@ class Trainer:
             if self.exchange is not None:
                 d = self.exchange.allreduce(d.broadcast(weight.data.shape))
             return d * self.learning_rate
-        self.P = Plugins(cumulative=False, optimizer_delta=delta, backend=self.backend)
+        self.P = Plugins(cumulative=False, optimizer_delta=delta, backend=self.backend, defer_updates=exchange is not None)
         self.L = Layers(self.P)
         self.weights: List = []
 
@@ -69,7 +87,11 @@ class Trainer:
 
     def run(self, loss_layer) -> float:
         """`loss.train` then the scalar loss read back (4 bytes D2H)."""
-        out = loss_layer.train().map(lambda data: float(data.sum().flat_array()[0])).run()
+        loss = loss_layer.train().map(lambda data: data.sum().do_cache()).run()
+        if self.exchange is not None:
+            self.exchange.flush()
+        self.P.flush_updates()
+        out = float(loss.flat_array()[0])
         if self.P.handled_exceptions:
             raise self.P.handled_exceptions.pop(0)
         return out
@@ -105,6 +127,9 @@ class CompiledStep:
         homes = [(w, w.data._buffer(), list(w.data.shape), w.data.padding) for w in trainer.weights]
         with be.capture() as graph:
             loss = trainer.loss_layer(self.x, self.target).train().map(lambda data: data.sum().do_cache()).run()
+            if trainer.exchange is not None:
+                trainer.exchange.flush()
+            trainer.P.flush_updates()
             for w, home, shape, padding in homes:
                 if w.data._buffer() is not home:
                     be.copy(home, w.data._buffer(), w.data.size)

@@ -164,17 +164,36 @@ class TensorWeight(Differentiable):
     def backward(self, original_delta: Do):
         """TW:50-74: delta = optimizer.delta; newData = (data - delta).doCache; release the old buffer; swap."""
         delta = original_delta.map(lambda d: self.plugins.optimizer_delta(self, d)).run()
+        if self.plugins.deferred_updates is not None:
+            # data-parallel training: the optimizer hook has put an all-reduce of this gradient in flight on the exchange
+            # stream; applying `data - delta` now would make the compute stream wait for it.  The swap is postponed to
+            # `flush_updates` (end of the step), so the collective overlaps the rest of the backward pass.  Forward
+            # values were computed from the tapes' own references, so the result is the same.
+            self.plugins.deferred_updates.append((self, delta))
+            return
+        self.apply(delta)
+
+    def apply(self, delta):
         old = self.data
         self.data = (old - delta).do_cache()
         old.release()                                                        # TW:65-72; tapes keep their own reference
 
 
 class Plugins:
-    def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None, backend=None):
+    def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None, backend=None,
+                 defer_updates: bool = False):
         self.cumulative = cumulative
+        self.deferred_updates: Optional[list] = [] if defer_updates else None
         self.backend = backend                                                    # None = the `gpu` singleton
         self.optimizer_delta = optimizer_delta or (lambda weight, delta: delta)   # Weights.scala:46-51 default
         self.handled_exceptions: List[BaseException] = []
+
+    def flush_updates(self):
+        """Apply the weight swaps postponed by `defer_updates`, in the order their deltas arrived."""
+        pending = self.deferred_updates
+        while pending:
+            weight, delta = pending.pop(0)
+            weight.apply(delta)
 
     def handle_exception(self, exc):                                         # Differentiables.scala:10-14
         self.handled_exceptions.append(exc)

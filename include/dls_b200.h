@@ -177,6 +177,9 @@ int dls_comm_unique_id(uint8_t *id128);                              /* 128-byte
 int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size);
 int dls_allreduce_sum(dls_ctx *ctx, dls_buf *buf, size_t n_floats, dls_event *const *deps, int n_deps,
                       dls_event **done);
+/* one bucket: every buffer SUM-all-reduced in place by one grouped NCCL launch on the exchange stream, overlapping the
+ * compute stream until a later launch touches one of the buffers (single-stream contexts; recordable) */
+int dls_allreduce_sum_many(dls_ctx *ctx, dls_buf *const *bufs, const size_t *n_floats, int n_bufs);
 int dls_comm_destroy(dls_ctx *ctx);
 
 /* ---- captured steps (new functionality).  The reference dispatches every tensor materialisation separately:
