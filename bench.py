@@ -43,7 +43,7 @@ def load_traffic():
     path = os.path.join(ROOT, "profiles", "r1_c2_traffic.json")
     try:
         with open(path) as f:
-            return float(json.load(f)["ew_vec_kernel<1>"])
+            return float(json.load(f)["ew_vec_kernel<1, 4>"])       # rows x inner launch, 4 tiles per lane: the C2a map
     except (OSError, KeyError, ValueError):
         return None
 
