@@ -27,6 +27,7 @@ DLS_OK, DLS_ERR_INVALID, DLS_ERR_NO_DEVICE, DLS_ERR_OOM, DLS_ERR_CUDA, DLS_ERR_U
 DLS_LAUNCH_DEFAULT, DLS_LAUNCH_REDUCE_SUM = 0, 1
 DLS_HASH_WANG, DLS_HASH_LCG = 0, 1
 DLS_GEMM_FP32, DLS_GEMM_TF32, DLS_GEMM_BF16 = 0, 1, 2
+DLS_OPT_MOMENTUM, DLS_OPT_ADAM = 0, 1
 
 
 class CtxOpts(C.Structure):
@@ -86,6 +87,7 @@ _SIG = {
     "dls_random": (C.c_int, [_P, C.c_size_t, C.c_uint32, _PP, _PP]),
     "dls_random_normal": (C.c_int, [_P, C.c_size_t, C.c_uint32, _PP, _PP]),
     "dls_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _PP, C.c_int, _PP]),
+    "dls_optimizer_step": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, C.c_size_t, _P]),
     "dls_matmul": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, _PP, C.c_int, _PP, _PP]),
     "dls_matmul_ex": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
                                 C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),

@@ -2,6 +2,7 @@
 //   N3  sum_kernel / sum_axis_*   full and single-axis reductions (warp shuffles + block tree, one launch)
 //   N5  random_kernel / random_normal_kernel   counter-based RNG, bit-compatible with Tensors:98-117, :398-443
 //   N6  sgd_kernel                fused in-place `data - lr * delta` (TW:63-72 without the buffer swap)
+//   N6b optimizer_kernel<kind>    momentum SGD / Adam: weight, state and gradient in one pass
 #include "common.h"
 #include "reduce.cuh"
 
@@ -274,6 +275,87 @@ __global__ void __launch_bounds__(kBlock) sgd_kernel(float *__restrict__ w, cons
 int launch_sgd(dls_ctx *ctx, int stream, float *w, const float *d, size_t n, float lr) {
   if (n == 0) return DLS_OK;
   sgd_kernel<<<grid_for(ctx, (n + 3) / 4), kBlock, 0, ctx->streams[stream]>>>(w, d, n, lr);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
+// ---- N6b: stateful optimizers, one pass over the weight, its state and the gradient -----------------------------------
+// The reference's extension point is `TensorOptimizerApi.delta` (TW:155-161, Weights:46-51); it ships learning rate /
+// L1 / L2 only for scalars (CumulativeFloatLayersSpec:18-47) and links Adagrad & co. from the README.  These kernels
+// are the fused form of the two stateful rules every model uses.  Arithmetic: one IEEE fp32 rounding per written
+// operation below, evaluated exactly in the written order (no FMA contraction: the file is built with -fmad=false),
+// so the CPU restatement used by the tests reproduces them bit for bit.
+struct OptArgs {
+  float lr, a, b, c, d, e;   // momentum: a = mu, b = weight_decay, c = nesterov (0/1)
+                             // adam:     a = beta1, b = beta2, c = eps, d = weight_decay, lr = lr / (1 - beta1^t), e = 1 / (1 - beta2^t)
+};
+
+__device__ __forceinline__ void momentum_one(float &w, float &v, float g, const OptArgs &o) {
+  if (o.b != 0.f) g = __fadd_rn(g, __fmul_rn(o.b, w));            // g += wd * w
+  v = __fadd_rn(__fmul_rn(o.a, v), g);                             // v = mu * v + g
+  const float step = o.c != 0.f ? __fadd_rn(g, __fmul_rn(o.a, v)) : v;   // nesterov: g + mu * v
+  w = __fsub_rn(w, __fmul_rn(o.lr, step));                         // w -= lr * step
+}
+
+__device__ __forceinline__ void adam_one(float &w, float &m, float &v, float g, const OptArgs &o) {
+  if (o.d != 0.f) g = __fadd_rn(g, __fmul_rn(o.d, w));            // g += wd * w   (L2 form, as in the original paper's code)
+  m = __fadd_rn(__fmul_rn(o.a, m), __fmul_rn(__fsub_rn(1.f, o.a), g));                   // m = b1 m + (1 - b1) g
+  v = __fadd_rn(__fmul_rn(o.b, v), __fmul_rn(__fmul_rn(__fsub_rn(1.f, o.b), g), g));     // v = b2 v + ((1 - b2) g) g
+  const float denom = __fadd_rn(__fsqrt_rn(__fmul_rn(v, o.e)), o.c);                     // sqrt(v / (1 - b2^t)) + eps
+  w = __fsub_rn(w, __fdiv_rn(__fmul_rn(o.lr, m), denom));                                // w -= (lr / (1 - b1^t)) m / denom
+}
+
+template <int KIND>  // 0: momentum SGD, 1: Adam
+__global__ void __launch_bounds__(kBlock) optimizer_kernel(float *__restrict__ w, float *__restrict__ s1, float *__restrict__ s2,
+                                                           const float *__restrict__ grad, size_t n,
+                                                           const OptArgs *__restrict__ hyper) {
+  // hyper-parameters live in device memory: Adam's bias corrections change every step, and a captured step (graph.cu)
+  // would otherwise replay the values of the step it was recorded on
+  const OptArgs o = *hyper;
+  const size_t n4 = n / 4;
+  float4 *w4 = reinterpret_cast<float4 *>(w), *a4 = reinterpret_cast<float4 *>(s1), *b4 = reinterpret_cast<float4 *>(s2);
+  const float4 *g4 = reinterpret_cast<const float4 *>(grad);
+  for (size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x; i < n4; i += (size_t)gridDim.x * kBlock) {
+    float4 x = w4[i], p = a4[i], g = __ldcs(g4 + i);
+    if (KIND == 0) {
+      momentum_one(x.x, p.x, g.x, o);
+      momentum_one(x.y, p.y, g.y, o);
+      momentum_one(x.z, p.z, g.z, o);
+      momentum_one(x.w, p.w, g.w, o);
+    } else {
+      float4 q = b4[i];
+      adam_one(x.x, p.x, q.x, g.x, o);
+      adam_one(x.y, p.y, q.y, g.y, o);
+      adam_one(x.z, p.z, q.z, g.z, o);
+      adam_one(x.w, p.w, q.w, g.w, o);
+      b4[i] = q;
+    }
+    w4[i] = x;
+    a4[i] = p;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const size_t i = n4 * 4 + threadIdx.x;
+    float x = w[i], p = s1[i];
+    if (KIND == 0) {
+      momentum_one(x, p, grad[i], o);
+    } else {
+      float q = s2[i];
+      adam_one(x, p, q, grad[i], o);
+      s2[i] = q;
+    }
+    w[i] = x;
+    s1[i] = p;
+  }
+}
+
+int launch_optimizer(dls_ctx *ctx, int stream, int kind, float *w, float *s1, float *s2, const float *grad, size_t n,
+                     const float *hyper) {
+  if (n == 0) return DLS_OK;
+  const OptArgs *o = reinterpret_cast<const OptArgs *>(hyper);
+  const int grid = grid_for(ctx, (n + 3) / 4);
+  if (kind == 0) optimizer_kernel<0><<<grid, kBlock, 0, ctx->streams[stream]>>>(w, s1, s2, grad, n, o);
+  else optimizer_kernel<1><<<grid, kBlock, 0, ctx->streams[stream]>>>(w, s1, s2, grad, n, o);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;

@@ -149,5 +149,7 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
 int launch_random(dls_ctx *ctx, int stream, float *out, size_t n, uint32_t seed, int hash_kind);
 int launch_random_normal(dls_ctx *ctx, int stream, float *out, size_t n_padded, uint32_t seed, int hash_kind);
 int launch_sgd(dls_ctx *ctx, int stream, float *w, const float *d, size_t n, float lr);
+int launch_optimizer(dls_ctx *ctx, int stream, int kind, float *w, float *s1, float *s2, const float *grad, size_t n,
+                     const float *hyper);
 
 }  // namespace dls

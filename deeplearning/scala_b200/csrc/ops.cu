@@ -201,4 +201,27 @@ int dls_sgd_update(dls_ctx *ctx, dls_buf *weight, dls_buf *delta, size_t n_float
   return finish_output(ctx, stream, &weight, 1, &delta, 1, done);
 }
 
+int dls_optimizer_step(dls_ctx *ctx, int kind, dls_buf *weight, dls_buf *state1, dls_buf *state2, dls_buf *grad, size_t n_floats,
+                       dls_buf *hyper) {
+  DLS_CHECK(ctx && weight && state1 && grad && hyper, DLS_ERR_INVALID, "dls_optimizer_step: NULL argument");
+  DLS_CHECK(kind == DLS_OPT_MOMENTUM || kind == DLS_OPT_ADAM, DLS_ERR_INVALID, "dls_optimizer_step: unknown optimizer kind");
+  DLS_CHECK(kind != DLS_OPT_ADAM || state2, DLS_ERR_INVALID, "dls_optimizer_step: Adam needs two state buffers");
+  DLS_CHECK(hyper->n >= 6, DLS_ERR_INVALID, "dls_optimizer_step: the hyper-parameter buffer holds six floats");
+  DLS_CHECK(n_floats <= weight->n && n_floats <= state1->n && n_floats <= grad->n && (!state2 || n_floats <= state2->n),
+            DLS_ERR_INVALID, "dls_optimizer_step: length exceeds a buffer");
+  DLS_CHECK(weight != grad && state1 != grad && state1 != weight && state2 != weight && state2 != state1 && state2 != grad,
+            DLS_ERR_INVALID, "dls_optimizer_step: buffers must be distinct");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CUDA(cudaSetDevice(ctx->device));
+  const int stream = pick_stream(ctx);
+  dls_buf *ins[5] = {weight, state1, grad, hyper, state2};
+  int rc = wait_inputs(ctx, stream, ins, state2 ? 5 : 4, nullptr, 0);
+  if (rc) return rc;
+  rc = launch_optimizer(ctx, stream, kind, weight->ptr, state1->ptr, state2 ? state2->ptr : nullptr, grad->ptr, n_floats, hyper->ptr);
+  if (rc) return rc;
+  dls_buf *outs[3] = {weight, state1, state2};
+  dls_buf *reads[2] = {grad, hyper};
+  return finish_output(ctx, stream, outs, state2 ? 3 : 2, reads, 2, nullptr);
+}
+
 }  // extern "C"

@@ -67,7 +67,9 @@ class Exchange:
 class Trainer:
     """One mixin stack + its weights.  `optimizer_delta` = learning_rate * (all-reduced) delta (TW:155-161)."""
 
-    def __init__(self, backend: Optional[T.Backend] = None, learning_rate: float = 0.01, exchange=None):
+    def __init__(self, backend: Optional[T.Backend] = None, learning_rate: float = 0.01, exchange=None, optimizer=None):
+        """`optimizer`: None = plain SGD through the `delta` hook (`delta * learning_rate`, one fused launch per weight),
+        or a stateful rule from `optimizers` (Momentum / Adam; `learning_rate` is then ignored)."""
         self.backend = backend or T.default_backend()
         self.learning_rate = float(learning_rate)
         self.exchange = exchange
@@ -75,8 +77,11 @@ class Trainer:
         def delta(weight, d):
             if self.exchange is not None:
                 d = self.exchange.allreduce(d.broadcast(weight.data.shape))
-            return d * self.learning_rate
-        self.P = Plugins(cumulative=False, optimizer_delta=delta, backend=self.backend, defer_updates=exchange is not None)
+            return d if optimizer is not None else d * self.learning_rate
+        self.P = Plugins(cumulative=False, optimizer_delta=delta, backend=self.backend, defer_updates=exchange is not None,
+                         optimizer=optimizer)
+        if exchange is not None:
+            self.P.before_flush.append(exchange.flush)
         self.L = Layers(self.P)
         self.weights: List = []
 
@@ -92,8 +97,6 @@ class Trainer:
     def run(self, loss_layer) -> float:
         """`loss.train` then the scalar loss read back (4 bytes D2H)."""
         loss = loss_layer.train().map(lambda data: data.sum().do_cache()).run()
-        if self.exchange is not None:
-            self.exchange.flush()
         self.P.flush_updates()
         out = float(loss.flat_array()[0])
         if self.P.handled_exceptions:
@@ -129,19 +132,25 @@ class CompiledStep:
         self.target = target.do_cache() if target is not None else None
         trainer.step(self.x, self.target)                    # eager once: every plan is built, operands are staged
         homes = [(w, w.data._buffer(), list(w.data.shape), w.data.padding) for w in trainer.weights]
-        with be.capture() as graph:
-            loss = trainer.loss_layer(self.x, self.target).train().map(lambda data: data.sum().do_cache()).run()
-            if trainer.exchange is not None:
-                trainer.exchange.flush()
-            trainer.P.flush_updates()
-            for w, home, shape, padding in homes:
-                if w.data._buffer() is not home:
-                    be.copy(home, w.data._buffer(), w.data.size)
-                    w.data.release()
-                    w.data = T.CachedTensor(be, home, shape, padding)
+        trainer.P.recording = True
+        try:
+            with be.capture() as graph:
+                loss = trainer.loss_layer(self.x, self.target).train().map(lambda data: data.sum().do_cache()).run()
+                trainer.P.flush_updates()
+                self._copy_back(homes)
+        finally:
+            trainer.P.recording = False
         if trainer.P.handled_exceptions:
             raise trainer.P.handled_exceptions.pop(0)
         self.graph, self._loss = graph, loss
+
+    def _copy_back(self, homes):
+        be = self.backend
+        for w, home, shape, padding in homes:
+            if w.data._buffer() is not home:                 # swapped (TW:63-72): the next replay must read the new value
+                be.copy(home, w.data._buffer(), w.data.size)
+                w.data.release()
+                w.data = T.CachedTensor(be, home, shape, padding)
 
     def write_inputs(self, x_host: np.ndarray, target_host: Optional[np.ndarray] = None):
         self.backend.write(self.x._buffer(), x_host)
@@ -149,6 +158,7 @@ class CompiledStep:
             self.backend.write(self.target._buffer(), target_host)
 
     def launch(self):
+        self.trainer.P.begin_step()                          # stateful optimizers: this replay's hyper-parameters
         self.graph.launch()
 
     def loss(self) -> float:

@@ -130,8 +130,14 @@ class TensorLayer(Differentiable):
         """TL:70-76: forward, backward with the scalar delta 1.0f (TL:55), yield the forward data."""
         def step(tape):
             tape.backward(Do.now(self.plugins.scalar(1.0)))
+            if not self.plugins.cumulative:                                  # cumulative layers flush on release: the
+                self.plugins.flush_updates()                                 # caller flushes after running the Do
             return Do.now(tape.data)
-        return self.forward().flat_map(step)
+
+        def begin():
+            self.plugins.begin_step()
+            return None, (lambda: None)
+        return Do(begin).flat_map(lambda _: self.forward()).flat_map(step)
 
     def predict(self) -> Do:
         """TL:78-80."""
@@ -181,9 +187,14 @@ class TensorWeight(Differentiable):
 
 class Plugins:
     def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None, backend=None,
-                 defer_updates: bool = False):
+                 defer_updates: bool = False, optimizer=None):
         self.cumulative = cumulative
-        self.deferred_updates: Optional[list] = [] if defer_updates else None
+        # a stateful optimizer (optimizers.Momentum / Adam) updates weights in place, which is only safe at the end of
+        # the step: it implies deferred updates
+        self.optimizer = optimizer
+        self.deferred_updates: Optional[list] = [] if (defer_updates or optimizer is not None) else None
+        self.before_flush: List[Callable] = []                                    # e.g. the gradient exchange's flush
+        self.recording = False                                                    # inside Backend.capture (harness.CompiledStep)
         self.backend = backend                                                    # None = the `gpu` singleton
         self.optimizer_delta = optimizer_delta or (lambda weight, delta: delta)   # Weights.scala:46-51 default
         self.handled_exceptions: List[BaseException] = []
@@ -191,9 +202,23 @@ class Plugins:
     def flush_updates(self):
         """Apply the weight swaps postponed by `defer_updates`, in the order their deltas arrived."""
         pending = self.deferred_updates
+        if not pending:
+            return
+        for hook in self.before_flush:
+            hook()
         while pending:
             weight, delta = pending.pop(0)
-            weight.apply(delta)
+            if self.optimizer is not None:
+                self.optimizer.step(weight, delta)
+            else:
+                weight.apply(delta)
+
+    def begin_step(self):
+        """Once per training step: a stateful optimizer advances its step counter and publishes this step's
+        hyper-parameters to the device.  Skipped while a step is being recorded (host writes cannot be captured; the
+        replays call it themselves)."""
+        if self.optimizer is not None and not self.recording:
+            self.optimizer.begin_step(self.backend or T.default_backend())
 
     def handle_exception(self, exc):                                         # Differentiables.scala:10-14
         self.handled_exceptions.append(exc)

@@ -151,6 +151,18 @@ int dls_random_normal(dls_ctx *ctx, size_t n_floats, uint32_t seed, dls_buf **ou
 int dls_sgd_update(dls_ctx *ctx, dls_buf *weight, dls_buf *delta, size_t n_floats, float learning_rate,
                    dls_event *const *deps, int n_deps, dls_event **done);
 
+/* ---- stateful optimizers behind TensorOptimizerApi.delta (TW:155-161, Weights:46-51; the reference has learning rate /
+ * L1 / L2 for scalars only, CumulativeFloatLayersSpec:18-47): weight, state and materialised gradient updated IN PLACE by
+ * one kernel.  `hyper` is a device buffer of six floats (device memory, so that a captured step replays with the values
+ * the host wrote before THIS replay -- Adam's bias corrections change every step):
+ *     momentum = {lr, mu, weight_decay, nesterov(0|1), 0, 0}
+ *     adam     = {lr / (1 - beta1^t), beta1, beta2, eps, weight_decay, 1 / (1 - beta2^t)}
+ * The rounding order is fixed (csrc/aux_kernels.cu) and restated by oracle/optim_oracle.py.  In-place, so only valid once
+ * every launch that reads the old weight has been issued (end of the step; harness `defer_updates`). */
+enum dls_optimizer_kind { DLS_OPT_MOMENTUM = 0, DLS_OPT_ADAM = 1 };
+int dls_optimizer_step(dls_ctx *ctx, int kind, dls_buf *weight, dls_buf *state1, dls_buf *state2, dls_buf *grad,
+                       size_t n_floats, dls_buf *hyper);
+
 /* ---- dense contraction C[M,N] = A[M,K] * B[K,N] (row-major, fp32 in/out); the lowering target for the unrolled
  * matmul trees of TensorsSpec:337-344 / :371-383 and the im2col convolution of TensorsSpec:144-210. */
 int dls_matmul(dls_ctx *ctx, dls_buf *a, dls_buf *b, size_t m, size_t n, size_t k, int transpose_a, int transpose_b,
