@@ -136,6 +136,78 @@ __global__ void __launch_bounds__(kBlock) sum_axis_slab_kernel(const float *__re
   }
 }
 
+// Tall narrow slabs with inner % 4 == 0 (bias gradients: [batch * H * W, channels]): a thread owns 4 consecutive columns
+// and walks rows with four independent 128-bit loads in flight; the block's row-lanes are folded through shared memory.
+__global__ void __launch_bounds__(kBlock) sum_axis_slab4_kernel(const float *__restrict__ in, float *__restrict__ out, size_t k,
+                                                                size_t inner, size_t rows_per_block) {
+  __shared__ float4 part[kBlock];
+  const size_t o = blockIdx.y;
+  const int inner4 = (int)(inner / 4);
+  const int lanes = kBlock / inner4;                      // row-lanes per block (>= 1)
+  const int c4 = threadIdx.x % inner4, rl = threadIdx.x / inner4;
+  const size_t r0 = (size_t)blockIdx.x * rows_per_block, r1 = min(k, r0 + rows_per_block);
+  float4 a[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rl < lanes) {
+    const float4 *p = reinterpret_cast<const float4 *>(in + o * k * inner) + c4;
+    size_t r = r0 + rl;
+    for (; r + 3 * (size_t)lanes < r1; r += 4 * (size_t)lanes) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldcs(p + (r + (size_t)u * lanes) * inner4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u].x += v[u].x;
+        a[u].y += v[u].y;
+        a[u].z += v[u].z;
+        a[u].w += v[u].w;
+      }
+    }
+    for (; r < r1; r += lanes) {
+      const float4 v = __ldcs(p + r * inner4);
+      a[0].x += v.x;
+      a[0].y += v.y;
+      a[0].z += v.z;
+      a[0].w += v.w;
+    }
+  }
+  part[threadIdx.x] = make_float4((a[0].x + a[1].x) + (a[2].x + a[3].x), (a[0].y + a[1].y) + (a[2].y + a[3].y),
+                                  (a[0].z + a[1].z) + (a[2].z + a[3].z), (a[0].w + a[1].w) + (a[2].w + a[3].w));
+  __syncthreads();
+  if (rl == 0) {
+    float4 s = part[c4];
+    for (int l = 1; l < lanes; ++l) {
+      const float4 v = part[l * inner4 + c4];
+      s.x += v.x;
+      s.y += v.y;
+      s.z += v.z;
+      s.w += v.w;
+    }
+    reinterpret_cast<float4 *>(out + (o * gridDim.x + blockIdx.x) * inner)[c4] = s;
+  }
+}
+
+// Second stage of the slab reduction: `rows` partial rows of `inner` columns per outer index; one warp per column.
+__global__ void __launch_bounds__(kBlock) sum_axis_finish_kernel(const float *__restrict__ in, float *__restrict__ out, size_t rows,
+                                                                 size_t inner) {
+  const size_t o = blockIdx.y;
+  const size_t col = (size_t)blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5);
+  if (col >= inner) return;
+  const float *p = in + o * rows * inner + col;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  size_t r = threadIdx.x & 31;
+  for (; r + 96 < rows; r += 128) {
+    s0 += __ldg(p + r * inner);
+    s1 += __ldg(p + (r + 32) * inner);
+    s2 += __ldg(p + (r + 64) * inner);
+    s3 += __ldg(p + (r + 96) * inner);
+  }
+  for (; r < rows; r += 32) s0 += __ldg(p + r * inner);
+  const float s = warp_sum((s0 + s1) + (s2 + s3));
+  if ((threadIdx.x & 31) == 0) out[o * inner + col] = s;
+}
+
 int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, size_t k, size_t inner, float *out) {
   cudaStream_t st = ctx->streams[stream];
   if (outer * inner == 0) return DLS_OK;
@@ -156,8 +228,12 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
     Block scratch;
     int rc = alloc_block(ctx, outer * blocks * inner * sizeof(float), stream, &scratch);
     if (rc) return rc;
-    sum_axis_slab_kernel<<<dim3((unsigned)blocks, (unsigned)outer), kBlock, 0, st>>>(in, (float *)scratch.ptr, k, inner, rows_per_block);
-    sum_axis_slab_kernel<<<dim3(1, (unsigned)outer), kBlock, 0, st>>>((const float *)scratch.ptr, out, blocks, inner, blocks);
+    if (inner % 4 == 0 && ((uintptr_t)in & 15) == 0)
+      sum_axis_slab4_kernel<<<dim3((unsigned)blocks, (unsigned)outer), kBlock, 0, st>>>(in, (float *)scratch.ptr, k, inner, rows_per_block);
+    else
+      sum_axis_slab_kernel<<<dim3((unsigned)blocks, (unsigned)outer), kBlock, 0, st>>>(in, (float *)scratch.ptr, k, inner, rows_per_block);
+    sum_axis_finish_kernel<<<dim3((unsigned)((inner + kBlock / 32 - 1) / (kBlock / 32)), (unsigned)outer), kBlock, 0, st>>>(
+        (const float *)scratch.ptr, out, blocks, inner);
     free_block(ctx, scratch);
     ctx->stats.kernel_launches++;
   } else if (outer * inner * 8 <= lanes_wanted && k >= 256) {
