@@ -452,14 +452,13 @@ struct G4Args {
   Instr code[kG4Code];
 };
 
-template <int V>
+template <int V, int R>
 __device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int *g, float *v) {
   const G4Leaf &L = A.leaves[li];
   const float *p = A.params[L.param];
   int addr = L.base;
 #pragma unroll
-  for (int d = 0; d < kMaxRank; ++d)
-    if (d < A.rank) addr += g[d] * L.ls[d];
+  for (int d = 0; d < R; ++d) addr += g[d] * L.ls[d];   // ls[d] == 0 and g[d] == 0 beyond the launch rank
   const int step = L.ls[0];
   unsigned valid = (1u << V) - 1u;
   const int nc = L.n_checks;
@@ -497,99 +496,136 @@ __device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int 
   for (int e = 0; e < V; ++e) v[e] = (valid >> e) & 1u ? __ldg(p + addr + e * step) : L.padding;
 }
 
-template <int V>
+// U tiles per lane per trip, a grid stride apart: every interpreted instruction issues U independent leaf fetches (the
+// interpreter cannot hoist loads across its own dispatch, so this is where memory-level parallelism comes from) and
+// its fetch / decode / branch is shared by U * V elements.
+// R: launch ranks this instantiation handles (4 covers NHWC tensors; 8 is the general case).
+template <int V, int U, int R>
 __global__ void __launch_bounds__(kBlock, 3) ew_gather4_kernel(const __grid_constant__ G4Args A) {
-  extern __shared__ float g4_slots[];   // [slot][V][thread], then the root staging area [thread][V][root]
-  float *stage = g4_slots + (size_t)A.n_slots * V * kBlock;
+  extern __shared__ float g4_slots[];   // [slot][U][V][thread], then the root staging area [U][thread][V][root]
+  float *stage = g4_slots + (size_t)A.n_slots * U * V * kBlock;
   float tsum = 0.f;
   const uint32_t stride = gridDim.x * kBlock;
   // with staged roots whole warps iterate together (the tail lanes of the last warp idle inside)
   const uint32_t t_end = A.stage_roots ? ((A.n_tiles + 31u) & ~31u) : A.n_tiles;
-  for (uint32_t t = blockIdx.x * kBlock + threadIdx.x; t < t_end; t += stride) {
-    const bool live = t < A.n_tiles;
-    int g[kMaxRank];
-    uint32_t row = fast_div(t, A.tpr);
-    g[0] = (int)(t - row * A.tpr.d) * V;
+  for (uint32_t t0 = blockIdx.x * kBlock + threadIdx.x; t0 < t_end; t0 += stride * U) {
+    bool live[U];
+    int g[U][R];
 #pragma unroll
-    for (int d = 1; d < kMaxRank; ++d) {
-      if (d < A.rank) {
+    for (int u = 0; u < U; ++u) {
+      const uint32_t t = t0 + (uint32_t)u * stride;
+      live[u] = t < A.n_tiles;
+      const uint32_t tc = live[u] ? t : 0u;          // dead tiles compute tile 0 (never stored): no predicated loads
+      uint32_t row = fast_div(tc, A.tpr);
+      g[u][0] = (int)(tc - row * A.tpr.d) * V;
+#pragma unroll
+      for (int d = 1; d < R; ++d) {                  // dims beyond the launch rank have extent 1: q == row, g == 0
         const uint32_t q = fast_div(row, A.dims[d]);
-        g[d] = (int)(row - q * A.dims[d].d);
+        g[u][d] = (int)(row - q * A.dims[d].d);
         row = q;
-      } else {
-        g[d] = 0;
       }
     }
-    float acc[V];
+    float acc[U][V];
 #pragma unroll
-    for (int e = 0; e < V; ++e) acc[e] = 0.f;
-    for (int pc = 0; live; ++pc) {
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int e = 0; e < V; ++e) acc[u][e] = 0.f;
+    for (int pc = 0;; ++pc) {
       const Instr in = A.code[pc];
       const int op = in.op;
       if (op == OP_END) break;
-      float s[V];
+      float s[U][V];
       if (in.src == SRC_LEAF) {
-        g4_leaf<V>(A, in.operand, g, s);
+#pragma unroll
+        for (int u = 0; u < U; ++u) g4_leaf<V, R>(A, in.operand, g[u], s[u]);
       } else if (in.src == SRC_LIT) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) s[e] = __uint_as_float(in.operand);
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) s[u][e] = __uint_as_float(in.operand);
       } else if (in.src == SRC_SLOT) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) s[e] = g4_slots[(in.operand * V + e) * kBlock + threadIdx.x];
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) s[u][e] = g4_slots[((in.operand * U + u) * V + e) * kBlock + threadIdx.x];
       }
       if (op <= OP_RMOD) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc[e] = apply_binary(op, acc[e], s[e]);
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[u][e] = apply_binary(op, acc[u][e], s[u][e]);
       } else if (op <= OP_LOG) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc[e] = apply_unary(op, acc[e]);
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[u][e] = apply_unary(op, acc[u][e]);
       } else if (op == OP_SAVE) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) g4_slots[(in.operand * V + e) * kBlock + threadIdx.x] = acc[e];
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) g4_slots[((in.operand * U + u) * V + e) * kBlock + threadIdx.x] = acc[u][e];
       } else if (op == OP_STORE) {
-        if (A.reduce) {
 #pragma unroll
-          for (int e = 0; e < V; ++e) tsum += acc[e];
-        } else if (A.stage_roots) {
+        for (int u = 0; u < U; ++u) {
+          if (A.reduce) {
+            if (live[u]) {
 #pragma unroll
-          for (int e = 0; e < V; ++e) stage[(threadIdx.x * V + e) * A.n_roots + in.operand] = acc[e];
-        } else {
+              for (int e = 0; e < V; ++e) tsum += acc[u][e];
+            }
+          } else if (A.stage_roots) {
 #pragma unroll
-          for (int e = 0; e < V; ++e) A.out[(size_t)(t * V + e) * A.n_roots + in.operand] = acc[e];
+            for (int e = 0; e < V; ++e) stage[((u * kBlock + threadIdx.x) * V + e) * A.n_roots + in.operand] = acc[u][e];
+          } else if (live[u]) {
+            const uint32_t t = t0 + (uint32_t)u * stride;
+#pragma unroll
+            for (int e = 0; e < V; ++e) A.out[(size_t)(t * V + e) * A.n_roots + in.operand] = acc[u][e];
+          }
         }
       } else {  // OP_MAC / OP_MSUB
-        float f[V];
-        g4_leaf<V>(A, in.aux, g, f);
+        float f[U][V];
 #pragma unroll
-        for (int e = 0; e < V; ++e) {
-          const float pr = __fmul_rn(f[e], s[e]);
-          acc[e] = op == OP_MAC ? __fadd_rn(acc[e], pr) : __fsub_rn(acc[e], pr);
-        }
+        for (int u = 0; u < U; ++u) g4_leaf<V, R>(A, in.aux, g[u], f[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) {
+            const float pr = __fmul_rn(f[u][e], s[u][e]);
+            acc[u][e] = op == OP_MAC ? __fadd_rn(acc[u][e], pr) : __fsub_rn(acc[u][e], pr);
+          }
       }
     }
     if (A.n_roots == 1) {
-      if (!live) continue;
-      if (A.reduce) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) tsum += acc[e];
-      } else if (V == 4) {
-        reinterpret_cast<float4 *>(A.out)[t] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      } else {
-        A.out[t] = acc[0];
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+        const uint32_t t = t0 + (uint32_t)u * stride;
+        if (A.reduce) {
+#pragma unroll
+          for (int e = 0; e < V; ++e) tsum += acc[u][e];
+        } else if (V == 4) {
+          reinterpret_cast<float4 *>(A.out)[t] = make_float4(acc[u][0], acc[u][1], acc[u][2], acc[u][3]);
+        } else {
+          A.out[t] = acc[u][0];
+        }
       }
     } else if (A.stage_roots) {
-      // the warp's 32 * V coordinates x n_roots outputs are one contiguous run of the output buffer
+      // a warp's 32 * V coordinates x n_roots outputs (per unrolled tile) are one contiguous run of the output buffer
       __syncwarp();
-      const uint32_t lane = threadIdx.x & 31u, t0 = t - lane;
-      const uint32_t lanes_live = min(32u, A.n_tiles - t0);
-      const uint32_t count = lanes_live * V * (uint32_t)A.n_roots;
-      const float *src = stage + (size_t)(threadIdx.x - lane) * V * A.n_roots;
-      float *dst = A.out + (size_t)t0 * V * A.n_roots;
-      if (V == 4) {
-        for (uint32_t i = lane * 4u; i < count; i += 128u)
-          *reinterpret_cast<float4 *>(dst + i) = *reinterpret_cast<const float4 *>(src + i);
-      } else {
-        for (uint32_t i = lane; i < count; i += 32u) dst[i] = src[i];
+      const uint32_t lane = threadIdx.x & 31u;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t tw = t0 - lane + (uint32_t)u * stride;          // first tile of this warp's run
+        if (tw >= A.n_tiles) continue;
+        const uint32_t lanes_live = min(32u, A.n_tiles - tw);
+        const uint32_t count = lanes_live * V * (uint32_t)A.n_roots;
+        const float *src = stage + (size_t)(u * kBlock + threadIdx.x - lane) * V * A.n_roots;
+        float *dst = A.out + (size_t)tw * V * A.n_roots;
+        if (V == 4) {
+          for (uint32_t i = lane * 4u; i < count; i += 128u)
+            *reinterpret_cast<float4 *>(dst + i) = *reinterpret_cast<const float4 *>(src + i);
+        } else {
+          for (uint32_t i = lane; i < count; i += 32u) dst[i] = src[i];
+        }
       }
       __syncwarp();
     }
@@ -597,13 +633,18 @@ __global__ void __launch_bounds__(kBlock, 3) ew_gather4_kernel(const __grid_cons
   if (A.reduce) grid_sum_finish(tsum, A.red);
 }
 
+constexpr int kG4SmemLimit = 75 * 1024;   // three CTAs per SM: slots + root staging of the widest im2col (2 x 9 roots x 4 KB)
+
 // ---- host side -------------------------------------------------------------------------------------------------------
 int query_ew_occupancy(dls_ctx *ctx) {
   int b = 0;
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   DLS_CUDA(cudaFuncSetAttribute(ew_gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+#define DLS_G4_ATTR(VV, UU, RR) \
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4_kernel<VV, UU, RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
+  DLS_G4_ATTR(4, 1, 4) DLS_G4_ATTR(1, 1, 4) DLS_G4_ATTR(4, 2, 4) DLS_G4_ATTR(1, 2, 4)
+  DLS_G4_ATTR(4, 1, 8) DLS_G4_ATTR(1, 1, 8) DLS_G4_ATTR(4, 2, 8) DLS_G4_ATTR(1, 2, 8)
+#undef DLS_G4_ATTR
 #define DLS_VEC_ATTR(O, UU) \
   DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<O, UU>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   DLS_VEC_ATTR(0, 1) DLS_VEC_ATTR(0, 2) DLS_VEC_ATTR(0, 4)
@@ -764,20 +805,44 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
     for (int i = 0; i < P.n_params; ++i) A.params[i] = params[i]->ptr;
     memcpy(A.leaves, P.g4leaves.data(), P.g4leaves.size() * sizeof(G4Leaf));
     memcpy(A.code, P.code.data(), P.code.size() * sizeof(Instr));
-    size_t smem = (size_t)P.n_slots * V * kBlock * sizeof(float);
-    const size_t stage_bytes = (size_t)kBlock * V * P.n_roots * sizeof(float);
-    A.stage_roots = P.n_roots > 1 && !reduce_sum && smem + stage_bytes <= 48 * 1024 ? 1 : 0;
+    static const int forced_g4_unroll = [] {
+      const char *e = getenv("DLS_G4_UNROLL");
+      return e ? atoi(e) : 0;
+    }();
+    // two tiles per lane once there is enough work for every SM to stay full; single-root programs only unless forced
+    // (the root staging area of a join doubles with U and costs occupancy)
+    int U = (long long)A.n_tiles >= (long long)ctx->sm_count * kBlock * 8 && P.n_roots == 1 ? 2 : 1;
+    if (forced_g4_unroll == 1 || forced_g4_unroll == 2) U = forced_g4_unroll;
+    size_t smem = 0, stage_bytes = 0;
+    for (;; U = 1) {
+      smem = (size_t)P.n_slots * U * V * kBlock * sizeof(float);
+      stage_bytes = (size_t)U * kBlock * V * P.n_roots * sizeof(float);
+      if (U == 1 || smem + (P.n_roots > 1 && !reduce_sum ? stage_bytes : 0) <= (size_t)kG4SmemLimit) break;
+    }
+    A.stage_roots = P.n_roots > 1 && !reduce_sum && smem + stage_bytes <= (size_t)kG4SmemLimit ? 1 : 0;
     if (A.stage_roots) smem += stage_bytes;
     int per_sm = 0;
-    if (V == 4) DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4_kernel<4>, kBlock, smem));
-    else DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4_kernel<1>, kBlock, smem));
+#define DLS_G4_OCC(VV, UU) DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4_kernel<VV, UU, 8>, kBlock, smem))
+    if (V == 4 && U == 2) DLS_G4_OCC(4, 2);
+    else if (V == 4) DLS_G4_OCC(4, 1);
+    else if (U == 2) DLS_G4_OCC(1, 2);
+    else DLS_G4_OCC(1, 1);
+#undef DLS_G4_OCC
     if (per_sm < 1) per_sm = 1;
-    long long want = ((long long)A.n_tiles + kBlock - 1) / kBlock;
+    long long want = ((long long)A.n_tiles + (long long)kBlock * U - 1) / ((long long)kBlock * U);
     long long cap = (long long)ctx->sm_count * per_sm;
     if (reduce_sum && cap > kReduceMaxBlocks) cap = kReduceMaxBlocks;
     const int grid = (int)std::max<long long>(1, std::min<long long>(want, cap));
-    if (V == 4) ew_gather4_kernel<4><<<grid, kBlock, smem, st>>>(A);
-    else ew_gather4_kernel<1><<<grid, kBlock, smem, st>>>(A);
+#define DLS_G4_GO(RR)                                                                   \
+  do {                                                                                  \
+    if (V == 4 && U == 2) ew_gather4_kernel<4, 2, RR><<<grid, kBlock, smem, st>>>(A);   \
+    else if (V == 4) ew_gather4_kernel<4, 1, RR><<<grid, kBlock, smem, st>>>(A);        \
+    else if (U == 2) ew_gather4_kernel<1, 2, RR><<<grid, kBlock, smem, st>>>(A);        \
+    else ew_gather4_kernel<1, 1, RR><<<grid, kBlock, smem, st>>>(A);                    \
+  } while (0)
+    if (r <= 4) DLS_G4_GO(4);
+    else DLS_G4_GO(8);
+#undef DLS_G4_GO
   } else {
     DLS_CHECK(P.n_params <= kInlineParams, DLS_ERR_UNSUPPORTED, "more than 128 distinct parameters in one gather tree");
     int rc = upload_tables(P);
