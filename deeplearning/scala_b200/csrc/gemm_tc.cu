@@ -131,6 +131,71 @@ __device__ __forceinline__ Tile tile_coord(int t, int tiles_m, int tiles_n) {
   return c;
 }
 
+#ifdef DLS_GEMM_TRACE
+// Debug build only (make NVFLAGS_EXTRA=-DDLS_GEMM_TRACE): CTA 0 records (event id, globaltimer ns) pairs of its pipeline,
+// 160 fire-and-forget slots per warp (no atomics: a returning atomic costs about a microsecond and would distort the trace).
+__device__ unsigned long long g_gemm_trace[1024];
+__device__ unsigned int g_gemm_trace_n;
+#define DLS_TRACE(id)                                                                                  \
+  do {                                                                                                 \
+    if (blockIdx.x == 0 && tr_n < 160) {                                                               \
+      unsigned long long t_;                                                                           \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                           \
+      g_gemm_trace[(threadIdx.x >> 5) * 160 + tr_n++] = ((unsigned long long)(id) << 48) | (t_ & 0xFFFFFFFFFFFFull); \
+    }                                                                                                  \
+  } while (0)
+#define DLS_TRACE_DECL unsigned tr_n = 0;
+#else
+#define DLS_TRACE(id)
+#define DLS_TRACE_DECL
+#endif
+
+// 32 lanes x 32 consecutive fp32 columns of the accumulator -> 32 registers per lane (asynchronous until tcgen05.wait::ld)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t (&v)[32], uint32_t taddr) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+// Epilogue arithmetic of one 32-column chunk.  The (bias, activation) combination is dispatched ONCE per chunk and each
+// combination is a straight-line loop: an epilogue warp is alone on its scheduler, so a per-element branch costs its
+// full pipeline latency with nothing to hide it (measured: 1.25 us per chunk with the branches inside the loop).
+template <int BIAS, int ACT>
+__device__ __forceinline__ void epi_math(const uint32_t (&v)[32], float (&f)[32], float row_bias, const float *__restrict__ bias,
+                                         int col0, int N) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    float x = __uint_as_float(v[j]);
+    if (BIAS == 1) x = __fadd_rn(x, row_bias);
+    if (BIAS == 2) x = __fadd_rn(x, (col0 + j < N) ? __ldg(bias + col0 + j) : 0.f);
+    if (ACT == 1) x = tanhf(x);
+    if (ACT == 2) x = fmaxf(x, 0.f);
+    f[j] = x;
+  }
+}
+
+__device__ __forceinline__ void epi_apply(const uint32_t (&v)[32], float (&f)[32], int bias_mode, int act, float row_bias,
+                                          const float *__restrict__ bias, int col0, int N) {
+  switch (bias_mode * 3 + act) {
+    case 0: epi_math<0, 0>(v, f, row_bias, bias, col0, N); break;
+    case 1: epi_math<0, 1>(v, f, row_bias, bias, col0, N); break;
+    case 2: epi_math<0, 2>(v, f, row_bias, bias, col0, N); break;
+    case 3: epi_math<1, 0>(v, f, row_bias, bias, col0, N); break;
+    case 4: epi_math<1, 1>(v, f, row_bias, bias, col0, N); break;
+    case 5: epi_math<1, 2>(v, f, row_bias, bias, col0, N); break;
+    case 6: epi_math<2, 0>(v, f, row_bias, bias, col0, N); break;
+    case 7: epi_math<2, 1>(v, f, row_bias, bias, col0, N); break;
+    default: epi_math<2, 2>(v, f, row_bias, bias, col0, N); break;
+  }
+}
+
 template <bool TF32, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
@@ -164,6 +229,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
   const int n_work = n_tiles * splits;
 
+  DLS_TRACE_DECL
+  if (threadIdx.x == 0) DLS_TRACE(1);
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), 1);
@@ -198,6 +265,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         const int kb0 = (w / n_tiles) * kb_per_split, kb1 = min(num_kb, kb0 + kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
+          DLS_TRACE(10);
           const uint32_t a_dst = smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_dst = a_dst + A_STAGE_BYTES;
           mbar_expect_tx(full_bar(stage), STAGE_BYTES);
@@ -246,6 +314,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         const int kb0 = (w / n_tiles) * kb_per_split, kb1 = min(num_kb, kb0 + kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
+          DLS_TRACE(20);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_STAGE_BYTES;
@@ -262,6 +331,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           }
         }
         umma_commit(tfull_bar(as));        // accumulator complete -> epilogue
+        DLS_TRACE(21);
       }
     }
   } else {
@@ -275,6 +345,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       mbar_wait(tfull_bar(as), aphase);
+      if (warp == 2 && lane == 0) DLS_TRACE(30);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       float row_bias = 0.f;
       if (bias_mode == 1 && tc.m0 + quarter * 32 + lane < M) row_bias = __ldg(bias + tc.m0 + quarter * 32 + lane);
@@ -285,28 +356,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         const int col0 = tc.n0 + c * EPI_CHUNK;
         if (col0 >= N) break;                                     // warp uniform
         uint32_t v[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN + c * EPI_CHUNK);
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-              "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-              "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-              "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-            : "r"(taddr)
-            : "memory");
+        tmem_ld_32x32(v, tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN + c * EPI_CHUNK));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float x = __uint_as_float(v[j]);
-          if (bias_mode == 1) x = __fadd_rn(x, row_bias);
-          else if (bias_mode == 2) x = __fadd_rn(x, (col0 + j < N) ? __ldg(bias + col0 + j) : 0.f);
-          if (act == 1) x = tanhf(x);
-          else if (act == 2) x = fmaxf(x, 0.f);
-          f[j] = x;
-        }
+        epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
         if (direct_store) {
           if (row < c_rows) {
             float *dst = C + (long long)row * ldc + col0;
@@ -337,12 +390,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(as));
+      if (warp == 2 && lane == 0) DLS_TRACE(31);
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
 
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (threadIdx.x == 0) DLS_TRACE(2);
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
@@ -595,8 +650,8 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
     sp.c_rows = sp.splits * m_pad;
     kepi = GemmEpilogue();
   }
-  const int direct = ((ld_dst % 4) != 0 || ((uintptr_t)dst % 16) != 0) ? 1 : 0;
-  if (!direct) {
+  const int direct = ((ld_dst % 4) != 0 || ((uintptr_t)dst % 16) != 0) ? 1 : 0;   // unaligned output: scalar stores
+  if (direct == 0) {
     rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dst, (uint64_t)N, (uint64_t)sp.c_rows, (uint64_t)ld_dst, EPI_CHUNK, 32);
   } else {
     mc = ma;   // unused by the kernel in direct-store mode
@@ -629,3 +684,17 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
 }
 
 }  // namespace dls
+
+#ifdef DLS_GEMM_TRACE
+extern "C" int dls_debug_gemm_trace(unsigned long long *out, int cap) {
+  static unsigned long long host[1024];
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(host, dls::tc::g_gemm_trace, sizeof(host));
+  int n = 0;
+  for (int i = 0; i < 1024 && n < cap; ++i)
+    if (host[i]) out[n++] = host[i];
+  memset(host, 0, sizeof(host));
+  cudaMemcpyToSymbol(dls::tc::g_gemm_trace, host, sizeof(host));
+  return n;
+}
+#endif
