@@ -98,6 +98,13 @@ int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size) 
   int e = g_nccl.comm_init_rank(&comm, world_size, id, rank);
   if (e) return nccl_fail(e, "ncclCommInitRank");
   ctx->nccl_comm = comm;
+  {
+    // a collective kernel runs one CTA per channel; a persistent one-CTA-per-SM GEMM launched next to it would otherwise
+    // queue the CTAs that find their SM taken behind the whole first wave (measured: the overlap hid almost nothing)
+    const char *e = getenv("NCCL_MAX_NCHANNELS");
+    const int ch = e ? atoi(e) : 0;
+    ctx->exchange_sms = ch > 0 && ch <= 64 ? ch : 16;
+  }
   ctx->comm_rank = rank;
   ctx->comm_world = world_size;
   return DLS_OK;

@@ -121,6 +121,8 @@ struct dls_ctx {
   // data-parallel exchange: collectives run on their own stream, forked from / joined to the compute stream with
   // events, so that an all-reduce overlaps the backward kernels launched after it (comm.cpp)
   cudaStream_t comm_stream = nullptr;
+  int exchange_sms = 0;                       // SMs a collective occupies (its channel count); one-CTA-per-SM kernels launched
+                                              // while an exchange is in flight leave that many SMs to it
   std::vector<dls_buf *> comm_pending;        // buffers whose comm_ready has not been waited for yet
   void *nccl_comm = nullptr;
   int comm_rank = 0, comm_world = 1;

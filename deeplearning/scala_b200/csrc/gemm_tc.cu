@@ -549,7 +549,9 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
     configured = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * sp.splits;
-  const int grid = tiles < ctx->sm_count ? tiles : ctx->sm_count;
+  // one persistent CTA per SM; SMs hosting an in-flight collective (data-parallel exchange) are left to it
+  const int sms = ctx->comm_pending.empty() ? ctx->sm_count : std::max(1, ctx->sm_count - ctx->exchange_sms);
+  const int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, sp.splits,
                                               sp.kb_per_split, sp.c_rows);
   DLS_CUDA(cudaGetLastError());

@@ -40,7 +40,8 @@ class Exchange:
         N.check(N.lib.dls_comm_unique_id(buf))
         return buf.raw
 
-    bucket_bytes = 1 << 20      # gradients are collected until this much is pending, then exchanged by ONE grouped launch
+    # gradients are collected until this much is pending, then exchanged by ONE grouped launch (DLS_BUCKET_BYTES overrides)
+    bucket_bytes = int(os.environ.get("DLS_BUCKET_BYTES", 1 << 20))
 
     def allreduce(self, tensor: T.Tensor) -> T.Tensor:
         """Materialise the local partial gradient and queue it; the bucket goes out once `bucket_bytes` are pending or
