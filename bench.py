@@ -525,6 +525,8 @@ def main_train(args, rank, world, local):
            "launches_per_step": r["launches_per_step"], "driver_allocs_in_timed_region": r["driver_allocs_in_timed_region"],
            "mode": r["mode"], "eager": r["eager"], "captured": r.get("captured"),
            "loss": {"first": r["first_loss"], "last": r["last_loss"]}}
+    if "exchange" in r:
+        out["config"]["exchange"] = r["exchange"]
     if rank == 0:
         print(json.dumps(out))
     if dist is not None:

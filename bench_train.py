@@ -49,7 +49,7 @@ def build(workload, be, exchange=None, rank=0, world=1, gemm_mode=None):
         desc = ("C3: CNN 3 conv3x3 (3-32-64-128, ReLU, 2x nearest down-sampling) via im2col + 2 FC (8192-256-10), "
                 "batch 256 NHWC 32x32x3 per GPU, squared error, SGD")
         if workload == "c5":
-            desc = "C5: " + desc[4:] + "; data parallel, weak scaling, NCCL SUM all-reduce of every weight gradient"
+            desc = "C5: " + desc[4:] + "; data parallel, weak scaling, SUM all-reduce of every weight gradient (NCCL + NVLink peer memory)"
     else:
         raise ValueError(workload)
     return model, x, t, batch, flop, desc
@@ -131,6 +131,10 @@ def run(workload, be, steps, warmup, e2e_steps=5, exchange=None, rank=0, world=1
     if pt is not None:
         N.lib.dls_host_free(pt)
     n_params = int(sum(np.prod(w.data.shape) for w in model.weights))
+    if exchange is not None:
+        out["exchange"] = ("gradients >= %d bytes: grouped NCCL all-reduce on the exchange stream; smaller ones summed over NVLink peer "
+                           "memory and every weight updated by one launch (dls_peer_sgd_step)" % exchange.peer_bytes
+                           if exchange.peer else "grouped NCCL all-reduce on the exchange stream, one update launch per weight")
     out.update({"ms_per_step": ms / steps, "ms_total": ms, "e2e_ms_per_step": e2e_s * 1e3 / e2e_steps, "parameters": n_params,
                 "launches_per_step": launches, "first_loss": losses[0], "last_loss": losses[-1]})
     return out

@@ -95,6 +95,9 @@ _SIG = {
     "dls_comm_init": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_int]),
     "dls_allreduce_sum": (C.c_int, [_P, _P, C.c_size_t, _PP, C.c_int, _PP]),
     "dls_allreduce_sum_many": (C.c_int, [_P, _PP, C.POINTER(C.c_size_t), C.c_int]),
+    "dls_peer_init": (C.c_int, [_P, C.c_size_t]),
+    "dls_peer_ready": (C.c_int, [_P]),
+    "dls_peer_sgd_step": (C.c_int, [_P, _PP, _PP, C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.c_int, C.c_float]),
     "dls_comm_destroy": (C.c_int, [_P]),
     "dls_graph_begin": (C.c_int, [_P]),
     "dls_graph_end": (C.c_int, [_P, _PP]),

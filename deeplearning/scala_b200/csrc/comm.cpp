@@ -18,6 +18,7 @@ typedef int (*fn_all_reduce)(const void *, void *, size_t, int, int, nccl_comm_t
 typedef int (*fn_comm_destroy)(nccl_comm_t);
 typedef const char *(*fn_get_error_string)(int);
 typedef int (*fn_group)(void);
+typedef int (*fn_all_gather)(const void *, void *, size_t, int, nccl_comm_t, cudaStream_t);
 
 struct NcclApi {
   void *handle = nullptr;
@@ -27,6 +28,7 @@ struct NcclApi {
   fn_comm_destroy comm_destroy = nullptr;
   fn_get_error_string get_error_string = nullptr;
   fn_group group_start = nullptr, group_end = nullptr;
+  fn_all_gather all_gather = nullptr;
 };
 
 NcclApi g_nccl;
@@ -54,6 +56,7 @@ int load_nccl() {
   g_nccl.get_error_string = (fn_get_error_string)dlsym(h, "ncclGetErrorString");
   g_nccl.group_start = (fn_group)dlsym(h, "ncclGroupStart");
   g_nccl.group_end = (fn_group)dlsym(h, "ncclGroupEnd");
+  g_nccl.all_gather = (fn_all_gather)dlsym(h, "ncclAllGather");
   if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.all_reduce || !g_nccl.comm_destroy) {
     dls::set_error("libnccl is missing a required symbol");
     dlclose(h);
@@ -71,6 +74,27 @@ int nccl_fail(int code, const char *what) {
 }
 
 }  // namespace
+
+namespace dls {
+
+// Small host-side all-gather over the context's communicator (setup paths only: it synchronises the stream).
+int comm_allgather_bytes(dls_ctx *ctx, const void *mine, void *all_host, size_t bytes) {
+  DLS_CHECK(ctx->nccl_comm && g_nccl.all_gather, DLS_ERR_COMM, "all-gather: no communicator, or libnccl lacks ncclAllGather");
+  char *dev = nullptr;
+  const size_t world = (size_t)ctx->comm_world;
+  DLS_CUDA(cudaMalloc((void **)&dev, bytes * (world + 1)));
+  cudaError_t ce = cudaMemcpyAsync(dev, mine, bytes, cudaMemcpyHostToDevice, ctx->streams[0]);
+  int e = 0;
+  if (ce == cudaSuccess) e = g_nccl.all_gather(dev, dev + bytes, bytes, /*ncclInt8*/ 0, ctx->nccl_comm, ctx->streams[0]);
+  if (ce == cudaSuccess && !e) ce = cudaMemcpyAsync(all_host, dev + bytes, bytes * world, cudaMemcpyDeviceToHost, ctx->streams[0]);
+  if (ce == cudaSuccess && !e) ce = cudaStreamSynchronize(ctx->streams[0]);
+  cudaFree(dev);
+  if (e) return nccl_fail(e, "ncclAllGather");
+  if (ce != cudaSuccess) return cuda_fail(ce, "all-gather staging", __FILE__, __LINE__);
+  return DLS_OK;
+}
+
+}  // namespace dls
 
 extern "C" {
 
@@ -178,6 +202,9 @@ int dls_allreduce_sum_many(dls_ctx *ctx, dls_buf *const *bufs, const size_t *n_f
 
 int dls_comm_destroy(dls_ctx *ctx) {
   if (!ctx || !ctx->nccl_comm) return DLS_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  dls::peer_destroy(ctx);
   if (ctx->comm_stream) {
     cudaStreamSynchronize(ctx->comm_stream);
     cudaStreamDestroy(ctx->comm_stream);

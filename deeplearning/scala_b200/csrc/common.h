@@ -58,6 +58,8 @@ struct CachedPlan {
 
 }  // namespace dls
 
+namespace dls { struct PeerState; }   // peer.cu
+
 struct dls_event {
   std::atomic<int> rc{1};
   dls_ctx *ctx = nullptr;
@@ -126,6 +128,7 @@ struct dls_ctx {
   std::vector<dls_buf *> comm_pending;        // buffers whose comm_ready has not been waited for yet
   void *nccl_comm = nullptr;
   int comm_rank = 0, comm_world = 1;
+  dls::PeerState *peer = nullptr;             // NVLink peer segment of the one-launch end-of-step exchange (peer.cu)
 };
 
 namespace dls {
@@ -140,6 +143,10 @@ int join_all_exchanges(dls_ctx *ctx, int stream);
 int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_event *const *deps, int n_deps);
 int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_written, dls_buf *const *read, int n_read,
                   dls_event **done);
+
+// peer.cu
+void peer_destroy(dls_ctx *ctx);
+int peer_check(dls_ctx *ctx);   // DLS_ERR_COMM once a peer exchange has timed out
 
 // ew_kernels.cu
 int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params, dls_buf *out, bool reduce_sum);

@@ -274,7 +274,7 @@ int dls_ctx_sync(dls_ctx *ctx) {
   DLS_CUDA(cudaSetDevice(ctx->device));
   if (ctx->comm_stream) DLS_CUDA(cudaStreamSynchronize(ctx->comm_stream));
   for (cudaStream_t s : ctx->streams) DLS_CUDA(cudaStreamSynchronize(s));
-  return DLS_OK;
+  return peer_check(ctx);
 }
 
 int dls_ctx_trim(dls_ctx *ctx) {
@@ -396,7 +396,7 @@ int dls_buf_read(dls_ctx *ctx, dls_buf *buf, size_t offset, float *dst, size_t n
   }
   if (done) return finish_output(ctx, stream, nullptr, 0, &buf, 1, done);
   DLS_CUDA(cudaStreamSynchronize(ctx->streams[stream]));
-  return DLS_OK;
+  return peer_check(ctx);   // a timed-out peer exchange invalidates whatever was read
 }
 
 int dls_buf_write(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, size_t n_floats, dls_event **done) {

@@ -7,6 +7,7 @@ Shapes, seeds and layouts follow SURVEY.md section 8(d).  Synthetic data only.
 from __future__ import annotations
 
 import os
+import sys
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -31,6 +32,16 @@ class Exchange:
         os.environ.setdefault("NCCL_MAX_NCHANNELS", "4")
         N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
         self._pending, self._pending_bytes = [], 0
+        self._over_nccl = set()                 # ids of the gradient buffers this step sent through NCCL
+        # gradients below `peer_bytes` skip NCCL: they are summed and applied by the one-launch end-of-step kernel over
+        # NVLink peer memory (csrc/peer.cu).  Needs cudaIpc between the ranks (one node); otherwise NCCL carries everything.
+        self.peer = False
+        if world_size > 1 and self.peer_bytes > 0:
+            rc = N.lib.dls_peer_init(backend.ctx, self.peer_staging_floats)
+            if rc == 0:
+                self.peer = True
+            else:
+                sys.stderr.write("dls exchange: peer-memory path unavailable (%s); NCCL carries every gradient\n" % N.last_error())
 
     @staticmethod
     def unique_id() -> bytes:
@@ -42,12 +53,17 @@ class Exchange:
 
     # gradients are collected until this much is pending, then exchanged by ONE grouped launch (DLS_BUCKET_BYTES overrides)
     bucket_bytes = int(os.environ.get("DLS_BUCKET_BYTES", 1 << 20))
+    # one-shot peer exchange below this size (every rank reads world-1 remote copies: latency optimal, bandwidth
+    # wasteful, so only for what is small); DLS_PEER_BYTES=0 turns the path off
+    peer_bytes = int(os.environ.get("DLS_PEER_BYTES", 1 << 20))
+    peer_staging_floats = 1 << 21
 
     def allreduce(self, tensor: T.Tensor) -> T.Tensor:
         """Materialise the local partial gradient and queue it; the bucket goes out once `bucket_bytes` are pending or
         at `flush` (end of the step).  Small gradients (biases, early convolutions) then share one NCCL launch instead
         of paying its latency each, and the big ones leave as soon as they exist and overlap the rest of backward."""
         cached = tensor.do_cache()
+        self._over_nccl.add(id(cached._buffer()))
         self._pending.append(cached)
         self._pending_bytes += cached.size * 4
         if self._pending_bytes >= self.bucket_bytes:
@@ -65,6 +81,47 @@ class Exchange:
         N.check(N.lib.dls_allreduce_sum_many(self.backend.ctx, handles, counts, len(bufs)))
 
 
+class ExchangeSgd:
+    """Plain SGD of a data-parallel job with the end of the step fused (takes the optimizer slot of `Plugins`): large
+    gradients leave over NCCL as soon as they exist (`Exchange.allreduce`, overlapping backward), small ones are only
+    materialised; `step_many` then issues ONE launch that sums the small ones over NVLink peer memory and updates every
+    weight in place, w = w - lr * sum (dls_peer_sgd_step).  Same arithmetic as `data - delta * learningRate`."""
+    t = 0
+
+    def __init__(self, exchange: "Exchange", learning_rate: float):
+        self.exchange, self.learning_rate = exchange, float(learning_rate)
+
+    def gradient(self, weight, delta: T.Tensor) -> T.Tensor:
+        ex = self.exchange
+        d = delta.broadcast(weight.data.shape)
+        if d.size * 4 >= ex.peer_bytes:
+            return ex.allreduce(d)
+        return d.do_cache()
+
+    def begin_step(self, backend=None):
+        pass
+
+    def state_of(self, weight):
+        return []
+
+    def state_arrays(self, weight):
+        return []
+
+    def step_many(self, pending):
+        import ctypes as C
+        from . import _native as N
+        ex = self.exchange
+        n = len(pending)
+        wbufs = [w.data._buffer() for w, _ in pending]
+        gbufs = [g._buffer() for _, g in pending]
+        weights = (C.c_void_p * n)(*[b.handle for b in wbufs])
+        grads = (C.c_void_p * n)(*[b.handle for b in gbufs])
+        counts = (C.c_size_t * n)(*[w.data.size for w, _ in pending])
+        flags = (C.c_int * n)(*[0 if id(b) in ex._over_nccl else 1 for b in gbufs])
+        ex._over_nccl.clear()
+        N.check(N.lib.dls_peer_sgd_step(ex.backend.ctx, weights, grads, counts, flags, n, self.learning_rate))
+
+
 class Trainer:
     """One mixin stack + its weights.  `optimizer_delta` = learning_rate * (all-reduced) delta (TW:155-161)."""
 
@@ -75,7 +132,13 @@ class Trainer:
         self.learning_rate = float(learning_rate)
         self.exchange = exchange
 
+        fused = None
+        if exchange is not None and optimizer is None and exchange.peer:
+            optimizer = fused = ExchangeSgd(exchange, self.learning_rate)
+
         def delta(weight, d):
+            if fused is not None:
+                return fused.gradient(weight, d)
             if self.exchange is not None:
                 d = self.exchange.allreduce(d.broadcast(weight.data.shape))
             return d if optimizer is not None else d * self.learning_rate

@@ -206,6 +206,9 @@ class Plugins:
             return
         for hook in self.before_flush:
             hook()
+        if hasattr(self.optimizer, "step_many"):                             # every update of the step in one launch
+            self.optimizer.step_many(list(pending))
+            del pending[:]
         while pending:
             weight, delta = pending.pop(0)
             if self.optimizer is not None:

@@ -192,6 +192,20 @@ int dls_allreduce_sum(dls_ctx *ctx, dls_buf *buf, size_t n_floats, dls_event *co
 /* one bucket: every buffer SUM-all-reduced in place by one grouped NCCL launch on the exchange stream, overlapping the
  * compute stream until a later launch touches one of the buffers (single-stream contexts; recordable) */
 int dls_allreduce_sum_many(dls_ctx *ctx, dls_buf *const *bufs, const size_t *n_floats, int n_bufs);
+/* The end of a data-parallel step as ONE kernel over NVLink peer memory (csrc/peer.cu).  dls_peer_init (collective, after
+ * dls_comm_init, ranks on one node) allocates this rank's peer-visible staging area of `staging_floats` x 2 and maps
+ * every peer's (cudaIpc handles all-gathered over the communicator).  dls_peer_sgd_step then does, in one launch:
+ *   for every i with exchange[i] != 0: grads[i] = sum over the ranks, added in rank order (bit-identical on every rank);
+ *   weights[i] = weights[i] - learning_rate * grads[i], in place (TW:64's `data - delta` with the optimizer hook of
+ *   TW:155-161 folded in); segments with exchange[i] == 0 are updated from their local (already reduced) gradient.
+ * weights == NULL: the sums are written back into grads[i] instead (all-reduce only, for stateful optimizers).
+ * Without any exchanged segment it is a multi-tensor SGD and needs neither communicator nor dls_peer_init.
+ * In place, so only valid at the end of the step; recordable.  Every rank must pass the same sizes in the same order.
+ * A peer that does not arrive within 20 s makes the next dls_ctx_sync / dls_buf_read return DLS_ERR_COMM. */
+int dls_peer_init(dls_ctx *ctx, size_t staging_floats);
+int dls_peer_ready(dls_ctx *ctx);                                    /* 1 after a successful dls_peer_init */
+int dls_peer_sgd_step(dls_ctx *ctx, dls_buf *const *weights, dls_buf *const *grads, const size_t *n_floats,
+                      const int *exchange, int n, float learning_rate);
 int dls_comm_destroy(dls_ctx *ctx);
 
 /* ---- captured steps (new functionality).  The reference dispatches every tensor materialisation separately:

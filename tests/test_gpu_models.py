@@ -158,6 +158,10 @@ def test_data_parallel_step_equals_the_full_batch_step(env):
     results = sorted([out_q.get(timeout=300) for _ in procs], key=lambda r: r[0])
     for p in procs:
         p.join(timeout=60)
+        if p.is_alive():
+            p.kill()
+            p.join(timeout=10)
+            pytest.fail("a rank process did not exit after delivering its result")
     (_, loss0, before, after0, x, t), (_, loss1, _, after1, _, _) = results
     want_loss, want, _ = MO.mlp_step(before, x, t, LR)
     assert abs((loss0 + loss1) - want_loss) <= 1e-5 * abs(want_loss)
