@@ -119,6 +119,7 @@ struct dls_ctx {
   int capture_pool = 0;                       // arena id while a capture is open, else 0
   int next_pool = 1;
   std::map<int, dls::GraphPool> pools;
+  std::vector<dls_graph *> graphs;            // captured steps still alive (their CUDA objects go with the context)
 
   // data-parallel exchange: collectives run on their own stream, forked from / joined to the compute stream with
   // events, so that an all-reduce overlaps the backward kernels launched after it (comm.cpp)
@@ -143,6 +144,9 @@ int join_all_exchanges(dls_ctx *ctx, int stream);
 int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_event *const *deps, int n_deps);
 int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_written, dls_buf *const *read, int n_read,
                   dls_event **done);
+
+// graph.cu
+void destroy_graphs(dls_ctx *ctx);
 
 // peer.cu
 void peer_destroy(dls_ctx *ctx);

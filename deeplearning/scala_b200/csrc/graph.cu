@@ -22,6 +22,24 @@
 
 using namespace dls;
 
+namespace dls {
+
+// Context teardown: the CUDA side of every captured step still alive goes before the communicator does -- NCCL counts
+// the graphs that captured its kernels and ncclCommDestroy waits for them, so a step that outlives its context would
+// otherwise block the teardown forever.  The handles stay valid for dls_graph_release, which then only frees the shell.
+void destroy_graphs(dls_ctx *ctx) {
+  for (dls_graph *g : ctx->graphs) {
+    if (g->exec) cudaGraphExecDestroy(g->exec);
+    if (g->graph) cudaGraphDestroy(g->graph);
+    g->exec = nullptr;
+    g->graph = nullptr;
+    g->ctx = nullptr;
+  }
+  ctx->graphs.clear();
+}
+
+}  // namespace dls
+
 extern "C" {
 
 int dls_graph_begin(dls_ctx *ctx) {
@@ -82,6 +100,7 @@ int dls_graph_end(dls_ctx *ctx, dls_graph **out) {
     cudaGraphNodeType t;
     if (cudaGraphNodeGetType(nodes[i], &t) == cudaSuccess && t == cudaGraphNodeTypeKernel) g->kernel_nodes++;
   }
+  ctx->graphs.push_back(g);
   *out = g;
   return DLS_OK;
 }
@@ -101,7 +120,7 @@ int dls_graph_abort(dls_ctx *ctx) {
 }
 
 int dls_graph_launch(dls_graph *g) {
-  DLS_CHECK(g && g->exec, DLS_ERR_INVALID, "dls_graph_launch: graph is NULL");
+  DLS_CHECK(g && g->exec && g->ctx, DLS_ERR_INVALID, "dls_graph_launch: graph is NULL, or its context has been destroyed");
   dls_ctx *ctx = g->ctx;
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_graph_launch: a capture is open on this context");
@@ -112,7 +131,7 @@ int dls_graph_launch(dls_graph *g) {
 }
 
 int dls_graph_info(const dls_graph *g, uint64_t *kernel_nodes, uint64_t *nodes, uint64_t *arena_bytes) {
-  DLS_CHECK(g, DLS_ERR_INVALID, "dls_graph_info: graph is NULL");
+  DLS_CHECK(g && g->ctx, DLS_ERR_INVALID, "dls_graph_info: graph is NULL, or its context has been destroyed");
   std::lock_guard<std::recursive_mutex> lk(g->ctx->mu);
   if (kernel_nodes) *kernel_nodes = g->kernel_nodes;
   if (nodes) *nodes = g->nodes;
@@ -131,13 +150,18 @@ void dls_graph_release(dls_graph *g) {
   if (!g) return;
   if (g->rc.fetch_sub(1, std::memory_order_acq_rel) != 1) return;
   dls_ctx *ctx = g->ctx;
-  {
+  if (ctx) {   // else the context went first and took the CUDA objects with it (destroy_graphs)
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->streams[0]);   // a replay may still be running out of the arena
     if (g->exec) cudaGraphExecDestroy(g->exec);
     if (g->graph) cudaGraphDestroy(g->graph);
     drop_pool(ctx, g->pool);
+    for (size_t i = 0; i < ctx->graphs.size(); ++i)
+      if (ctx->graphs[i] == g) {
+        ctx->graphs.erase(ctx->graphs.begin() + i);
+        break;
+      }
   }
   delete g;
 }

@@ -24,7 +24,6 @@
 // The segment is one cudaMalloc per rank, exported with cudaIpcGetMemHandle; the 64-byte handles are all-gathered over
 // the NCCL communicator the context already has (comm.cpp), so no extra rendezvous channel is needed.
 #include <string.h>
-#include <unistd.h>
 
 #include "common.h"
 
@@ -67,10 +66,8 @@ struct PeerState {
 
 namespace {
 
-// head of the segment: the arrival flags [world][kPeerGrid], then one "departed" word per rank (teardown, peer_destroy)
-constexpr size_t kDepartOffset = 4096;
-constexpr size_t kFlagBytes = 8192;
-static_assert(kPeerMaxWorld * kPeerGrid * 4 <= kDepartOffset, "flag array does not fit its page");
+constexpr size_t kFlagBytes = 4096;   // head of the segment: the arrival flags [world][kPeerGrid]
+static_assert(kPeerMaxWorld * kPeerGrid * 4 <= kFlagBytes, "flag array does not fit its page");
 constexpr unsigned long long kPeerTimeoutNs = 20ull * 1000 * 1000 * 1000;
 
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
@@ -226,32 +223,22 @@ __global__ void __launch_bounds__(kPeerBlock) peer_step_kernel(const __grid_cons
 
 int comm_allgather_bytes(dls_ctx *ctx, const void *mine, void *all_host, size_t bytes);   // comm.cpp
 
-// Teardown order matters: an exporter must not free a segment that an importer still has open (undefined behaviour per
-// the cudaIpc contract), and ranks leave at different times.  Every rank therefore marks its departure in the owner's
-// segment before it closes the mapping, and an owner frees its segment only once every importer has left; if one has
-// not within two seconds (it crashed, or it is simply still running) the segment is left to process teardown.
+// Teardown: the cudaIpc contract makes it undefined behaviour for an exporter to free a segment that an importer still
+// has open, and ranks leave at different times with no channel left to agree on an order (the communicator may already
+// be gone on the other side).  So a rank closes its imports -- always legal -- and does NOT free the segment it exported:
+// the driver reclaims it when the process exits, which is also what happens to every mapping after a crash.  The cost
+// is one staging area (16 MB by default) per dls_peer_init for the life of the process.
 void peer_destroy(dls_ctx *ctx) {
   PeerState *P = ctx->peer;
   if (!P) return;
   cudaDeviceSynchronize();
-  const uint32_t one = 1;
+  bool imported = false;
   for (int r = 0; r < P->world; ++r) {
     if (r == P->rank || !P->peer_base[r]) continue;
-    cudaMemcpy(static_cast<char *>(P->peer_base[r]) + kDepartOffset + 4 * P->rank, &one, 4, cudaMemcpyHostToDevice);
-    cudaDeviceSynchronize();
+    imported = true;
     cudaIpcCloseMemHandle(P->peer_base[r]);
   }
-  if (P->segment) {
-    bool all_left = false;
-    for (int tries = 0; tries < 2000 && !all_left; ++tries) {
-      uint32_t left[kPeerMaxWorld] = {};
-      if (cudaMemcpy(left, static_cast<char *>(P->segment) + kDepartOffset, 4 * P->world, cudaMemcpyDeviceToHost) != cudaSuccess) break;
-      all_left = true;
-      for (int r = 0; r < P->world; ++r) all_left &= r == P->rank || left[r] == 1;
-      if (!all_left) usleep(1000);
-    }
-    if (all_left) cudaFree(P->segment);
-  }
+  if (P->segment && !imported && P->world == 1) cudaFree(P->segment);
   cudaGetLastError();
   if (P->epochs) cudaFree(P->epochs);
   if (P->error_host) cudaFreeHost(P->error_host);

@@ -295,8 +295,9 @@ void dls_ctx_destroy(dls_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
-  dls_comm_destroy(ctx);
   dls_graph_abort(ctx);
+  destroy_graphs(ctx);
+  dls_comm_destroy(ctx);
   dls_ctx_trim(ctx);
   for (auto &kv : ctx->pools)
     for (auto &fb : kv.second.free_blocks) cudaFree(fb.second.ptr);

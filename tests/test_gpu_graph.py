@@ -135,3 +135,22 @@ def test_compiled_training_step_is_bit_identical_to_eager_steps(env, kind, mode)
     for g, w in zip(got_params, want_params):
         assert g.shape == w.shape and (bits(g) == bits(w)).all()
     assert len({float(v) for v in got_losses}) > 1                       # the weights really moved between replays
+
+
+def test_a_step_that_outlives_its_backend_is_harmless(env):
+    """The context takes the CUDA side of live recordings with it (NCCL would otherwise wait for them forever in
+    ncclCommDestroy); the handle stays valid for an error return and for its release."""
+    B, _, _ = env
+    from deeplearning.scala_b200 import _native as N
+    be = B.Backend()
+    a = be.tensor(rnd(1, 64, 64)).do_cache()
+    with be.capture() as step:
+        y = (a * 2.0).do_cache()
+    step.launch()
+    assert np.isfinite(y.flat_array()).all()
+    handle, step.handle = step.handle, None
+    del a, y
+    be.close()
+    assert N.lib.dls_graph_launch(handle) != 0
+    assert "destroyed" in N.last_error()
+    N.lib.dls_graph_release(handle)

@@ -59,7 +59,7 @@ def test_multi_tensor_sgd_on_one_gpu_is_bit_exact():
 
 def _setup(rank, world, uid_queue, staging):
     import faulthandler
-    faulthandler.dump_traceback_later(240, exit=True)                   # a rank that hangs says where, then goes away
+    faulthandler.dump_traceback_later(120, exit=True)                   # a rank that hangs says where (stderr), then exits 1
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     import deeplearning.scala_b200.tensors as B
     import deeplearning.scala_b200.harness as H
@@ -144,12 +144,13 @@ def spawn(target, *args):
     results = sorted([out_q.get(timeout=300) for _ in procs], key=lambda r: r[0])
     stuck = []
     for p in procs:
-        p.join(timeout=60)
+        p.join(timeout=150)
         if p.is_alive():                                                # never leave a child behind: pytest would wait for it at exit
             stuck.append(p.pid)
             p.kill()
             p.join(timeout=10)
     assert not stuck, "rank process(es) %r did not exit after delivering their results" % stuck
+    assert [p.exitcode for p in procs] == [0, 0], "a rank did not shut down cleanly (see its traceback on stderr)"
     for r in results:
         assert not isinstance(r[1], str), "rank %d failed: %s" % (r[0], r[1])
     return results
