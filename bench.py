@@ -384,7 +384,9 @@ def make_exchange(be, rank, world, dist):
     if rank == 0:
         uid = torch.tensor(list(Exchange.unique_id()), dtype=torch.uint8, device="cuda")
     dist.broadcast(uid, 0)
-    return Exchange(be, rank, world, bytes(uid.cpu().tolist()))
+    exchange = Exchange(be, rank, world, bytes(uid.cpu().tolist()))
+    exchange.verify()                                          # known-answer sum over every rank's peer segment (untimed)
+    return exchange
 
 
 def train_once(workload, args, rank, world, local, dist, steps, warmup, e2e_steps):

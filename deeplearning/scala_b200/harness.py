@@ -43,6 +43,23 @@ class Exchange:
             else:
                 sys.stderr.write("dls exchange: peer-memory path unavailable (%s); NCCL carries every gradient\n" % N.last_error())
 
+    def verify(self, n: int = 300001) -> None:
+        """Known-answer check of the peer path (run once after construction by the bench and the tests): rank r
+        contributes (i % 251) * (r + 1), every rank must read back (i % 251) * W (W + 1) / 2 -- exact in fp32 -- so a
+        segment that is not mapped, or a rank that is left out of the sum, fails loudly before any training step."""
+        if not self.peer:
+            return
+        C, N, be = self._C, self._N, self.backend
+        base = (np.arange(n) % 251).astype(np.float32)
+        buf = be.upload(base * np.float32(self.rank + 1))
+        handles, counts, flags = (C.c_void_p * 1)(buf.handle), (C.c_size_t * 1)(n), (C.c_int * 1)(1)
+        N.check(N.lib.dls_peer_sgd_step(be.ctx, None, handles, counts, flags, 1, 0.0))
+        got = be.download(buf, n)
+        want = base * np.float32(self.world_size * (self.world_size + 1) // 2)
+        if not (got == want).all():
+            raise RuntimeError("peer exchange self-test failed on rank %d: %d of %d sums are wrong"
+                               % (self.rank, int((got != want).sum()), n))
+
     @staticmethod
     def unique_id() -> bytes:
         import ctypes as C

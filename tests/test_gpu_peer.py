@@ -74,7 +74,9 @@ def _setup(rank, world, uid_queue, staging):
         uid = uid_queue.get(timeout=120)
     if staging is not None:
         H.Exchange.peer_staging_floats = staging
-    return B, H, N, be, H.Exchange(be, rank, world, uid)
+    ex = H.Exchange(be, rank, world, uid)
+    ex.verify()
+    return B, H, N, be, ex
 
 
 def _abi_rank(rank, world, uid_queue, out_queue):
