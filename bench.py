@@ -200,6 +200,7 @@ def main():
                     help="c2 (default) = BASELINE configs[1]; c1/c3/c4/c5 = the training configs (samples/s)")
     ap.add_argument("--gemm-mode", default="bf16", choices=["fp32", "tf32", "bf16"], help="contraction precision of the training legs")
     ap.add_argument("--no-train", action="store_true", help="skip the short training legs appended to the C2 line")
+    ap.add_argument("--strong", action="store_true", help="c5 only: strong scaling, global batch 2048 sharded over the ranks")
     ap.add_argument("--eager", action="store_true", help="training legs: time only the eager path (no captured step)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -285,6 +286,23 @@ def main():
     be.synchronize()
     ms_fused = B.elapsed_ms(k0, k1) / args.steps
     del y, s
+    # SURVEY 8(d) also asks for the per-COLUMN broadcast of c (`c.reshape([1, COLS])`: one value per column, repeated down
+    # the rows).  A side measurement: it must never cost the headline line, so any failure is recorded instead of raised.
+    variants = {}
+    try:
+        c_col = (be.random([COLS], seed=4 + 16 * rank) * 4.0 - 2.0).do_cache().reshape([1, COLS])
+        y = be.tanh(a * b + c_col).do_cache()
+        be.synchronize()
+        k0 = be.record_event()
+        for _ in range(args.steps):
+            y = be.tanh(a * b + c_col).do_cache()
+        k1 = be.record_event()
+        be.synchronize()
+        ms_col = B.elapsed_ms(k0, k1) / args.steps
+        variants["c2a_column_broadcast"] = {"ms": ms_col, "gbs": n * BYTES_MAP / (ms_col / 1e3) / 1e9}
+        del y, c_col
+    except Exception as exc:                                  # noqa: BLE001
+        variants["c2a_column_broadcast"] = {"error": repr(exc)}
 
     # ---- e2e: host inputs in pinned memory, H2D + compute + D2H of the sum inside the timed region -------------------
     def pinned(count):
@@ -349,6 +367,10 @@ def main():
                                                                       "frac": n * 8 / (ms_fused / 1e3) / 1e9 / peak}},
         "checksum": {"sum": check_sum, "e2e_sum": e2e_sum},
     }
+    for name, v in variants.items():
+        if "gbs" in v:
+            v["frac"] = v["gbs"] / peak
+        out["kernels"][name] = v
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sample_rows = 1024
         cpu_step, threads = cpu_step_runner(sample_rows)
@@ -495,6 +517,9 @@ def main_train(args, rank, world, local):
     workload = args.workload
     if workload == "c3" and world > 1:
         workload = "c5"
+    if args.strong and workload == "c5":
+        import bench_train
+        bench_train.C5_GLOBAL_BATCH = 2048
     sampler = ClockSampler(local)
     time.sleep(0.25)
     wall0 = time.time()
@@ -510,7 +535,8 @@ def main_train(args, rank, world, local):
         pass
     tensor_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
     out = {"metric": "train samples/sec", "value": r["samples_per_s"], "unit": "samples/s", "n_gpus": world, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+           "scaling": "strong" if args.strong and workload == "c5" else "weak", "vs_baseline": None,
            "dtype": {"fp32": "f32", "tf32": "tf32 (fp32 accumulate)", "bf16": "bf16 (fp32 accumulate)"}[args.gemm_mode],
            "data": "synthetic",
            "config": {"workload": r["workload"], "batch_per_gpu": r["batch_per_gpu"], "parameters": r["parameters"],

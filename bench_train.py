@@ -20,6 +20,11 @@ def pinned_like(N, array):
     return p, view
 
 
+# `bench.py --workload c5 --strong`: SURVEY 8(d)'s strong-scaling variant -- a fixed global batch sharded over the ranks
+# (None = weak scaling, 256 samples per GPU)
+C5_GLOBAL_BATCH = None
+
+
 def build(workload, be, exchange=None, rank=0, world=1, gemm_mode=None):
     """-> (model, x_host, target_host or None, per-rank batch, flop per step per rank, description)"""
     import deeplearning.scala_b200.harness as H
@@ -40,6 +45,10 @@ def build(workload, be, exchange=None, rank=0, world=1, gemm_mode=None):
         desc = "C4: wide MLP 4 x (4096x4096) tanh, batch 8192, loss = sum(out), 11 GEMMs of 8192x4096x4096 per step"
     elif workload in ("c3", "c5"):
         batch = 256
+        if workload == "c5" and C5_GLOBAL_BATCH is not None:
+            if C5_GLOBAL_BATCH % world:
+                raise ValueError("global batch %d is not divisible by %d ranks" % (C5_GLOBAL_BATCH, world))
+            batch = C5_GLOBAL_BATCH // world
         model = H.Cnn(image=32, channels=(3, 32, 64, 128), hidden=256, classes=10, backend=be, learning_rate=1e-3 / world, exchange=exchange)
         x = rng.rand(batch, 32, 32, 3).astype(np.float32)
         t = H.one_hot(rng.randint(0, 10, size=batch), 10, feature_major=False)
@@ -47,9 +56,9 @@ def build(workload, be, exchange=None, rank=0, world=1, gemm_mode=None):
         fwd = sum(2.0 * batch * hw * 9 * ci * co for hw, ci, co in conv) + 2.0 * batch * (8192 * 256 + 256 * 10)
         flop = 3.0 * fwd - 2.0 * batch * 32 * 32 * 27 * 32
         desc = ("C3: CNN 3 conv3x3 (3-32-64-128, ReLU, 2x nearest down-sampling) via im2col + 2 FC (8192-256-10), "
-                "batch 256 NHWC 32x32x3 per GPU, squared error, SGD")
+                "batch %d NHWC 32x32x3 per GPU, squared error, SGD" % batch)
         if workload == "c5":
-            desc = "C5: " + desc[4:] + "; data parallel, weak scaling, SUM all-reduce of every weight gradient (NCCL + NVLink peer memory)"
+            desc = "C5: " + desc[4:] + "; data parallel, " + ("weak" if C5_GLOBAL_BATCH is None else "strong") + " scaling, SUM all-reduce of every weight gradient (NCCL + NVLink peer memory)"
     else:
         raise ValueError(workload)
     return model, x, t, batch, flop, desc
