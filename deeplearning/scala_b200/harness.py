@@ -32,6 +32,7 @@ class Exchange:
         os.environ.setdefault("NCCL_MAX_NCHANNELS", "4")
         N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
         self._pending, self._pending_bytes = [], 0
+        self._held = []                         # small gradients waiting for the one-launch peer sum at `flush`
         self._over_nccl = set()                 # ids of the gradient buffers this step sent through NCCL
         # gradients below `peer_bytes` skip NCCL: they are summed and applied by the one-launch end-of-step kernel over
         # NVLink peer memory (csrc/peer.cu).  Needs cudaIpc between the ranks (one node); otherwise NCCL carries everything.
@@ -74,28 +75,51 @@ class Exchange:
     # wasteful, so only for what is small); DLS_PEER_BYTES=0 turns the path off
     peer_bytes = int(os.environ.get("DLS_PEER_BYTES", 1 << 20))
     peer_staging_floats = 1 << 21
+    # `reduce` (the route of stateful optimizers) only uses the peer sum when asked to: that combination has not run on
+    # hardware yet (the kernel mode it uses has: tests/test_gpu_peer.py::test_peer_exchange_abi_on_two_gpus)
+    peer_reduce = os.environ.get("DLS_PEER_REDUCE", "0") == "1"
 
     def allreduce(self, tensor: T.Tensor) -> T.Tensor:
         """Materialise the local partial gradient and queue it; the bucket goes out once `bucket_bytes` are pending or
         at `flush` (end of the step).  Small gradients (biases, early convolutions) then share one NCCL launch instead
         of paying its latency each, and the big ones leave as soon as they exist and overlap the rest of backward."""
         cached = tensor.do_cache()
-        self._over_nccl.add(id(cached._buffer()))
         self._pending.append(cached)
         self._pending_bytes += cached.size * 4
         if self._pending_bytes >= self.bucket_bytes:
-            self.flush()
+            self._flush_bucket()
         return cached
 
-    def flush(self):
-        pending, self._pending, self._pending_bytes = self._pending, [], 0
-        if not pending:
-            return
+    def reduce(self, tensor: T.Tensor) -> T.Tensor:
+        """SUM over the ranks, by whichever route fits the size: NCCL now (`allreduce`) for `peer_bytes` and more, else
+        materialise and hold for ONE peer-memory launch at `flush` (dls_peer_sgd_step without weights: the sums are
+        written back into the gradient buffers, which a stateful optimizer then consumes)."""
+        if not (self.peer and self.peer_reduce) or tensor.size * 4 >= self.peer_bytes:
+            return self.allreduce(tensor)
+        cached = tensor.do_cache()
+        self._held.append(cached)
+        return cached
+
+    def _flush_bucket(self):
         C, N = self._C, self._N
-        bufs = [t._buffer() for t in pending]
-        handles = (C.c_void_p * len(bufs))(*[b.handle for b in bufs])
-        counts = (C.c_size_t * len(bufs))(*[t.size for t in pending])
-        N.check(N.lib.dls_allreduce_sum_many(self.backend.ctx, handles, counts, len(bufs)))
+        pending, self._pending, self._pending_bytes = self._pending, [], 0
+        if pending:
+            bufs = [t._buffer() for t in pending]
+            handles = (C.c_void_p * len(bufs))(*[b.handle for b in bufs])
+            counts = (C.c_size_t * len(bufs))(*[t.size for t in pending])
+            N.check(N.lib.dls_allreduce_sum_many(self.backend.ctx, handles, counts, len(bufs)))
+
+    def flush(self):
+        """End of the step: the leftover NCCL bucket goes out first (asynchronously, on the exchange stream), then the
+        held small gradients are summed by one peer-memory launch on the compute stream.  Same order on every rank."""
+        self._flush_bucket()
+        C, N = self._C, self._N
+        held, self._held = self._held, []
+        if held:
+            handles = (C.c_void_p * len(held))(*[t._buffer().handle for t in held])
+            counts = (C.c_size_t * len(held))(*[t.size for t in held])
+            flags = (C.c_int * len(held))(*([1] * len(held)))
+            N.check(N.lib.dls_peer_sgd_step(self.backend.ctx, None, handles, counts, flags, len(held), 0.0))
 
 
 class ExchangeSgd:
@@ -112,7 +136,9 @@ class ExchangeSgd:
         ex = self.exchange
         d = delta.broadcast(weight.data.shape)
         if d.size * 4 >= ex.peer_bytes:
-            return ex.allreduce(d)
+            cached = ex.allreduce(d)
+            ex._over_nccl.add(id(cached._buffer()))
+            return cached
         return d.do_cache()
 
     def begin_step(self, backend=None):
@@ -157,7 +183,7 @@ class Trainer:
             if fused is not None:
                 return fused.gradient(weight, d)
             if self.exchange is not None:
-                d = self.exchange.allreduce(d.broadcast(weight.data.shape))
+                d = self.exchange.reduce(d.broadcast(weight.data.shape))
             return d if optimizer is not None else d * self.learning_rate
         self.P = Plugins(cumulative=False, optimizer_delta=delta, backend=self.backend, defer_updates=exchange is not None,
                          optimizer=optimizer)

@@ -45,7 +45,6 @@ class FakeExchange:
 
     def allreduce(self, tensor):
         cached = tensor.do_cache()
-        self._over_nccl.add(id(cached._buffer()))
         self.sent.append(cached)
         return cached
 
@@ -105,3 +104,37 @@ def test_plugins_hand_all_deferred_updates_to_step_many_at_once():
     assert seen == [[("w0", "g0"), ("w1", "g1")]] and P.deferred_updates == []
     P.flush_updates()                                                          # nothing pending: no hooks, no launch
     assert order == ["exchange.flush"] and len(seen) == 1
+
+
+def test_reduce_routes_by_size_and_flush_issues_nccl_before_the_peer_launch(H):
+    """The route stateful optimizers take: `Exchange.reduce` per gradient, `Exchange.flush` at the end of the step."""
+    log = []
+
+    def many(ctx, handles, counts, n):
+        log.append(("nccl", [handles[i] for i in range(n)], [counts[i] for i in range(n)]))
+        return 0
+
+    def peer(ctx, weights, grads, counts, flags, n, lr):
+        log.append(("peer", weights, [grads[i] for i in range(n)], [counts[i] for i in range(n)], [flags[i] for i in range(n)], lr))
+        return 0
+    ex = object.__new__(H.Exchange)                                            # no communicator: only the routing is under test
+    ex.backend = SimpleNamespace(ctx=C.c_void_p(1))
+    ex._C, ex._N = C, SimpleNamespace(lib=SimpleNamespace(dls_allreduce_sum_many=many, dls_peer_sgd_step=peer), check=lambda rc: None)
+    ex._pending, ex._pending_bytes, ex._held, ex._over_nccl = [], 0, [], set()
+    ex.peer, ex.peer_reduce, ex.peer_bytes, ex.bucket_bytes = True, True, 1 << 20, 1 << 20
+    small0, big, small1 = FakeTensor((10,), 1), FakeTensor((8192, 256), 2), FakeTensor((3, 3, 64, 128), 3)
+    assert ex.reduce(small0) is small0 and log == []                           # held, nothing launched
+    assert ex.reduce(big) is big
+    assert log == [("nccl", [2], [8192 * 256])]                                # a full bucket leaves at once ...
+    assert ex.reduce(small1) is small1 and len(log) == 1                       # ... without dragging the held ones along
+    ex.flush()
+    assert log[1:] == [("peer", None, [1, 3], [10, 3 * 3 * 64 * 128], [1, 1], 0.0)]
+    ex.flush()
+    assert len(log) == 2                                                       # nothing pending
+    # without the peer path everything is bucketed for NCCL, small gradients share one launch at flush
+    ex.peer = False
+    del log[:]
+    ex.reduce(small0), ex.reduce(small1)
+    assert log == []
+    ex.flush()
+    assert log == [("nccl", [1, 3], [10, 3 * 3 * 64 * 128])]

@@ -106,12 +106,17 @@ def _abi_rank(rank, world, uid_queue, out_queue):
         raise
 
 
-def _model_rank(rank, world, uid_queue, out_queue, peer_bytes, compiled):
+def _model_rank(rank, world, uid_queue, out_queue, peer_bytes, compiled, optimizer=None):
     try:
         os.environ["DLS_PEER_BYTES"] = str(peer_bytes)
+        os.environ["DLS_PEER_REDUCE"] = "1"
         B, H, N, be, ex = _setup(rank, world, uid_queue, None)
         assert ex.peer == (peer_bytes > 0)
-        model = H.Mlp((24, 16, 6), bias=True, backend=be, learning_rate=0.05, exchange=ex)
+        opt = None
+        if optimizer == "adam":
+            import deeplearning.scala_b200.optimizers as Opt
+            opt = Opt.Adam(1e-2)
+        model = H.Mlp((24, 16, 6), bias=True, backend=be, learning_rate=0.05, exchange=ex, optimizer=opt)
         rng = np.random.RandomState(5)
         x = rng.rand(24, 16).astype(F)
         t = H.one_hot(rng.randint(0, 6, size=16), 6, feature_major=True)
@@ -191,3 +196,17 @@ def test_peer_and_nccl_exchange_train_the_same_replicas(compiled):
         assert (bits(a) == bits(c)).all() and (bits(b) == bits(d)).all()  # paths
     if not compiled:
         assert launches_peer < launches_nccl
+
+
+@pytest.mark.parametrize("compiled", [False, True])
+def test_stateful_optimizer_takes_its_small_gradients_from_the_peer_sum(compiled):
+    """Adam under data parallelism: `Exchange.reduce` holds the small gradients for one peer-memory all-reduce launch
+    (dls_peer_sgd_step without weights) instead of NCCL; at two ranks both routes give the same bits."""
+    peer = spawn(_model_rank, 1 << 20, compiled, "adam")
+    nccl = spawn(_model_rank, 0, compiled, "adam")
+    (_, pl0, pp0, _), (_, pl1, pp1, _) = peer
+    (_, nl0, np0, _), (_, nl1, np1, _) = nccl
+    assert pl0 == nl0 and pl1 == nl1 and len(set(pl0)) > 1
+    for a, b, c, d in zip(pp0, pp1, np0, np1):
+        assert (bits(a) == bits(b)).all()
+        assert (bits(a) == bits(c)).all() and (bits(b) == bits(d)).all()
