@@ -129,13 +129,16 @@ class ExchangeSgd:
     weight in place, w = w - lr * sum (dls_peer_sgd_step).  Same arithmetic as `data - delta * learningRate`."""
     t = 0
 
-    def __init__(self, exchange: "Exchange", learning_rate: float):
+    def __init__(self, exchange: Optional["Exchange"], learning_rate: float, backend: Optional[T.Backend] = None):
+        """`exchange=None`: single GPU -- every gradient is materialised and one multi-tensor launch updates all weights in
+        place (no per-weight update launch, no swap, so a captured step needs no copy-back either)."""
         self.exchange, self.learning_rate = exchange, float(learning_rate)
+        self.backend = exchange.backend if exchange is not None else (backend or T.default_backend())
 
     def gradient(self, weight, delta: T.Tensor) -> T.Tensor:
         ex = self.exchange
         d = delta.broadcast(weight.data.shape)
-        if d.size * 4 >= ex.peer_bytes:
+        if ex is not None and d.size * 4 >= ex.peer_bytes:
             cached = ex.allreduce(d)
             ex._over_nccl.add(id(cached._buffer()))
             return cached
@@ -160,9 +163,11 @@ class ExchangeSgd:
         weights = (C.c_void_p * n)(*[b.handle for b in wbufs])
         grads = (C.c_void_p * n)(*[b.handle for b in gbufs])
         counts = (C.c_size_t * n)(*[w.data.size for w, _ in pending])
-        flags = (C.c_int * n)(*[0 if id(b) in ex._over_nccl else 1 for b in gbufs])
-        ex._over_nccl.clear()
-        N.check(N.lib.dls_peer_sgd_step(ex.backend.ctx, weights, grads, counts, flags, n, self.learning_rate))
+        flags = None
+        if ex is not None:
+            flags = (C.c_int * n)(*[0 if id(b) in ex._over_nccl else 1 for b in gbufs])
+            ex._over_nccl.clear()
+        N.check(N.lib.dls_peer_sgd_step(self.backend.ctx, weights, grads, counts, flags, n, self.learning_rate))
 
 
 class Trainer:
@@ -178,6 +183,9 @@ class Trainer:
         fused = None
         if exchange is not None and optimizer is None and exchange.peer:
             optimizer = fused = ExchangeSgd(exchange, self.learning_rate)
+        elif exchange is None and optimizer is None and os.environ.get("DLS_FUSED_SGD") == "1":
+            # opt-in until its first hardware run: the single-GPU step with all updates in one in-place launch
+            optimizer = fused = ExchangeSgd(None, self.learning_rate, self.backend)
 
         def delta(weight, d):
             if fused is not None:

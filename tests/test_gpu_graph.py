@@ -154,3 +154,45 @@ def test_a_step_that_outlives_its_backend_is_harmless(env):
     assert N.lib.dls_graph_launch(handle) != 0
     assert "destroyed" in N.last_error()
     N.lib.dls_graph_release(handle)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("DLS_TEST_UNVERIFIED") != "1",
+                    reason="opt-in path wired without hardware access; run with DLS_TEST_UNVERIFIED=1 first")
+@pytest.mark.parametrize("compiled", [False, True])
+def test_fused_single_gpu_update_equals_the_per_weight_swaps(env, monkeypatch, compiled):
+    """DLS_FUSED_SGD=1: every gradient materialised, ONE in-place multi-tensor launch (dls_peer_sgd_step without
+    exchange) instead of one `data - delta * lr` launch + swap (+ copy-back when captured) per weight.  Same arithmetic,
+    so the same bits; fewer launches."""
+    B, H, _ = env
+
+    def run(fused):
+        if fused:
+            monkeypatch.setenv("DLS_FUSED_SGD", "1")
+        else:
+            monkeypatch.delenv("DLS_FUSED_SGD", raising=False)
+        be = B.Backend(gemm_mode="fp32")
+        try:
+            model = H.Mlp((20, 16, 6), bias=True, last_activation="none", backend=be, learning_rate=1e-2)
+            rng = np.random.RandomState(3)
+            x = be.tensor(rng.rand(20, 12).astype(np.float32)).do_cache()
+            t = be.tensor(H.one_hot(rng.randint(0, 6, size=12), 6, feature_major=True)).do_cache()
+            if compiled:
+                step = model.compile(x, t)
+                launches0 = be.stats()["kernel_launches"]
+                losses = [step() for _ in range(4)]
+                per_step = (be.stats()["kernel_launches"] - launches0) / 4
+                del step
+            else:
+                model.step(x, t)
+                launches0 = be.stats()["kernel_launches"]
+                losses = [model.step(x, t) for _ in range(4)]
+                per_step = (be.stats()["kernel_launches"] - launches0) / 4
+            return losses, [p.copy() for p in model.parameters()], per_step
+        finally:
+            be.close()
+    want_l, want_p, want_n = run(False)
+    got_l, got_p, got_n = run(True)
+    assert got_l == want_l and len(set(got_l)) > 1
+    for g, w in zip(got_p, want_p):
+        assert (bits(g) == bits(w)).all()
+    assert got_n < want_n
