@@ -70,6 +70,8 @@ _SIG = {
     "dls_buf_device_ptr": (_P, [_P]),
     "dls_buf_read": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_size_t, _PP, C.c_int, _PP]),
     "dls_buf_write": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_size_t, _PP]),
+    "dls_buf_upload_async": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_size_t, _PP, C.c_int, _PP]),
+    "dls_stream_wait_event": (C.c_int, [_P, C.c_int, _P]),
     "dls_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.POINTER(C.c_float))]),
     "dls_host_free": (None, [_P]),
     "dls_event_retain": (None, [_P]),

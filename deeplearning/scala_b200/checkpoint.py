@@ -101,7 +101,8 @@ def snapshot(trainer) -> Dict[str, np.ndarray]:
             for k, s in enumerate(opt.state_arrays(w)):
                 arrays["w%d.s%d" % (i, k)] = s
     if opt is not None:
-        arrays["optimizer.t"] = np.array([opt.t], dtype=np.float32)
+        # two 16-bit halves: each is exact in fp32, so the count survives up to 2^32 steps (a single fp32 stops at 2^24)
+        arrays["optimizer.t"] = np.array([opt.t & 0xFFFF, (opt.t >> 16) & 0xFFFF], dtype=np.float32)
     return arrays
 
 
@@ -131,5 +132,6 @@ def restore(path: str, trainer) -> None:
     if opt is not None:
         if "optimizer.t" not in arrays:
             raise ValueError("checkpoint has no optimizer step count")
-        opt.t = int(arrays["optimizer.t"][0])
+        t = arrays["optimizer.t"].reshape(-1)
+        opt.t = int(t[0]) + (int(t[1]) << 16 if t.size > 1 else 0)      # one-element entries: files written before the split
     be.synchronize()

@@ -123,6 +123,7 @@ struct dls_ctx {
 
   // data-parallel exchange: collectives run on their own stream, forked from / joined to the compute stream with
   // events, so that an all-reduce overlaps the backward kernels launched after it (comm.cpp)
+  cudaStream_t copy_stream = nullptr;         // dls_buf_upload_async: host -> device copies that overlap the compute stream
   cudaStream_t comm_stream = nullptr;
   int exchange_sms = 0;                       // SMs a collective occupies (its channel count); one-CTA-per-SM kernels launched
                                               // while an exchange is in flight leave that many SMs to it
@@ -144,6 +145,8 @@ int join_all_exchanges(dls_ctx *ctx, int stream);
 int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_event *const *deps, int n_deps);
 int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_written, dls_buf *const *read, int n_read,
                   dls_event **done);
+int wait_streams(dls_ctx *ctx, int stream, uint32_t mask);   // multi-stream contexts: `stream` waits for the tail of every stream in `mask`
+int wait_readers(dls_ctx *ctx, int stream, dls_buf *buf);    // ... of every stream that touched `buf` (before an in-place write)
 
 // graph.cu
 void destroy_graphs(dls_ctx *ctx);

@@ -543,10 +543,12 @@ template <bool TF32, bool A_MN, bool B_MN>
 static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mc,
                           float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct, const SplitPlan &sp) {
   auto kern = gemm_tc_kernel<TF32, A_MN, B_MN>;
-  static bool configured = false;
-  if (!configured) {
+  // the attribute is per DEVICE (one process may hold a context on every GPU of the node), guarded by ctx->mu per context
+  static std::atomic<bool> configured[64];
+  const int dev = ctx->device & 63;
+  if (!configured[dev].load(std::memory_order_acquire)) {
     DLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    configured = true;
+    configured[dev].store(true, std::memory_order_release);
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * sp.splits;
   // one persistent CTA per SM; SMs hosting an in-flight collective (data-parallel exchange) are left to it

@@ -174,6 +174,7 @@ int dls_buf_copy(dls_ctx *ctx, dls_buf *dst, dls_buf *src, size_t n_floats) {
   const int stream = ctx->n_streams == 1 ? 0 : dst->last_stream;
   dls_buf *both[2] = {src, dst};
   int rc = wait_inputs(ctx, stream, both, 2, nullptr, 0);
+  if (!rc) rc = wait_readers(ctx, stream, dst);
   if (rc) return rc;
   if (n_floats && dst->ptr != src->ptr)
     DLS_CUDA(cudaMemcpyAsync(dst->ptr, src->ptr, n_floats * sizeof(float), cudaMemcpyDeviceToDevice, ctx->streams[stream]));

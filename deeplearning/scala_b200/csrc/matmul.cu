@@ -107,91 +107,6 @@ int launch_bias_act(dls_ctx *ctx, int stream, float *c, size_t m, size_t n, cons
   return DLS_OK;
 }
 
-// ---- skinny contraction: K <= 32 and N <= 32 with a long M (conv1's im2col product: M = 262 144, K = 27, N = 32) -------
-// Such a product is HBM bound by two orders of magnitude (864 FMA per 236 bytes), and the tensor-core kernel spends
-// it on per-tile latency (one k-block per 128-row tile: 40 us against a 7 us floor) plus a bf16 staging pass over A.
-// Here a CTA streams 256-row slabs of A through shared memory with coalesced loads (row stride padded to an odd number of
-// words, so the per-thread row reads are conflict free), every thread owns one output row with N accumulators in
-// registers, B (<= 4 KB) sits in shared memory and is read as a broadcast, and the row leaves with 16-byte stores.
-// fp32 FMA throughout: closer to the reference's fp32 chain than the bf16 / tf32 paths it replaces.
-// OPT-IN (DLS_SKINNY_GEMM=1): written and compiled in round 1, not yet run on hardware.
-template <int NP>
-__global__ void __launch_bounds__(256) skinny_gemm_kernel(const float *__restrict__ A, const float *__restrict__ B,
-                                                          float *__restrict__ C, long long M, int N, int K,
-                                                          const float *__restrict__ bias, int bias_mode, int act) {
-  extern __shared__ float sm[];
-  const int KP = K | 1;
-  float *sB = sm;                 // [K][NP], columns >= N are zero
-  float *sA = sm + 32 * NP;       // [256][KP]
-  const int tid = threadIdx.x;
-  for (int i = tid; i < K * NP; i += 256) {
-    const int kk = i / NP, nn = i - kk * NP;
-    sB[i] = nn < N ? B[(size_t)kk * N + nn] : 0.f;
-  }
-  for (long long row0 = (long long)blockIdx.x * 256; row0 < M; row0 += (long long)gridDim.x * 256) {
-    const int rows = (int)(M - row0 < 256 ? M - row0 : 256);
-    __syncthreads();              // the previous slab has been consumed (and sB is complete on the first trip)
-    const float *src = A + row0 * K;
-    for (int i = tid; i < rows * K; i += 256) {
-      const int r = i / K;
-      sA[r * KP + (i - r * K)] = src[i];
-    }
-    __syncthreads();
-    if (tid >= rows) continue;
-    float acc[NP];
-#pragma unroll
-    for (int n = 0; n < NP; ++n) acc[n] = 0.f;
-    const float *arow = sA + tid * KP;
-    for (int k = 0; k < K; ++k) {
-      const float a = arow[k];
-      const float *brow = sB + k * NP;
-#pragma unroll
-      for (int n = 0; n < NP; ++n) acc[n] = fmaf(a, brow[n], acc[n]);
-    }
-    const long long row = row0 + tid;
-    const float brow_bias = bias_mode == 1 ? __ldg(bias + row) : 0.f;
-#pragma unroll
-    for (int n = 0; n < NP; ++n) {
-      float x = acc[n];
-      if (bias_mode == 1) x = __fadd_rn(x, brow_bias);
-      else if (bias_mode == 2 && n < N) x = __fadd_rn(x, __ldg(bias + n));
-      if (act == 1) x = tanhf(x);
-      else if (act == 2) x = fmaxf(x, 0.f);
-      acc[n] = x;
-    }
-    float *dst = C + row * N;
-    if ((N & 3) == 0) {           // rows are 16-byte aligned: C comes from the allocator and N * 4 is a multiple of 16
-#pragma unroll
-      for (int n = 0; n < NP; n += 4)
-        if (n < N) *reinterpret_cast<float4 *>(dst + n) = make_float4(acc[n], acc[n + 1], acc[n + 2], acc[n + 3]);
-    } else {
-#pragma unroll
-      for (int n = 0; n < NP; ++n)
-        if (n < N) dst[n] = acc[n];
-    }
-  }
-}
-
-bool skinny_gemm_wanted(size_t m, size_t n, size_t k, bool ta, bool tb) {
-  const char *e = getenv("DLS_SKINNY_GEMM");
-  return e && e[0] == '1' && !ta && !tb && k >= 1 && k <= 32 && n >= 1 && n <= 32 && m >= 4096;
-}
-
-int launch_skinny_gemm(dls_ctx *ctx, int stream, const float *A, const float *B, float *C, size_t m, int n, int k,
-                       const float *bias, int bias_mode, int act) {
-  const int np = n <= 8 ? 8 : n <= 16 ? 16 : 32;
-  const size_t smem = (32 * np + 256 * (k | 1)) * sizeof(float);
-  const size_t slabs = (m + 255) / 256;
-  const int grid = (int)std::min<size_t>(slabs, (size_t)ctx->sm_count * 4);
-  cudaStream_t st = ctx->streams[stream];
-  if (np == 8) skinny_gemm_kernel<8><<<grid, 256, smem, st>>>(A, B, C, (long long)m, n, k, bias, bias_mode, act);
-  else if (np == 16) skinny_gemm_kernel<16><<<grid, 256, smem, st>>>(A, B, C, (long long)m, n, k, bias, bias_mode, act);
-  else skinny_gemm_kernel<32><<<grid, 256, smem, st>>>(A, B, C, (long long)m, n, k, bias, bias_mode, act);
-  DLS_CUDA(cudaGetLastError());
-  ctx->stats.kernel_launches++;
-  return DLS_OK;
-}
-
 }  // namespace dls
 
 using namespace dls;
@@ -237,6 +152,10 @@ int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long ro
     tag_r = tag_rows;
     tag_c = cols;
   } else {
+    // reused from another stream of the pool: wait for the staging kernel that produced the copy (and, being
+    // conservative, for everything else those streams have queued)
+    int rc = wait_streams(ctx, stream, sh.stream_mask);
+    if (rc) return rc;
     sh.stream_mask |= 1u << stream;
   }
   *ptr = sh.ptr;
@@ -264,8 +183,6 @@ int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_b
     if (!rc) rc = launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
     return rc;
   }
-  if (skinny_gemm_wanted(m, n, k, transpose_a, transpose_b))
-    return launch_skinny_gemm(ctx, stream, a->ptr, b->ptr, c->ptr, m, (int)n, (int)k, bias_ptr, bias_mode, activation);
   const void *pa, *pb;
   long long lda, ldb;
   bool a_mn, b_mn;

@@ -34,7 +34,10 @@ static int get_plan(dls_ctx *ctx, const uint8_t *tree, size_t len, std::shared_p
   cp->blob.assign(tree, tree + len);
   ctx->stats.plan_cache_misses++;
   const size_t cap = ctx->opts.plan_cache_capacity > 0 ? (size_t)ctx->opts.plan_cache_capacity : 4096;
-  if (ctx->plans.size() >= cap) {  // crude bound: drop everything (plans are cheap to rebuild, no compilation involved)
+  // crude bound: drop everything (plans are cheap to rebuild, no compilation involved).  Captured steps have the
+  // device tables of the plans they recorded baked into their kernel nodes, and a device-wide synchronise would
+  // invalidate an open capture: while a capture is open or a captured step is alive the cache is allowed to grow.
+  if (ctx->plans.size() >= cap && ctx->capture_pool == 0 && ctx->graphs.empty()) {
     cudaDeviceSynchronize();
     for (auto &kv : ctx->plans)
       if (kv.second->plan.d_tables) cudaFree(kv.second->plan.d_tables);
@@ -195,6 +198,7 @@ int dls_sgd_update(dls_ctx *ctx, dls_buf *weight, dls_buf *delta, size_t n_float
   const int stream = pick_stream(ctx);
   dls_buf *ins[2] = {weight, delta};
   int rc = wait_inputs(ctx, stream, ins, 2, deps, n_deps);
+  if (!rc) rc = wait_readers(ctx, stream, weight);
   if (rc) return rc;
   rc = launch_sgd(ctx, stream, weight->ptr, delta->ptr, n_floats, learning_rate);
   if (rc) return rc;
@@ -216,6 +220,9 @@ int dls_optimizer_step(dls_ctx *ctx, int kind, dls_buf *weight, dls_buf *state1,
   const int stream = pick_stream(ctx);
   dls_buf *ins[5] = {weight, state1, grad, hyper, state2};
   int rc = wait_inputs(ctx, stream, ins, state2 ? 5 : 4, nullptr, 0);
+  if (!rc) rc = wait_readers(ctx, stream, weight);
+  if (!rc) rc = wait_readers(ctx, stream, state1);
+  if (!rc) rc = wait_readers(ctx, stream, state2);
   if (rc) return rc;
   rc = launch_optimizer(ctx, stream, kind, weight->ptr, state1->ptr, state2 ? state2->ptr : nullptr, grad->ptr, n_floats, hyper->ptr);
   if (rc) return rc;

@@ -181,6 +181,30 @@ int wait_inputs(dls_ctx *ctx, int stream, dls_buf *const *bufs, int n_bufs, dls_
   return DLS_OK;
 }
 
+// Multi-stream contexts order work by the last WRITER's event only (`dls_buf::ready`).  The reference never writes a
+// buffer in place, so that is all it needs; the in-place entry points of this library (dls_sgd_update,
+// dls_optimizer_step, dls_buf_write, dls_buf_copy) must in addition wait for every stream that may still be READING the
+// buffer.  `stream_mask` records every pool stream that touched the block; the writer's stream waits for the current
+// tail of each of them (conservative: a marker event per stream, not per reader).
+int wait_streams(dls_ctx *ctx, int stream, uint32_t mask) {
+  if (ctx->n_streams <= 1) return DLS_OK;
+  for (int s = 0; s < ctx->n_streams; ++s) {
+    if (s == stream || !(mask & (1u << s))) continue;
+    cudaEvent_t ev;
+    DLS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    cudaError_t e = cudaEventRecord(ev, ctx->streams[s]);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->streams[stream], ev, 0);
+    cudaEventDestroy(ev);   // released by the runtime once the wait has been satisfied
+    if (e != cudaSuccess) return cuda_fail(e, "wait_streams", __FILE__, __LINE__);
+  }
+  return DLS_OK;
+}
+
+int wait_readers(dls_ctx *ctx, int stream, dls_buf *buf) {
+  if (!buf) return DLS_OK;
+  return wait_streams(ctx, stream, buf->block.stream_mask);
+}
+
 int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_written, dls_buf *const *read, int n_read,
                   dls_event **done) {
   cudaStream_t st = ctx->streams[stream];
@@ -273,6 +297,7 @@ int dls_ctx_sync(dls_ctx *ctx) {
   DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_ctx_sync: a capture is open on this context");
   DLS_CUDA(cudaSetDevice(ctx->device));
   if (ctx->comm_stream) DLS_CUDA(cudaStreamSynchronize(ctx->comm_stream));
+  if (ctx->copy_stream) DLS_CUDA(cudaStreamSynchronize(ctx->copy_stream));
   for (cudaStream_t s : ctx->streams) DLS_CUDA(cudaStreamSynchronize(s));
   return peer_check(ctx);
 }
@@ -305,6 +330,7 @@ void dls_ctx_destroy(dls_ctx *ctx) {
   for (auto &kv : ctx->plans)
     if (kv.second->plan.d_tables) cudaFree(kv.second->plan.d_tables);
   ctx->plans.clear();
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   for (int s = 0; s < ctx->n_streams; ++s) {
     cudaFree(ctx->red_partials[s]);
     cudaFree(ctx->red_counter[s]);
@@ -408,12 +434,51 @@ int dls_buf_write(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, s
   DLS_CUDA(cudaSetDevice(ctx->device));
   int stream = buf->last_stream;
   int rc = join_exchange(ctx, stream, buf);
+  if (!rc) rc = wait_readers(ctx, stream, buf);
   if (rc) return rc;
   if (n_floats) {
     DLS_CUDA(cudaMemcpyAsync(buf->ptr + offset, src, n_floats * sizeof(float), cudaMemcpyHostToDevice, ctx->streams[stream]));
     ctx->stats.h2d_bytes += n_floats * sizeof(float);
   }
   return finish_output(ctx, stream, &buf, 1, nullptr, 0, done);
+}
+
+int dls_buf_upload_async(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, size_t n_floats, dls_event *const *deps,
+                         int n_deps, dls_event **done) {
+  DLS_CHECK(ctx && buf && done && (src || n_floats == 0), DLS_ERR_INVALID, "dls_buf_upload_async: NULL argument");
+  DLS_CHECK(offset + n_floats <= buf->n, DLS_ERR_INVALID, "dls_buf_upload_async: range exceeds the buffer");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_buf_upload_async: host transfers cannot be recorded into a captured step");
+  DLS_CUDA(cudaSetDevice(ctx->device));
+  if (!ctx->copy_stream) DLS_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < n_deps; ++i)
+    if (deps && deps[i] && deps[i]->ev) DLS_CUDA(cudaStreamWaitEvent(ctx->copy_stream, deps[i]->ev, 0));
+  if (n_floats) {
+    DLS_CUDA(cudaMemcpyAsync(buf->ptr + offset, src, n_floats * sizeof(float), cudaMemcpyHostToDevice, ctx->copy_stream));
+    ctx->stats.h2d_bytes += n_floats * sizeof(float);
+  }
+  for (int k = 0; k < 2; ++k)   // the contents change: operand shadows are stale
+    if (buf->shadow[k].ptr) free_block(ctx, buf->shadow[k]);
+  dls_event *e = new dls_event();
+  e->ctx = ctx;
+  cudaError_t err = cudaEventCreate(&e->ev);
+  if (err == cudaSuccess) err = cudaEventRecord(e->ev, ctx->copy_stream);
+  if (err != cudaSuccess) {
+    delete e;
+    return cuda_fail(err, "cudaEventRecord(copy stream)", __FILE__, __LINE__);
+  }
+  *done = e;
+  return DLS_OK;
+}
+
+int dls_stream_wait_event(dls_ctx *ctx, int stream_index, dls_event *ev) {
+  DLS_CHECK(ctx && ev && ev->ev && stream_index >= 0 && stream_index < ctx->n_streams, DLS_ERR_INVALID,
+            "dls_stream_wait_event: bad argument");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_stream_wait_event: not inside a captured step");
+  DLS_CUDA(cudaSetDevice(ctx->device));
+  DLS_CUDA(cudaStreamWaitEvent(ctx->streams[stream_index], ev->ev, 0));
+  return DLS_OK;
 }
 
 int dls_host_alloc(size_t n_floats, float **out) {

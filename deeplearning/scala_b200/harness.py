@@ -75,9 +75,10 @@ class Exchange:
     # wasteful, so only for what is small); DLS_PEER_BYTES=0 turns the path off
     peer_bytes = int(os.environ.get("DLS_PEER_BYTES", 1 << 20))
     peer_staging_floats = 1 << 21
-    # `reduce` (the route of stateful optimizers) only uses the peer sum when asked to: that combination has not run on
-    # hardware yet (the kernel mode it uses has: tests/test_gpu_peer.py::test_peer_exchange_abi_on_two_gpus)
-    peer_reduce = os.environ.get("DLS_PEER_REDUCE", "0") == "1"
+    # `reduce` (the route of stateful optimizers) sends its small gradients through the peer sum as well
+    # (tests/test_gpu_peer.py::test_stateful_optimizer_takes_its_small_gradients_from_the_peer_sum); DLS_PEER_REDUCE=0
+    # keeps them on NCCL
+    peer_reduce = os.environ.get("DLS_PEER_REDUCE", "1") != "0"
 
     def allreduce(self, tensor: T.Tensor) -> T.Tensor:
         """Materialise the local partial gradient and queue it; the bucket goes out once `bucket_bytes` are pending or
@@ -183,8 +184,9 @@ class Trainer:
         fused = None
         if exchange is not None and optimizer is None and exchange.peer:
             optimizer = fused = ExchangeSgd(exchange, self.learning_rate)
-        elif exchange is None and optimizer is None and os.environ.get("DLS_FUSED_SGD") == "1":
-            # opt-in until its first hardware run: the single-GPU step with all updates in one in-place launch
+        elif exchange is None and optimizer is None and os.environ.get("DLS_FUSED_SGD", "1") != "0":
+            # the single-GPU step with all updates in ONE in-place launch (no per-weight `data - delta` launch, no swap,
+            # no copy-back in a captured step); DLS_FUSED_SGD=0 keeps the reference-literal per-weight swaps of TW:63-72
             optimizer = fused = ExchangeSgd(None, self.learning_rate, self.backend)
 
         def delta(weight, d):
@@ -258,6 +260,62 @@ class CompiledStep:
         if trainer.P.handled_exceptions:
             raise trainer.P.handled_exceptions.pop(0)
         self.graph, self._loss = graph, loss
+        self._pipe = None
+
+    # -- pipelined replays: the next batch travels while this step computes -------------------------------------------
+    def submit(self, x_host: np.ndarray, target_host: Optional[np.ndarray] = None) -> Optional[float]:
+        """One replay on a HOST batch, pipelined: the batch is uploaded on the context's copy stream into staging buffers
+        (overlapping the replay submitted before), copied device-to-device into the step's input buffers, the step is
+        replayed and its scalar loss is read back asynchronously.  Returns the loss of the PREVIOUS submitted step
+        (None for the first): the host only ever waits for a step that has a successor queued behind it, so PCIe,
+        the device and the host overlap.  `x_host` / `target_host` should be page-locked and must stay unchanged until
+        the next `submit` (or `drain`) returns.  Same arithmetic as `__call__`; `drain()` yields the last loss."""
+        import ctypes as C
+        from . import _native as N
+        be = self.backend
+        if self._pipe is None:
+            host = C.POINTER(C.c_float)()
+            N.check(N.lib.dls_host_alloc(2, C.byref(host)))
+            sx = be.fill(0.0, self.x.shape).do_cache()
+            stt = be.fill(0.0, self.target.shape).do_cache() if self.target is not None else None
+            self._pipe = {"x": sx, "t": stt, "free": None, "pending": None, "slot": 0, "host": host}
+        p = self._pipe
+        deps = [p["free"]] if p["free"] is not None else []
+        uploads = [be.upload_async(p["x"]._buffer(), x_host, deps)]
+        if target_host is not None:
+            uploads.append(be.upload_async(p["t"]._buffer(), target_host, deps))
+        for ev in uploads:
+            be.stream_wait(ev)
+        be.copy(self.x._buffer(), p["x"]._buffer(), self.x.size)
+        if target_host is not None:
+            be.copy(self.target._buffer(), p["t"]._buffer(), self.target.size)
+        p["free"] = be.record_event()                        # the staging buffers may be overwritten from here on
+        self.launch()
+        previous, slot = p["pending"], p["slot"]
+        p["slot"] ^= 1
+        done = be.read_async(self._loss._buffer(), C.cast(C.addressof(p["host"].contents) + 4 * slot, C.c_void_p), 1)
+        p["pending"] = (done, slot)
+        if previous is None:
+            return None
+        previous[0].wait()
+        return float(p["host"][previous[1]])
+
+    def drain(self) -> Optional[float]:
+        """Wait for the last submitted step and return its loss."""
+        p = self._pipe
+        if p is None or p["pending"] is None:
+            return None
+        done, slot = p["pending"]
+        p["pending"] = None
+        done.wait()
+        return float(p["host"][slot])
+
+    def __del__(self):
+        p, self._pipe = getattr(self, "_pipe", None), None
+        if p is not None and p.get("host"):
+            from . import _native as N
+            if N is not None:
+                N.lib.dls_host_free(p["host"])
 
     def _copy_back(self, homes):
         be = self.backend

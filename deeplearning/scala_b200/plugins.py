@@ -66,6 +66,24 @@ def broadcast_then_sum(tensor, shape):
     return sum_as(tensor, shape)
 
 
+def _may_read_weights(data, pending) -> bool:
+    """Does materialising the lazy tensor `data` later read a buffer that an in-place update in `pending` is about to
+    overwrite?  Leaves that are pinned buffers are compared by identity; a leaf whose buffer does not exist yet is of
+    unknown provenance and counts as a reader."""
+    if not pending or isinstance(data, T.CachedTensor):
+        return False
+    from .trees import serialize
+    live = {id(w.data._buf) for w, _ in pending if isinstance(w.data, T.CachedTensor)}
+    _, params = serialize([data.closure()], data.shape)
+    for p in params:
+        if isinstance(p, T.CachedTensor):
+            if id(p._buf) in live:
+                return True
+        elif not (isinstance(p, T.UploadTensor) and p._buf is not None):
+            return True
+    return False
+
+
 class Differentiable:
     plugins: "Plugins"
 
@@ -130,9 +148,14 @@ class TensorLayer(Differentiable):
         """TL:70-76: forward, backward with the scalar delta 1.0f (TL:55), yield the forward data."""
         def step(tape):
             tape.backward(Do.now(self.plugins.scalar(1.0)))
+            data = tape.data
+            if self.plugins.optimizer is not None and _may_read_weights(data, self.plugins.deferred_updates):
+                # an in-place rule is about to overwrite the weights a lazy forward expression still reads: pin the
+                # forward value first, so `train` yields the data of THIS step like the reference (TL:70-76)
+                data = data.do_cache()
             if not self.plugins.cumulative:                                  # cumulative layers flush on release: the
                 self.plugins.flush_updates()                                 # caller flushes after running the Do
-            return Do.now(tape.data)
+            return Do.now(data)
 
         def begin():
             self.plugins.begin_step()
@@ -209,6 +232,11 @@ class Plugins:
         if hasattr(self.optimizer, "step_many"):                             # every update of the step in one launch
             self.optimizer.step_many(list(pending))
             del pending[:]
+        elif self.optimizer is not None:
+            # in-place rules: every still-lazy delta is materialised BEFORE the first weight is overwritten -- a delta may
+            # read another weight's live buffer (`w1 * w2`: the gradient of w2 is d * w1.data), and the reference's
+            # swap (TW:63-72) leaves the tapes the pre-update values
+            pending[:] = [(w, d.broadcast(w.data.shape).do_cache()) for w, d in pending]
         while pending:
             weight, delta = pending.pop(0)
             if self.optimizer is not None:

@@ -177,6 +177,27 @@ class Backend:
         flat = np.ascontiguousarray(flat, dtype=F32).reshape(-1)
         N.check(N.lib.dls_buf_write(self.ctx, buf.handle, offset, flat.ctypes.data_as(C.c_void_p), flat.size, None))
 
+    def upload_async(self, buf: DeviceBuffer, flat: np.ndarray, deps: Sequence[Event] = (), offset: int = 0) -> Event:
+        """Host -> device on the context's COPY stream (`dls_buf_upload_async`): overlaps whatever the compute stream
+        runs.  `flat` should live in page-locked memory (`dls_host_alloc`) and must not change until the returned event
+        completes; consumers are ordered with `stream_wait` on that event."""
+        flat = np.ascontiguousarray(flat, dtype=F32).reshape(-1)
+        arr = (C.c_void_p * max(1, len(deps)))(*[d.handle for d in deps])
+        h = C.c_void_p()
+        N.check(N.lib.dls_buf_upload_async(self.ctx, buf.handle, offset, flat.ctypes.data_as(C.c_void_p), flat.size, arr,
+                                           len(deps), C.byref(h)))
+        return Event(h)
+
+    def stream_wait(self, event: Event, stream: int = 0):
+        """Everything queued on pool stream `stream` after this call waits for `event`."""
+        N.check(N.lib.dls_stream_wait_event(self.ctx, stream, event.handle))
+
+    def read_async(self, buf: DeviceBuffer, host_ptr, n: int, offset: int = 0) -> Event:
+        """Non-blocking read-back into (page-locked) host memory; the data is valid once the returned event completes."""
+        h = C.c_void_p()
+        N.check(N.lib.dls_buf_read(self.ctx, buf.handle, offset, host_ptr, n, None, 0, C.byref(h)))
+        return Event(h)
+
     def download(self, buf: DeviceBuffer, n: Optional[int] = None, offset: int = 0) -> np.ndarray:
         n = buf.length - offset if n is None else n
         out = np.empty(n, dtype=F32)

@@ -103,6 +103,16 @@ int dls_buf_read(dls_ctx *ctx, dls_buf *buf, size_t offset, float *dst, size_t n
                  dls_event *const *deps, int n_deps, dls_event **done);
 int dls_buf_write(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, size_t n_floats, dls_event **done);
 
+/* Upload on the context's COPY stream (new functionality: a stream of its own, so the next batch travels over PCIe while
+ * the current step computes; the reference uploads on the compute queue, Tensors:445-463).  The copy stream first waits
+ * for `deps` (e.g. the event after the last consumer of `buf`); `*done` completes when the data is in `buf`.  Nothing
+ * else is ordered: consumers must wait for `*done` (dls_stream_wait_event, or the deps of a launch).  `src` should be
+ * page-locked (dls_host_alloc) and must stay valid until `*done`. */
+int dls_buf_upload_async(dls_ctx *ctx, dls_buf *buf, size_t offset, const float *src, size_t n_floats,
+                         dls_event *const *deps, int n_deps, dls_event **done);
+/* make pool stream `stream_index` wait for `ev` before running anything queued after this call (clEnqueueBarrierWithWaitList) */
+int dls_stream_wait_event(dls_ctx *ctx, int stream_index, dls_event *ev);
+
 /* page-locked host staging memory: replaces Memory.allocate / MemoryUtil.memAllocFloat (Memory.scala:184-208) for
  * buffers that feed dls_buf_write / dls_buf_read at full PCIe rate without a bounce copy. */
 int dls_host_alloc(size_t n_floats, float **out);

@@ -122,44 +122,3 @@ def test_sum_axis(backends, shape):
     if k <= 5000:
         fold = O.sum_axis(O.tensor(x), 1).flat_array().reshape(outer, inner)
         assert (np.abs(got - fold) / scale).max() <= 1e-5
-
-
-UNVERIFIED = pytest.mark.skipif(__import__("os").environ.get("DLS_TEST_UNVERIFIED") != "1",
-                                reason="opt-in kernel written without hardware access; run with DLS_TEST_UNVERIFIED=1 first")
-
-
-@UNVERIFIED
-@pytest.mark.parametrize("m,n,k,bias_mode,activation", [
-    (262144, 32, 27, "col", "relu"),      # conv1 of C3: the shape the kernel exists for
-    (5000, 32, 27, "none", "none"),       # ragged last slab
-    (4096, 8, 3, "row", "tanh"),
-    (70001, 10, 32, "col", "none"),       # N not a multiple of four (scalar stores), even K (padded row stride)
-    (4097, 16, 1, "none", "relu"),
-])
-def test_skinny_contraction_opt_in(backends, monkeypatch, m, n, k, bias_mode, activation):
-    """DLS_SKINNY_GEMM=1: K <= 32, N <= 32 products leave the tensor-core path for the fp32 slab kernel (matmul.cu).
-    fp32 FMA accumulation, so the bound against the float64 product is a few ulp of sum |a||b|."""
-    O, B = backends
-    monkeypatch.setenv("DLS_SKINNY_GEMM", "1")
-    rng = np.random.RandomState(m % 1000 + n + k)
-    a = rng.standard_normal((m, k)).astype(np.float32)
-    b = rng.standard_normal((k, n)).astype(np.float32)
-    kw = {}
-    bias = None
-    if bias_mode != "none":
-        bias = rng.standard_normal(m if bias_mode == "row" else n).astype(np.float32)
-        kw["bias"] = B.tensor(bias)
-    launches0 = B.default_backend().stats()["kernel_launches"]
-    got = B.matmul(B.tensor(a), B.tensor(b), mode="bf16", bias_mode=bias_mode, activation=activation, **kw).flat_array().reshape(m, n)
-    assert B.default_backend().stats()["kernel_launches"] - launches0 == 1          # no staging passes, no tensor-core launch
-    want = a.astype(np.float64) @ b.astype(np.float64)
-    if bias_mode == "row":
-        want = want + bias[:, None]
-    elif bias_mode == "col":
-        want = want + bias[None, :]
-    if activation == "tanh":
-        want = np.tanh(want)
-    elif activation == "relu":
-        want = np.maximum(want, 0.0)
-    scale = np.abs(a).astype(np.float64) @ np.abs(b).astype(np.float64) + 1.0
-    assert (np.abs(got - want) <= 4e-6 * scale).all()

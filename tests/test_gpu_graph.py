@@ -156,20 +156,15 @@ def test_a_step_that_outlives_its_backend_is_harmless(env):
     N.lib.dls_graph_release(handle)
 
 
-@pytest.mark.skipif(__import__("os").environ.get("DLS_TEST_UNVERIFIED") != "1",
-                    reason="opt-in path wired without hardware access; run with DLS_TEST_UNVERIFIED=1 first")
 @pytest.mark.parametrize("compiled", [False, True])
 def test_fused_single_gpu_update_equals_the_per_weight_swaps(env, monkeypatch, compiled):
-    """DLS_FUSED_SGD=1: every gradient materialised, ONE in-place multi-tensor launch (dls_peer_sgd_step without
-    exchange) instead of one `data - delta * lr` launch + swap (+ copy-back when captured) per weight.  Same arithmetic,
-    so the same bits; fewer launches."""
+    """The default single-GPU update of the harness (DLS_FUSED_SGD=0 turns it off): every gradient materialised, ONE
+    in-place multi-tensor launch (dls_peer_sgd_step without exchange) instead of one `data - delta * lr` launch + swap
+    (+ copy-back when captured) per weight.  Same arithmetic, so the same bits; fewer launches."""
     B, H, _ = env
 
     def run(fused):
-        if fused:
-            monkeypatch.setenv("DLS_FUSED_SGD", "1")
-        else:
-            monkeypatch.delenv("DLS_FUSED_SGD", raising=False)
+        monkeypatch.setenv("DLS_FUSED_SGD", "1" if fused else "0")
         be = B.Backend(gemm_mode="fp32")
         try:
             model = H.Mlp((20, 16, 6), bias=True, last_activation="none", backend=be, learning_rate=1e-2)

@@ -116,7 +116,7 @@ def test_cnn_step(env, mode, tol):
         assert rel(ob - gb, ob - rb) <= tol, "bias gradient of layer %d" % i
 
 
-def _dp_rank(rank, world, uid_queue, out_queue):
+def _dp_rank(rank, world, uid_queue, out_queue, kind):
     import os
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -131,20 +131,33 @@ def _dp_rank(rank, world, uid_queue, out_queue):
     else:
         uid = uid_queue.get(timeout=120)
     ex = H.Exchange(be, rank, world, uid)
-    model = H.Mlp((24, 16, 6), bias=True, backend=be, learning_rate=LR, exchange=ex)
+    ex.verify()
     rng = np.random.RandomState(5)
-    x = rng.rand(24, 16).astype(np.float32)
-    t = H.one_hot(rng.randint(0, 6, size=16), 6, feature_major=True)
-    before = [(w.data.flat_array().reshape(w.data.shape), b.data.flat_array()) for w, b in model.layers]
-    loss = model.step(be.tensor(H.shard(x, 1, rank, world)), be.tensor(H.shard(t, 1, rank, world)))
-    after = [(w.data.flat_array().reshape(w.data.shape), b.data.flat_array()) for w, b in model.layers]
+    if kind == "mlp":
+        model = H.Mlp((24, 16, 6), bias=True, backend=be, learning_rate=LR, exchange=ex)
+        x = rng.rand(24, 16).astype(np.float32)
+        t = H.one_hot(rng.randint(0, 6, size=16), 6, feature_major=True)
+        axis = 1
+        pairs = model.layers
+    else:                                # the C5 model (C3's CNN) at a size the oracle steps in milliseconds
+        model = H.Cnn(image=8, channels=(3, 4, 6, 8), hidden=16, classes=10, backend=be, learning_rate=LR, exchange=ex)
+        x = rng.rand(8, 8, 8, 3).astype(np.float32)
+        t = H.one_hot(rng.randint(0, 10, size=8), 10, feature_major=False)
+        axis = 0
+        pairs = model.convs + [model.fc1, model.fc2]
+    read = lambda: [(w.data.flat_array().reshape(w.data.shape), b.data.flat_array()) for w, b in pairs]
+    before = read()
+    loss = model.step(be.tensor(H.shard(x, axis, rank, world)), be.tensor(H.shard(t, axis, rank, world)))
+    after = read()
     out_queue.put((rank, loss, before, after, x, t))
     be.close()
 
 
-def test_data_parallel_step_equals_the_full_batch_step(env):
+@pytest.mark.parametrize("kind", ["mlp", "cnn"])
+def test_data_parallel_step_equals_the_full_batch_step(env, kind):
     """C5's exchange on two B200s: replicas initialised from the same counter-based RNG, batch sharded, every weight
-    gradient SUM-all-reduced over NCCL before the update  ==  the oracle's full-batch step."""
+    gradient SUM-all-reduced (NCCL for the large ones, the NVLink peer-memory launch for the small ones) before the
+    update  ==  the oracle's full-batch step; `cnn` is the C5 model at a small size."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (ranks must not share a device)")
@@ -152,7 +165,7 @@ def test_data_parallel_step_equals_the_full_batch_step(env):
     MO = env[0]
     ctx = mp.get_context("spawn")
     uid_q, out_q = ctx.Queue(), ctx.Queue()
-    procs = [ctx.Process(target=_dp_rank, args=(r, 2, uid_q, out_q)) for r in range(2)]
+    procs = [ctx.Process(target=_dp_rank, args=(r, 2, uid_q, out_q, kind)) for r in range(2)]
     for p in procs:
         p.start()
     results = sorted([out_q.get(timeout=300) for _ in procs], key=lambda r: r[0])
@@ -163,7 +176,11 @@ def test_data_parallel_step_equals_the_full_batch_step(env):
             p.join(timeout=10)
             pytest.fail("a rank process did not exit after delivering its result")
     (_, loss0, before, after0, x, t), (_, loss1, _, after1, _, _) = results
-    want_loss, want, _ = MO.mlp_step(before, x, t, LR)
+    if kind == "mlp":
+        want_loss, want, _ = MO.mlp_step(before, x, t, LR)
+    else:
+        want_loss, nconvs, nfc1, nfc2 = MO.cnn_step(before[:3], before[3], before[4], x, t, LR)
+        want = nconvs + [nfc1, nfc2]
     assert abs((loss0 + loss1) - want_loss) <= 1e-5 * abs(want_loss)
     for (w0, b0), (w1, b1), (rw, rb), (ow, ob) in zip(after0, after1, want, before):
         assert (w0 == w1).all() and (b0 == b1).all()            # replicas stay bit-identical

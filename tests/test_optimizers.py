@@ -163,3 +163,37 @@ def test_compiled_step_with_a_stateful_optimizer_equals_eager(gpu, which):
     assert got_l == want_l and len(set(got_l)) > 1
     for g, w in zip(got_p, want_p):
         assert (bits(g) == bits(w)).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["momentum", "adam"])
+def test_in_place_rules_see_the_pre_update_weights_of_other_weights(gpu, which):
+    """`w1 * w2` under an in-place rule: the gradient of w2 is `d * w1.data`, a LAZY expression over w1's live buffer
+    when the updates are flushed.  The reference swaps buffers (TW:63-72), so every delta reads pre-update values; here
+    all pending deltas must be materialised before the first in-place step, and the data `train` yields must be the
+    forward value of this step, not a recomputation from the updated weights."""
+    B, H, Opt, Plugins, be = gpu
+    n = 1000
+    a0, b0 = rnd(50, n), rnd(51, n)
+    if which == "momentum":
+        opt, step, hyper = Opt.Momentum(0.05, 0.9), OO.momentum_step, (lambda t: OO.momentum_hyper(0.05, 0.9))
+    else:
+        opt, hyper = Opt.Adam(1e-2), (lambda t: OO.adam_hyper(1e-2, 0.9, 0.999, 1e-8, 0.0, t))
+    P = Plugins(optimizer=opt, backend=be)
+    w1, w2 = P.weight(be.tensor(a0)), P.weight(be.tensor(b0))
+    a, b = a0.copy(), b0.copy()
+    sa = [np.zeros(n, F), np.zeros(n, F)]
+    sb = [np.zeros(n, F), np.zeros(n, F)]
+    for t in range(1, 4):
+        out = (w1 * w2).train().run().flat_array()
+        P.flush_updates()
+        assert (bits(out) == bits(a * b)).all(), "step %d: train() yielded data computed from updated weights" % t
+        ga, gb = b.copy(), a.copy()                     # d(w1*w2)/dw1 = w2, /dw2 = w1, both PRE-update (seed delta 1.0)
+        if which == "momentum":
+            a, sa[0] = OO.momentum_step(a, sa[0], ga, hyper(t))
+            b, sb[0] = OO.momentum_step(b, sb[0], gb, hyper(t))
+        else:
+            a, sa[0], sa[1] = OO.adam_step(a, sa[0], sa[1], ga, hyper(t))
+            b, sb[0], sb[1] = OO.adam_step(b, sb[0], sb[1], gb, hyper(t))
+        assert (bits(w1.data.flat_array()) == bits(a)).all(), "w1 after step %d" % t
+        assert (bits(w2.data.flat_array()) == bits(b)).all(), "w2 after step %d" % t
