@@ -28,6 +28,7 @@ DLS_LAUNCH_DEFAULT, DLS_LAUNCH_REDUCE_SUM = 0, 1
 DLS_HASH_WANG, DLS_HASH_LCG = 0, 1
 DLS_GEMM_FP32, DLS_GEMM_TF32, DLS_GEMM_BF16 = 0, 1, 2
 DLS_OPT_MOMENTUM, DLS_OPT_ADAM = 0, 1
+DLS_CONV_FORWARD, DLS_CONV_BACKWARD_DATA, DLS_CONV_BACKWARD_WEIGHTS = 0, 1, 2
 
 
 class CtxOpts(C.Structure):
@@ -38,6 +39,10 @@ class CtxOpts(C.Structure):
 
 class GemmOpts(C.Structure):
     _fields_ = [("mode", C.c_int32), ("bias_mode", C.c_int32), ("activation", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ConvOpts(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("activation", C.c_int32), ("in_stride", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -93,6 +98,13 @@ _SIG = {
     "dls_matmul": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, _PP, C.c_int, _PP, _PP]),
     "dls_matmul_ex": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
                                 C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_conv3x3_supported": (C.c_int, [_P, C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]),
+    "dls_conv3x3_forward": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                      C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_conv3x3_backward_data": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                            C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_conv3x3_backward_weights": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                               C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
     "dls_comm_unique_id": (C.c_int, [C.c_char_p]),
     "dls_comm_init": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_int]),
     "dls_allreduce_sum": (C.c_int, [_P, _P, C.c_size_t, _PP, C.c_int, _PP]),

@@ -76,6 +76,18 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
       "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap *map, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0),
                "r"(c1)
@@ -129,6 +141,18 @@ __device__ __forceinline__ Tile tile_coord(int t, int tiles_m, int tiles_n) {
   c.m0 = (first_m + r % gsz) * BM;
   c.n0 = (r / gsz) * BN;
   return c;
+}
+
+// Implicit-GEMM convolution: pixel tile `t` of an NHWC tensor -> (first image, first row).  A tile is `bb` whole images
+// x `bh` rows x the full width, `bb * bh * W` = 128 (CONV 1: the rows of one output tile) or = BLOCK_K (CONV 2: one k block).
+__device__ __forceinline__ void pixel_tile(const ConvGeom &g, int t, int &b0, int &y0) {
+  if (g.bb == 1) {
+    b0 = t / g.tiles_per_img;
+    y0 = (t - b0 * g.tiles_per_img) * g.bh;
+  } else {
+    b0 = t * g.bb;
+    y0 = 0;
+  }
 }
 
 #ifdef DLS_GEMM_TRACE
@@ -196,12 +220,21 @@ __device__ __forceinline__ void epi_apply(const uint32_t (&v)[32], float (&f)[32
   }
 }
 
-template <bool TF32, bool A_MN, bool B_MN>
+// CONV selects where the operand tiles come from:
+//   0  plain GEMM: 2-D boxes of A and B.
+//   1  implicit-GEMM 3x3 'same' convolution, forward or backward-data (TensorsSpec:144-210 without the im2col matrix):
+//      M = pixels of an NHWC tensor, K = 9 taps x channels.  The A tile of tap (oy, ox) is ONE 4-D TMA box
+//      (channels, W, rows, images) whose start is shifted by the tap; whatever falls outside the image is zero-filled by
+//      the TMA unit -- that fill IS the 'same' padding, and images never bleed into each other because the batch is its
+//      own tensor dimension.  B = the weights of that tap, a 3-D box of [9][N][K] (K-major).
+//   2  convolution weight gradient: M = 9 taps x channels, N = output channels, K = pixels; both operands MN-major, A again
+//      through tap-shifted 4-D boxes.
+template <bool TF32, bool A_MN, bool B_MN, int CONV>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
                    const float *__restrict__ bias, int bias_mode, int act, int direct_store, int splits, int kb_per_split,
-                   int c_rows) {
+                   int c_rows, const ConvGeom cg) {
   // splits > 1 (split-K): work item w = split * n_tiles + tile covers k blocks [split * kb_per_split, ...) and writes its
   // partial tile at row offset split * tiles_m * BM of a [splits * tiles_m * BM, N] scratch matrix (c_rows = its row count);
   // the epilogue (bias / activation) then runs in splitk_reduce_kernel.
@@ -226,7 +259,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
   const int n_tiles = tiles_m * tiles_n;
-  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  const int num_kb = CONV == 1 ? 9 * cg.kc_per_tap : (K + BLOCK_K - 1) / BLOCK_K;
   const int n_work = n_tiles * splits;
 
   DLS_TRACE_DECL
@@ -263,13 +296,48 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
         const Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n);
         const int kb0 = (w / n_tiles) * kb_per_split, kb1 = min(num_kb, kb0 + kb_per_split);
+        int img0 = 0, row0 = 0;
+        if (CONV == 1) pixel_tile(cg, tc.m0 / BM, img0, row0);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           DLS_TRACE(10);
           const uint32_t a_dst = smem_u32(smem + stage * STAGE_BYTES);
           const uint32_t b_dst = a_dst + A_STAGE_BYTES;
-          mbar_expect_tx(full_bar(stage), STAGE_BYTES);
           const int k0 = kb * BLOCK_K;
+          if (CONV == 1) {
+            // k block = (tap, channel block): the activation box shifted by the tap, and that tap's weights
+            const int tap = kb / cg.kc_per_tap, kc = kb - tap * cg.kc_per_tap;
+            const int oy = tap / 3 - 1, ox = tap - (tap / 3) * 3 - 1;
+            mbar_expect_tx(full_bar(stage), A_STAGE_BYTES + cg.b_bytes);
+            tma_load_4d(a_dst, &map_a, full_bar(stage), kc * BLOCK_K, -cg.tap_sign * ox, row0 - cg.tap_sign * oy, img0);
+            tma_load_3d(b_dst, &map_b, full_bar(stage), kc * BLOCK_K, 0, tap);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+            continue;
+          }
+          if (CONV == 2) {
+            // k block = 64 pixels; A atom j = (tap, 64-channel block) `tc.m0 / 64 + j`: the pixel box shifted by that tap;
+            // B atoms = 64-column blocks of the delta at the same (unshifted) pixels
+            int pi, py;
+            pixel_tile(cg, kb, pi, py);
+            const int rb0 = tc.m0 / MN_ATOM, n_rb = 9 * cg.cblks;
+            const int a_atoms = min(BM / MN_ATOM, n_rb - rb0), b_atoms = (cg.n_mma + MN_ATOM - 1) / MN_ATOM;
+            mbar_expect_tx(full_bar(stage), (a_atoms + b_atoms) * BLOCK_K * 128);
+            for (int j = 0; j < a_atoms; ++j) {
+              const int rb = rb0 + j, tap = rb / cg.cblks, cb = rb - tap * cg.cblks;
+              const int oy = tap / 3 - 1, ox = tap - (tap / 3) * 3 - 1;
+              tma_load_4d(a_dst + j * BLOCK_K * 128, &map_a, full_bar(stage), cb * MN_ATOM, -ox, py - oy, pi);
+            }
+            for (int j = 0; j < b_atoms; ++j) tma_load_2d(b_dst + j * BLOCK_K * 128, &map_b, full_bar(stage), j * MN_ATOM, k0);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+            continue;
+          }
+          mbar_expect_tx(full_bar(stage), STAGE_BYTES);
           if (A_MN) {
 #pragma unroll
             for (int j = 0; j < BM / MN_ATOM; ++j)
@@ -297,7 +365,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       // instruction descriptor (cute::UMMA::InstrDescriptor): D = fp32, A/B format, major-ness, N >> 3, M >> 4
       const uint32_t fmt = TF32 ? 2u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
-                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+                             ((uint32_t)((CONV ? cg.n_mma : BN) >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
       // K-major: 8-row groups are 1024 B apart (SBO), one swizzle atom along K (LBO unused).
       // MN-major: 8 K-rows of 128 B form an atom (SBO = 1024 B), atoms along MN are BLOCK_K * 128 B apart (LBO).
       const uint32_t a_lbo = A_MN ? BLOCK_K * 128 : 0, b_lbo = B_MN ? BLOCK_K * 128 : 0;
@@ -519,6 +587,31 @@ static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, co
   return DLS_OK;
 }
 
+// rank-N row-major tensor (dims[0] innermost, strides in bytes for dims 1..rank-1) with a 128B-swizzled box; elements
+// outside the tensor read as zero.
+static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *base, int rank, const uint64_t *dims,
+                       const uint64_t *strides_bytes, const uint32_t *box) {
+  encode_tiled_fn enc = get_encoder();
+  DLS_CHECK(enc != nullptr, DLS_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t d[5], s[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) {
+    d[i] = dims[i];
+    b[i] = box[i];
+    e[i] = 1;
+    if (i + 1 < rank) s[i] = strides_bytes[i];
+  }
+  CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void *>(base), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    std::string t = "cuTensorMapEncodeTiled (rank " + std::to_string(rank) + ") failed with CUresult " + std::to_string((int)r) + ": dims";
+    for (int i = 0; i < rank; ++i) t += " " + std::to_string(dims[i]) + "/" + std::to_string(box[i]);
+    set_error(t);
+    return DLS_ERR_CUDA;
+  }
+  return DLS_OK;
+}
+
 // out[i] = act(sum_s partial[s * stride + i] + bias), i < m * n: the second half of a split-K contraction.
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restrict__ partial, float *__restrict__ out, size_t m,
                                                             size_t n, size_t stride, int splits, const float *__restrict__ bias,
@@ -539,10 +632,11 @@ struct SplitPlan {
   int splits = 1, kb_per_split = 0, c_rows = 0;
 };
 
-template <bool TF32, bool A_MN, bool B_MN>
+template <bool TF32, bool A_MN, bool B_MN, int CONV = 0>
 static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mc,
-                          float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct, const SplitPlan &sp) {
-  auto kern = gemm_tc_kernel<TF32, A_MN, B_MN>;
+                          float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct, const SplitPlan &sp,
+                          const ConvGeom &cg = ConvGeom()) {
+  auto kern = gemm_tc_kernel<TF32, A_MN, B_MN, CONV>;
   // the attribute is per DEVICE (one process may hold a context on every GPU of the node), guarded by ctx->mu per context
   static std::atomic<bool> configured[64];
   const int dev = ctx->device & 63;
@@ -555,7 +649,7 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
   const int sms = ctx->comm_pending.empty() ? ctx->sm_count : std::max(1, ctx->sm_count - ctx->exchange_sms);
   const int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, sp.splits,
-                                              sp.kb_per_split, sp.c_rows);
+                                              sp.kb_per_split, sp.c_rows, cg);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;
@@ -684,6 +778,146 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
     }
   }
   if (scratch.ptr) free_block(ctx, scratch);
+  return rc;
+}
+
+// Pixel tiling of an NHWC tensor for the implicit-GEMM kernels: `pixels` (128 or BLOCK_K) consecutive pixels must be `bb` whole
+// images x `bh` rows x the full width.
+bool conv_tiling(int H, int W, int pixels, ConvGeom *g) {
+  if (W <= 0 || H <= 0 || W > 256 || pixels % W) return false;
+  g->H = H;
+  g->W = W;
+  g->bw = W;
+  if ((long long)W * H >= pixels) {
+    g->bh = pixels / W;
+    if (H % g->bh) return false;
+    g->bb = 1;
+    g->tiles_per_img = H / g->bh;
+  } else {
+    if (pixels % (W * H)) return false;
+    g->bh = H;
+    g->bb = pixels / (W * H);
+    g->tiles_per_img = 0;
+  }
+  return g->bh <= 256 && g->bb <= 256;
+}
+
+bool conv_tc_supported(int kind, int H, int W, int k_channels, int n) {
+  ConvGeom g;
+  const int block_k = kind == DLS_GEMM_TF32 ? 32 : 64;
+  return (kind == DLS_GEMM_TF32 || kind == DLS_GEMM_BF16) && conv_tiling(H, W, tc::BM, &g) && k_channels > 0 &&
+         k_channels % block_k == 0 && n >= 1 && n <= tc::BN;
+}
+
+int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batch, int H, int W, int kp, const void *wts, int N,
+                   float *C, int tap_sign, const GemmEpilogue &epi) {
+  using namespace tc;
+  DLS_CHECK(conv_tc_supported(kind, H, W, kp, N), DLS_ERR_UNSUPPORTED, "launch_conv_tc: shape not supported by the implicit-GEMM kernel");
+  const bool tf32 = kind == DLS_GEMM_TF32;
+  const int elem = tf32 ? 4 : 2, block_k = 128 / elem;
+  ConvGeom cg;
+  conv_tiling(H, W, BM, &cg);
+  cg.kc_per_tap = kp / block_k;
+  cg.tap_sign = tap_sign;
+  cg.n_mma = (N + 15) & ~15;
+  cg.b_bytes = cg.n_mma * 128;
+  const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap ma, mb, mc;
+  {
+    const uint64_t dims[4] = {(uint64_t)kp, (uint64_t)W, (uint64_t)H, (uint64_t)batch};
+    const uint64_t str[3] = {(uint64_t)kp * elem, (uint64_t)kp * elem * W, (uint64_t)kp * elem * W * H};
+    const uint32_t box[4] = {(uint32_t)block_k, (uint32_t)cg.bw, (uint32_t)cg.bh, (uint32_t)cg.bb};
+    int rc = make_map_nd(&ma, dt, act, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)kp, (uint64_t)N, 9};
+    const uint64_t str[2] = {(uint64_t)kp * elem, (uint64_t)kp * elem * N};
+    const uint32_t box[3] = {(uint32_t)block_k, (uint32_t)cg.n_mma, 1};
+    int rc = make_map_nd(&mb, dt, wts, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  const long long P = (long long)batch * H * W;
+  DLS_CHECK(P < (1LL << 31), DLS_ERR_UNSUPPORTED, "launch_conv_tc: too many pixels");
+  const int direct = ((N % 4) != 0 || ((uintptr_t)C % 16) != 0) ? 1 : 0;
+  int rc = DLS_OK;
+  if (direct == 0) rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, C, (uint64_t)N, (uint64_t)P, (uint64_t)N, EPI_CHUNK, 32);
+  else mc = ma;
+  if (rc) return rc;
+  SplitPlan sp;
+  sp.kb_per_split = 9 * cg.kc_per_tap;
+  sp.c_rows = (int)P;
+  cudaStream_t st = ctx->streams[stream];
+  if (tf32) return launch_variant<true, false, false, 1>(ctx, st, ma, mb, mc, C, (int)P, N, 9 * kp, N, epi, direct, sp, cg);
+  return launch_variant<false, false, false, 1>(ctx, st, ma, mb, mc, C, (int)P, N, 9 * kp, N, epi, direct, sp, cg);
+}
+
+// dw[(tap * cin + c) * cout + f] = sum_s partial[s * stride + (tap * cxp + c) * ldp + f]: the second half of the split
+// weight-gradient contraction; drops the zero rows of the padded channels.
+__global__ void __launch_bounds__(256) conv_dw_reduce_kernel(const float *__restrict__ partial, float *__restrict__ dw, int splits,
+                                                             size_t stride, int cxp, int cin, int cout, int ldp) {
+  const int total = 9 * cin * cout;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int f = i % cout, c = (i / cout) % cin, tap = i / (cout * cin);
+    const float *src = partial + (size_t)(tap * cxp + c) * ldp + f;
+    float x = __ldg(src);
+    for (int sp = 1; sp < splits; ++sp) x = __fadd_rn(x, __ldg(src + (size_t)sp * stride));
+    dw[i] = x;
+  }
+}
+
+bool conv_dw_tc_supported(int kind, int H, int W, int cin, int cout) {
+  ConvGeom g;
+  return kind == DLS_GEMM_BF16 && conv_tiling(H, W, 64, &g) && cin >= 1 && cout >= 1 && cout <= tc::BN;
+}
+
+int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int cxp, const void *dz, int cdp, int batch, int H, int W,
+                      int cin, int cout, float *dw) {
+  using namespace tc;
+  DLS_CHECK(conv_dw_tc_supported(kind, H, W, cin, cout) && cxp % 64 == 0 && cdp % 64 == 0, DLS_ERR_UNSUPPORTED,
+            "launch_conv_dw_tc: shape not supported by the implicit-GEMM weight-gradient kernel");
+  ConvGeom cg;
+  conv_tiling(H, W, 64, &cg);
+  cg.cblks = cxp / 64;
+  cg.n_mma = (cout + 15) & ~15;
+  const long long P = (long long)batch * H * W;
+  DLS_CHECK(P < (1LL << 31), DLS_ERR_UNSUPPORTED, "launch_conv_dw_tc: too many pixels");
+  const int M = 9 * cxp, N = cout;
+  CUtensorMap ma, mb, mc;
+  {
+    const uint64_t dims[4] = {(uint64_t)cxp, (uint64_t)W, (uint64_t)H, (uint64_t)batch};
+    const uint64_t str[3] = {(uint64_t)cxp * 2, (uint64_t)cxp * 2 * W, (uint64_t)cxp * 2 * W * H};
+    const uint32_t box[4] = {64, (uint32_t)cg.bw, (uint32_t)cg.bh, (uint32_t)cg.bb};
+    int rc = make_map_nd(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, act, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  int rc = make_map(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dz, (uint64_t)cdp, (uint64_t)P, (uint64_t)cdp, 64, 64);
+  if (rc) return rc;
+  const int tiles = (M + BM - 1) / BM;
+  const int num_kb = (int)((P + 63) / 64);
+  SplitPlan sp;
+  int want = std::max(1, std::min(ctx->sm_count / tiles, num_kb / 8));
+  sp.kb_per_split = (num_kb + want - 1) / want;
+  sp.splits = (num_kb + sp.kb_per_split - 1) / sp.kb_per_split;
+  const int m_pad = tiles * BM;
+  const int ldp = (N + 3) & ~3;
+  sp.c_rows = sp.splits * m_pad;
+  Block scratch;
+  rc = alloc_block(ctx, (size_t)sp.c_rows * ldp * sizeof(float), stream, &scratch);
+  if (rc) return rc;
+  float *part = (float *)scratch.ptr;
+  rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, part, (uint64_t)N, (uint64_t)sp.c_rows, (uint64_t)ldp, EPI_CHUNK, 32);
+  cudaStream_t st = ctx->streams[stream];
+  if (!rc) rc = launch_variant<false, true, true, 2>(ctx, st, ma, mb, mc, part, M, N, (int)P, ldp, GemmEpilogue(), 0, sp, cg);
+  if (!rc) {
+    const int total = 9 * cin * cout;
+    conv_dw_reduce_kernel<<<std::min((total + 255) / 256, ctx->sm_count * 8), 256, 0, st>>>(part, dw, sp.splits, (size_t)m_pad * ldp, cxp,
+                                                                                            cin, cout, ldp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) rc = cuda_fail(e, "conv_dw_reduce_kernel", __FILE__, __LINE__);
+    ctx->stats.kernel_launches++;
+  }
+  free_block(ctx, scratch);
   return rc;
 }
 

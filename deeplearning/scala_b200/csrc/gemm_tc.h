@@ -10,6 +10,46 @@ struct GemmEpilogue {
   int act = 0;         // 0 none, 1 tanh, 2 relu (= Tensor.max(x, fill 0))
 };
 
+// Geometry of the implicit-GEMM convolution modes of gemm_tc_kernel (zero for a plain GEMM).
+struct ConvGeom {
+  int H = 0, W = 0;               // spatial size of the NHWC tensor whose pixels are tiled
+  int bw = 0, bh = 0, bb = 0;     // TMA box of one pixel tile: bb images x bh rows x bw (= W) columns
+  int tiles_per_img = 0;          // H / bh when bb == 1
+  int kc_per_tap = 0;             // CONV 1: k blocks per tap (padded channels / BLOCK_K)
+  int tap_sign = 1;               // CONV 1: +1 forward (reads x[y - oy, x - ox]), -1 backward-data (reads dz[y + oy, x + ox])
+  int n_mma = 0;                  // UMMA N (multiple of 16, <= 256) and rows of the weight box
+  int b_bytes = 0;                // bytes of one B stage (n_mma x 128)
+  int cblks = 0;                  // CONV 2: 64-channel blocks per tap
+};
+
+// Implicit-GEMM 'same' 3x3 convolution on the tensor cores, out[P, N] fp32 (P = batch*H*W pixels, row-major) =
+//   sum over taps t = (ky, kx) and channels k of act[b, y - s*(ky-1), x - s*(kx-1), k] * wts[t][n][k]   (s = tap_sign)
+// act: staged NHWC operand [batch][H][W][kp] (bf16, or tf32-rounded fp32), kp % BLOCK_K == 0 (64 bf16 / 32 tf32);
+// wts: staged [9][N][kp] in the same element type.  Forward: act = x, wts[t][f][c] = w[t][c][f], s = +1.
+// Backward-data: act = dz, wts[t][c][f] = w[t][c][f], s = -1.
+bool conv_tc_supported(int kind, int H, int W, int k_channels, int n);
+bool conv_tiling(int H, int W, int pixels, ConvGeom *g);
+int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batch, int H, int W, int kp, const void *wts, int N,
+                   float *C, int tap_sign, const GemmEpilogue &epi);
+
+// Weight gradient dw[9*cin, cout] fp32 (= [3,3,cin,cout]) = sum over pixels of act[p - tap][c] * dz[p][f]: contraction over the
+// pixels, both operands read MN-major from their staged NHWC copies (act [batch][H][W][cxp], dz [batch*H*W][cdp]; bf16 only,
+// channels padded to 64), A through tap-shifted 4-D boxes; split over the SMs along the pixels + one reduce launch.
+bool conv_dw_tc_supported(int kind, int H, int W, int cin, int cout);
+int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int cxp, const void *dz, int cdp, int batch, int H, int W,
+                      int cin, int cout, float *dw);
+
+// conv.cu
+bool conv_direct_supported(int cin, int cout);
+int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, const float *w, const float *bias, float *out, int B,
+                           int H, int W, int cin, int cout, int act);
+int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
+                          int cout);
+int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
+                          int stride);
+int launch_conv_pack_weights(dls_ctx *ctx, int stream, int mode, const float *w, void *wf, void *wb, int cin, int cout, int cinp,
+                             int coutp);
+
 // D[M,N] fp32 row-major (pitch ldc) = A * B (+ epilogue).
 //   kind  : DLS_GEMM_BF16 (operands are bf16 in HBM) or DLS_GEMM_TF32 (operands are fp32 in HBM, read as tf32)
 //   a_mn  : false -> A stored [M][K] (K contiguous, pitch lda elements); true -> stored [K][M] (M contiguous)

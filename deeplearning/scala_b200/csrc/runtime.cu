@@ -215,7 +215,7 @@ int finish_output(dls_ctx *ctx, int stream, dls_buf *const *written, int n_writt
     if (!b) continue;
     b->block.stream_mask |= 1u << stream;
     b->last_stream = stream;
-    for (int k = 0; k < 2; ++k)   // the contents changed: operand shadows are stale
+    for (int k = 0; k < kShadows; ++k)   // the contents changed: operand shadows are stale
       if (b->shadow[k].ptr) free_block(ctx, b->shadow[k]);
     if (ctx->n_streams > 1) {
       if (!b->ready) DLS_CUDA(cudaEventCreateWithFlags(&b->ready, cudaEventDisableTiming));
@@ -397,7 +397,7 @@ void dls_buf_release(dls_buf *buf) {
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
     if (buf->comm_ready) join_exchange(ctx, buf->last_stream, buf);   // the block may be reused right away
     if (buf->ready) cudaEventDestroy(buf->ready);
-    for (int k = 0; k < 2; ++k) free_block(ctx, buf->shadow[k]);
+    for (int k = 0; k < kShadows; ++k) free_block(ctx, buf->shadow[k]);
     free_block(ctx, buf->block);
   }
   delete buf;
@@ -457,7 +457,7 @@ int dls_buf_upload_async(dls_ctx *ctx, dls_buf *buf, size_t offset, const float 
     DLS_CUDA(cudaMemcpyAsync(buf->ptr + offset, src, n_floats * sizeof(float), cudaMemcpyHostToDevice, ctx->copy_stream));
     ctx->stats.h2d_bytes += n_floats * sizeof(float);
   }
-  for (int k = 0; k < 2; ++k)   // the contents change: operand shadows are stale
+  for (int k = 0; k < kShadows; ++k)   // the contents change: operand shadows are stale
     if (buf->shadow[k].ptr) free_block(ctx, buf->shadow[k]);
   dls_event *e = new dls_event();
   e->ctx = ctx;

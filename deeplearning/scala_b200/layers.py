@@ -215,30 +215,51 @@ class Layers:
     def conv2d_3x3(self, x, w, bias=None, activation: str = "none") -> TensorLayer:
         """'Same' 3x3 convolution of an NHWC tensor with weights [3, 3, Cin, Cout] (the layout and the index convention
         of TensorsSpec:144-210: out[b,y,x,f] = bias[f] + sum x[b, y-(ky-1), x-(kx-1), c] * w[ky,kx,c,f], zero padding from
-        the bounds check of `translate`).  Lowered as im2col + GEMM: the nine translated views are written by ONE
-        multi-root gather launch (`Tensor.join`), then out = col[BHW, Cin*9] . wmat[Cin*9, Cout] on the tensor cores."""
+        the bounds check of `translate`).
+        In the tensor-core modes each of the three passes has a kernel of its own (csrc/conv.cu: implicit GEMM whose
+        operand tiles are tap-shifted TMA boxes of the activation, direct kernels for a first layer with Cin <= 4), and a
+        preceding `downsample` view is read in place.  Where no such kernel applies (fp32 parity mode, odd shapes) the
+        pass is composed the way the reference composes it: the nine translated views written by ONE multi-root gather
+        launch (`Tensor.join`), then out = col[BHW, Cin*9] . wmat[Cin*9, Cout]."""
         offsets = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
         inputs = [x, w] + ([bias] if bias is not None else [])
 
         def build(tapes):
             tx, tw = tapes[0], tapes[1]
             X, W = tx.data, tw.data
+            be = X.backend
             bsz, h, wd, cin = X.shape
             cout = W.shape[3]
             m = bsz * h * wd
-            col = T.join([X.translate([0, oy, ox, 0]) for (oy, ox) in offsets]).reshape([m, cin * 9]).do_cache()
-            wmat = W.permute([2, 0, 1, 3]).reshape([cin * 9, cout]).do_cache()
             bias_t = tapes[2].data if bias is not None else None
-            y = T.matmul(col, wmat, bias=bias_t, bias_mode="col" if bias is not None else "none", activation=activation)
-            owned = [col, wmat]
+            owned = []
+            lazy = {}
+
+            def col():                                               # the im2col matrix, only where a composed pass needs it
+                if "col" not in lazy:
+                    lazy["col"] = T.join([X.translate([0, oy, ox, 0]) for (oy, ox) in offsets]).reshape([m, cin * 9]).do_cache()
+                    owned.append(lazy["col"])
+                return lazy["col"]
+
+            def wmat():
+                if "wmat" not in lazy:
+                    lazy["wmat"] = W.permute([2, 0, 1, 3]).reshape([cin * 9, cout]).do_cache()
+                    owned.append(lazy["wmat"])
+                return lazy["wmat"]
+
+            if be.conv3x3_supported("forward", h, wd, cin, cout):
+                y = be.conv3x3_forward(X, W, bias_t, activation)
+            else:
+                y = T.matmul(col(), wmat(), bias=bias_t, bias_mode="col" if bias is not None else "none",
+                             activation=activation).reshape([bsz, h, wd, cout])
 
             def backward(y_cached):
                 def run(do_delta: Do):
                     memo = {}
 
-                    def dz_of(d):
+                    def dz_of(d):                                    # [B, H, W, Cout], shared by the three consumers
                         if "dz" not in memo:
-                            d = d.broadcast([bsz, h, wd, cout]).reshape([m, cout])
+                            d = d.broadcast([bsz, h, wd, cout])
                             if activation == "tanh":
                                 d = d * (1.0 - y_cached * y_cached)
                             elif activation == "relu":
@@ -248,7 +269,9 @@ class Layers:
                         return memo["dz"]
 
                     def delta_x(d):
-                        dcol = T.matmul(dz_of(d), wmat, transpose_b=True).reshape([bsz, h, wd, cin, 9])
+                        if be.conv3x3_supported("backward_data", h, wd, cin, cout):
+                            return be.conv3x3_backward_data(dz_of(d), W)
+                        dcol = T.matmul(dz_of(d).reshape([m, cout]), wmat(), transpose_b=True).reshape([bsz, h, wd, cin, 9])
                         parts = [s.translate([0, -oy, -ox, 0]) for s, (oy, ox) in zip(dcol.split(4), offsets)]
                         acc = parts[0]
                         for p in parts[1:]:
@@ -256,20 +279,18 @@ class Layers:
                         return acc
 
                     def delta_w(d):
-                        dw = T.matmul(col, dz_of(d), transpose_a=True)              # [Cin*9, Cout]
+                        if be.conv3x3_supported("backward_weights", h, wd, cin, cout):
+                            return be.conv3x3_backward_weights(X, dz_of(d))
+                        dw = T.matmul(col(), dz_of(d).reshape([m, cout]), transpose_a=True)     # [Cin*9, Cout]
                         return dw.reshape([cin, 3, 3, cout]).permute([1, 2, 0, 3])
 
                     tx.backward(do_delta.map(delta_x))
                     tw.backward(do_delta.map(delta_w))
                     if bias is not None:
-                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), 0)))
+                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d).reshape([m, cout]), 0)))
                 return run
             return y, backward, owned
-
-        def view(cached, tapes):                                    # [B*H*W, Cout] -> [B, H, W, Cout], same buffer
-            bsz, h, wd, _ = tapes[0].data.shape
-            return cached.reshape([bsz, h, wd, tapes[1].data.shape[3]])
-        return self._pinned(inputs, build, view)
+        return self._pinned(inputs, build)
 
 
 def relu_mask(y):

@@ -313,6 +313,77 @@ class Backend:
             return DeviceBuffer(self, h, m * n)
         return ProducedTensor(self, produce, [m, n], a.padding)
 
+    # -- 'same' 3x3 convolution without an im2col matrix (csrc/conv.cu; TensorsSpec:144-210 spells it with nine translates) --
+    _MODES = {None: -1, "fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}
+
+    def conv3x3_supported(self, which: str, h: int, w: int, cin: int, cout: int, mode: Optional[str] = None) -> bool:
+        """Does libdlsb200 have a dedicated kernel for this pass ("forward" / "backward_data" / "backward_weights") at this
+        shape in this contraction mode?  If not, compose the convolution from `translate`, `join` and `matmul`."""
+        p = {"forward": N.DLS_CONV_FORWARD, "backward_data": N.DLS_CONV_BACKWARD_DATA, "backward_weights": N.DLS_CONV_BACKWARD_WEIGHTS}[which]
+        return bool(N.lib.dls_conv3x3_supported(self.ctx, p, h, w, cin, cout, self._MODES[mode]))
+
+    @staticmethod
+    def _sampled_source(x: "Tensor"):
+        """(tensor to read, stride): a nearest-neighbour `scale` down by an integer factor of the two middle dims of a
+        MATERIALISED NHWC tensor is read in place by the convolution kernels instead of being gathered first."""
+        if isinstance(x, TransformedTensor) and len(x.shape) == 4 and isinstance(x.checkpoint, NonInlineTensor):
+            src = x.checkpoint.shape
+            m = x.matrix
+            if m.shape == (4, 5) and src[0] == x.shape[0] and src[3] == x.shape[3] and x.shape[1] and src[1] % x.shape[1] == 0:
+                s = src[1] // x.shape[1]
+                want = np.zeros((4, 5))
+                want[0, 0] = want[3, 3] = 1.0
+                want[1, 1] = want[2, 2] = float(s)
+                if s > 1 and src[2] == x.shape[2] * s and np.array_equal(m, want):
+                    return x.checkpoint, s
+        return x, 1
+
+    def conv3x3_forward(self, x: "Tensor", w: "Tensor", bias: Optional["Tensor"] = None, activation: str = "none",
+                        mode: Optional[str] = None) -> "NonInlineTensor":
+        """out[b,y,x,f] = act(bias[f] + sum x[b, y-(ky-1), x-(kx-1), c] w[ky,kx,c,f]) for NHWC `x` and `w` [3,3,Cin,Cout]."""
+        batch, h, wd, cin = x.shape
+        cout = w.shape[3]
+        src, stride = self._sampled_source(x)
+        opts = N.ConvOpts(mode=self._MODES[mode], activation={"none": 0, "tanh": 1, "relu": 2}[activation], in_stride=stride, reserved=0)
+
+        def produce():
+            bx, bw = src._buffer(), w._buffer()
+            bb = bias._buffer() if bias is not None else None
+            hd = C.c_void_p()
+            N.check(N.lib.dls_conv3x3_forward(self.ctx, bx.handle, bw.handle, bb.handle if bb else None, batch, h, wd, cin, cout,
+                                              C.byref(opts), None, 0, C.byref(hd), None))
+            return DeviceBuffer(self, hd, batch * h * wd * cout)
+        return ProducedTensor(self, produce, [batch, h, wd, cout], x.padding)
+
+    def conv3x3_backward_data(self, dz: "Tensor", w: "Tensor", mode: Optional[str] = None) -> "NonInlineTensor":
+        """dx[b,y,x,c] = sum dz[b, y+(ky-1), x+(kx-1), f] w[ky,kx,c,f]."""
+        batch, h, wd, cout = dz.shape
+        cin = w.shape[2]
+        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=1, reserved=0)
+
+        def produce():
+            bd, bw = dz._buffer(), w._buffer()
+            hd = C.c_void_p()
+            N.check(N.lib.dls_conv3x3_backward_data(self.ctx, bd.handle, bw.handle, batch, h, wd, cin, cout, C.byref(opts), None, 0,
+                                                    C.byref(hd), None))
+            return DeviceBuffer(self, hd, batch * h * wd * cin)
+        return ProducedTensor(self, produce, [batch, h, wd, cin], dz.padding)
+
+    def conv3x3_backward_weights(self, x: "Tensor", dz: "Tensor", mode: Optional[str] = None) -> "NonInlineTensor":
+        """dw[ky,kx,c,f] = sum over b,y,x of x[b, y-(ky-1), x-(kx-1), c] dz[b,y,x,f]."""
+        batch, h, wd, cin = x.shape
+        cout = dz.shape[3]
+        src, stride = self._sampled_source(x)
+        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=stride, reserved=0)
+
+        def produce():
+            bx, bd = src._buffer(), dz._buffer()
+            hd = C.c_void_p()
+            N.check(N.lib.dls_conv3x3_backward_weights(self.ctx, bx.handle, bd.handle, batch, h, wd, cin, cout, C.byref(opts), None, 0,
+                                                       C.byref(hd), None))
+            return DeviceBuffer(self, hd, 9 * cin * cout)
+        return ProducedTensor(self, produce, [3, 3, cin, cout], x.padding)
+
     def sum_axis(self, t: "Tensor", axis: int) -> "NonInlineTensor":
         """Sum away one dimension: what TensorLayers.sumAs spells as `split(axis).reduce(_ + _)` (TL:124-162), as one
         row / column reduction kernel (`dls_sum_axis`) instead of a host-unrolled chain of `shape[axis]` additions."""

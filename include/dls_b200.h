@@ -194,6 +194,35 @@ int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m,
                   int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
                   dls_event **done);
 
+/* ---- 'same' 3x3 convolution of NHWC tensors with [3,3,Cin,Cout] weights, without an im2col matrix.  The reference spells
+ * a convolution as nine `translate`d views, `join` and an unrolled matmul (TensorsSpec:144-210 `convolute`,
+ * benchmarks.scala:412-632); these three entries are the lowering target of that composite and of its two gradients:
+ *   forward           out[b,y,x,f] = act(bias[f] + sum_{ky,kx,c} xs[b, y-(ky-1), x-(kx-1), c] * w[ky,kx,c,f])
+ *   backward_data     dx[b,y,x,c]  = sum_{ky,kx,f} dz[b, y+(ky-1), x+(kx-1), f] * w[ky,kx,c,f]
+ *   backward_weights  dw[ky,kx,c,f] = sum_{b,y,x} xs[b, y-(ky-1), x-(kx-1), c] * dz[b,y,x,f]
+ * with zero padding outside the image.  xs is the [batch,h,w,cin] input; with in_stride = s > 1 it is read in place from a
+ * [batch, h*s, w*s, cin] buffer as xs[b,y,x,c] = x[b, s*y, s*x, c] -- the nearest-neighbour `scale` view (Tensors:950-965)
+ * that precedes the convolution, never materialised.  Tensor-core modes only (mode = -1 takes the context's gemm_mode):
+ * operands rounded to bf16 / tf32 like every contraction of the mode, fp32 accumulation; same stated tolerances as
+ * dls_matmul_ex.  Cin <= 4 (first layer) runs on direct CUDA-core kernels, everything else as an implicit GEMM on the
+ * tcgen05 tensor cores.  DLS_ERR_UNSUPPORTED (ask dls_conv3x3_supported first) means: compose it from views + dls_matmul. */
+enum dls_conv_pass { DLS_CONV_FORWARD = 0, DLS_CONV_BACKWARD_DATA = 1, DLS_CONV_BACKWARD_WEIGHTS = 2 };
+typedef struct dls_conv_opts {
+  int32_t mode;        /* enum dls_gemm_mode, or -1 = context default */
+  int32_t activation;  /* enum dls_activation (forward only)          */
+  int32_t in_stride;   /* 0 / 1 = dense input; s > 1 = input sampled at stride s (forward, backward_weights) */
+  int32_t reserved;
+} dls_conv_opts;
+int dls_conv3x3_supported(dls_ctx *ctx, int pass, size_t h, size_t w, size_t cin, size_t cout, int mode);
+int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, size_t batch, size_t h, size_t wd, size_t cin,
+                        size_t cout, const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
+                        dls_event **done);
+int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
+                              const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done);
+int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin,
+                                 size_t cout, const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
+                                 dls_event **done);
+
 /* ---- data-parallel exchange (new functionality: the reference has no collective) */
 int dls_comm_unique_id(uint8_t *id128);                              /* 128-byte NCCL unique id (rank 0)   */
 int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size);

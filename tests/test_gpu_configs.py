@@ -6,8 +6,16 @@ weight gradients contract over K = 262 144 / 65 536 / 16 384 pixels (split-K), c
 down-sampling backward gathers cross image boundaries thousands of times, and an 8192 x 4096 x 4096 product covers 1024
 output tiles (7 waves, grouped raster wrap-around).
 
-Bars (same as tests/test_gpu_models.py): fp32 mode 1e-5 relative; tensor-core modes 2e-4 against the oracle evaluated
-with the same operand rounding (bf16 RNE / tf32 RNA), i.e. only the accumulation order differs.
+Bars.  fp32 mode: 1e-5 relative (north_star's reductions bar) -- this is the run that proves the graph, the gathers, the
+reductions and the split-K bookkeeping at scale.  Tensor-core modes: every gradient within 3 x the mode's stated bound
+(tf32 1e-3, bf16 4e-3; a gradient chains several rounded contractions) of the fp32 oracle, and within 1 x the stated
+bound of the oracle evaluated with the same operand rounding.  The second bar cannot be tightened at these sizes the way
+the small model tests (2e-4) and the single-contraction tests (2e-6 of sum |a||b|, below and in test_gpu_gemm.py) do:
+two evaluations that differ only in fp32 accumulation order (~1e-6 relative after cancellation) re-round a fraction
+~1e-6 / ulp of each layer's activations to the neighbouring bf16 / tf32 value, a wide next layer sums thousands of them,
+and after two or three layers the two evaluations are decorrelated at the rounding level itself (measured on a B200:
+1.4e-3 bf16, 6e-4 tf32 -- the sqrt(8) ratio of the two ulps -- while tools/accum_probe.py shows the contraction kernel
+itself within 1e-7 of sum |a||b| at K = 262 144).
 """
 import os
 import sys
@@ -42,7 +50,10 @@ def read_pair(pair):
     return pair[0].data.flat_array().reshape(pair[0].data.shape), pair[1].data.flat_array()
 
 
-@pytest.mark.parametrize("mode,tol", [("fp32", 1e-5), ("tf32", 2e-4), ("bf16", 2e-4)])
+STATED = {"tf32": 1e-3, "bf16": 4e-3}
+
+
+@pytest.mark.parametrize("mode,tol", [("fp32", 1e-5), ("tf32", 1e-3), ("bf16", 4e-3)])
 @pytest.mark.parametrize("compiled", [False, True], ids=["eager", "captured"])
 def test_c3_step_at_the_benched_size(env, mode, tol, compiled):
     """ONE step of the benched C3 (batch 256, 32x32x3, 3-32-64-128, fc 8192-256-10): loss, every bias gradient and every
@@ -58,6 +69,10 @@ def test_c3_step_at_the_benched_size(env, mode, tol, compiled):
         rounding = None if mode == "fp32" else (lambda a: O.round_operand(a, mode))
         want_loss, nconvs, nfc1, nfc2 = MO.cnn_step(before[:3], before[3], before[4], x, t, LR, rounding)
         want = nconvs + [nfc1, nfc2]
+        want32 = want
+        if mode != "fp32":
+            _, c32, f1, f2 = MO.cnn_step(before[:3], before[3], before[4], x, t, LR, None)
+            want32 = c32 + [f1, f2]
         if compiled:
             # the recording runs one eager step first (weights move), so replay from restored weights
             xd, td = be.tensor(x).do_cache(), be.tensor(t).do_cache()
@@ -69,17 +84,33 @@ def test_c3_step_at_the_benched_size(env, mode, tol, compiled):
         else:
             got_loss = model.step(be.tensor(x), be.tensor(t))
         got = [read_pair(p) for p in model.convs] + [read_pair(model.fc1), read_pair(model.fc2)]
-        assert abs(got_loss - want_loss) <= tol * abs(want_loss), (got_loss, want_loss)
         names = ["conv1", "conv2", "conv3", "fc1", "fc2"]
-        for name, (gw, gb), (rw, rb), (ow, ob) in zip(names, got, want, before):
-            assert np.isfinite(gw).all() and np.isfinite(gb).all()
-            assert rel(ow - gw, ow - rw) <= tol, "weight gradient of %s: %g" % (name, rel(ow - gw, ow - rw))
-            assert rel(ob - gb, ob - rb) <= tol, "bias gradient of %s: %g" % (name, rel(ob - gb, ob - rb))
+        report, bad = ["loss %.8g vs %.8g" % (got_loss, want_loss)], []
+        if not abs(got_loss - want_loss) <= tol * abs(want_loss):
+            bad.append("loss")
+        for name, (gw, gb), (rw, rb), (fw, fb), (ow, ob) in zip(names, got, want, want32, before):
+            ew, eb = rel(ow - gw, ow - rw), rel(ob - gb, ob - rb)
+            if mode != "fp32":
+                e32w, e32b = rel(ow - gw, ow - fw), rel(ob - gb, ob - fb)
+                report.append("%s vs the fp32 oracle: dW rel %.3g, db rel %.3g" % (name, e32w, e32b))
+                if not (e32w <= 3 * tol and e32b <= 3 * tol):
+                    bad.append("%s against the fp32 oracle" % name)
             # no stray element: the worst entry stays within 50 x tol of the gradient's rms (catches one bad tile that
             # a Frobenius norm over 2 M entries would hide)
             g_got, g_ref = (ow - gw).astype(np.float64), (ow - rw).astype(np.float64)
             rms = np.sqrt((g_ref ** 2).mean()) + 1e-30
-            assert np.abs(g_got - g_ref).max() <= 50 * tol * rms + 4 * np.spacing(np.abs(ow).max()), name
+            worst = np.abs(g_got - g_ref).max() / rms
+            report.append("%s: dW rel %.3g, db rel %.3g, worst entry %.3g rms" % (name, ew, eb, worst))
+            if not (np.isfinite(gw).all() and np.isfinite(gb).all()):
+                bad.append(name + " not finite")
+            if not ew <= tol:
+                bad.append("weight gradient of " + name)
+            if not eb <= tol:
+                bad.append("bias gradient of " + name)
+            if not worst <= 50 * tol + 4 * np.spacing(np.abs(ow).max()) / rms:
+                bad.append("stray entry in " + name)
+        print("\n".join(report))
+        assert not bad, "%s\n%s" % (bad, "\n".join(report))
     finally:
         be.close()
 
@@ -98,9 +129,22 @@ def test_c4_model_at_width_4096_on_a_256_sample_slice(env, mode):
         got_loss = model.step(be.tensor(x), None)
         want_loss, want, _ = MO.mlp_step(before, x, None, LR, "tanh", lambda a: O.round_operand(a, mode))
         got = [w.data.flat_array().reshape(w.data.shape) for w, _ in model.layers]
-        assert abs(got_loss - want_loss) <= 2e-4 * abs(want_loss) + 1e-3, (got_loss, want_loss)
-        for i, (gw, (rw, _), (ow, _)) in enumerate(zip(got, want, before)):
-            assert rel(ow - gw, ow - rw) <= 2e-4, "weight gradient of layer %d: %g" % (i, rel(ow - gw, ow - rw))
+        want32_loss, want32, hs = MO.mlp_step(before, x, None, LR, "tanh", None)
+        # the loss is a sum of 4096 x 256 tanh outputs of mixed sign: per-element errors at the stated level add up like a
+        # random walk, so the bound is stated * sqrt(n) * rms(out)
+        out = hs[-1].astype(np.float64)
+        loss_tol = STATED[mode] * np.sqrt(out.size) * np.sqrt((out ** 2).mean())
+        report = ["loss %.8g, rounded oracle %.8g, fp32 oracle %.8g, bound %.3g" % (got_loss, want_loss, want32_loss, loss_tol)]
+        bad = []
+        if not (abs(got_loss - want_loss) <= loss_tol and abs(got_loss - want32_loss) <= 3 * loss_tol):
+            bad.append("loss")
+        for i, (gw, (rw, _), (fw, _), (ow, _)) in enumerate(zip(got, want, want32, before)):
+            e, e32 = rel(ow - gw, ow - rw), rel(ow - gw, ow - fw)
+            report.append("layer %d: dW rel %.3g (same rounding), %.3g (fp32 oracle)" % (i, e, e32))
+            if not (e <= STATED[mode] and e32 <= 3 * STATED[mode]):
+                bad.append("weight gradient of layer %d" % i)
+        print("\n".join(report))
+        assert not bad, "%s\n%s" % (bad, "\n".join(report))
     finally:
         be.close()
 
