@@ -106,7 +106,8 @@ __global__ void __launch_bounds__(256) conv_pack_weights_kernel(const float *__r
 constexpr int kDirectWarps = 8;
 
 template <int CIN, int MODE>
-__device__ __forceinline__ void direct_fill_patch(float *sx, const float *__restrict__ x, long long b, int y0, int R, int H, int W) {
+__device__ __forceinline__ void direct_fill_patch(float *sx, const float *__restrict__ x, long long b, int y0, int R, int H, int W,
+                                                  int stride) {
   const int row_len = (W + 2) * CIN;
   const int total = (R + 2) * row_len;
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
@@ -114,7 +115,9 @@ __device__ __forceinline__ void direct_fill_patch(float *sx, const float *__rest
     const int col = rem / CIN, c = rem - col * CIN;
     const int gy = y0 + r - 1, gx = col - 1;
     float v = 0.f;
-    if (gy >= 0 && gy < H && gx >= 0 && gx < W) v = round_operand<MODE>(__ldg(x + ((b * H + gy) * (long long)W + gx) * CIN + c));
+    // the source is [B, H*stride, W*stride, CIN] sampled at `stride` (the `scale` down-sampling view read in place)
+    if (gy >= 0 && gy < H && gx >= 0 && gx < W)
+      v = round_operand<MODE>(__ldg(x + (((b * H + gy) * stride) * (long long)(W * stride) + (long long)gx * stride) * CIN + c));
     sx[i] = v;
   }
 }
@@ -122,7 +125,7 @@ __device__ __forceinline__ void direct_fill_patch(float *sx, const float *__rest
 template <int CIN, int MODE>
 __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_fwd_kernel(const float *__restrict__ x, const float *__restrict__ w,
                                                                             const float *__restrict__ bias, float *__restrict__ out,
-                                                                            int B, int H, int W, int Cout, int act, int R) {
+                                                                            int B, int H, int W, int Cout, int act, int R, int stride) {
   extern __shared__ float sx[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float wr[9 * CIN];
@@ -136,7 +139,7 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_fwd_kernel(cons
     const int y0 = (int)(t - b * bands) * R;
     const int rows = min(R, H - y0);
     __syncthreads();                          // the previous band has been consumed
-    direct_fill_patch<CIN, MODE>(sx, x, b, y0, R, H, W);
+    direct_fill_patch<CIN, MODE>(sx, x, b, y0, R, H, W, stride);
     __syncthreads();
     for (int p = warp; p < rows * W; p += kDirectWarps) {
       const int yy = p / W, xx = p - yy * W;
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_fwd_kernel(cons
 template <int CIN, int MODE>
 __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const float *__restrict__ x, const float *__restrict__ dz,
                                                                            float *__restrict__ partial, int B, int H, int W, int Cout,
-                                                                           int R) {
+                                                                           int R, int stride) {
   extern __shared__ float sx[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float acc[9 * CIN];
@@ -184,7 +187,7 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const
     const int y0 = (int)(t - b * bands) * R;
     const int rows = min(R, H - y0);
     __syncthreads();
-    direct_fill_patch<CIN, MODE>(sx, x, b, y0, R, H, W);
+    direct_fill_patch<CIN, MODE>(sx, x, b, y0, R, H, W, stride);
     __syncthreads();
     for (int p = warp; p < rows * W; p += kDirectWarps) {
       const int yy = p / W, xx = p - yy * W;
@@ -236,16 +239,16 @@ bool conv_direct_supported(int cin, int cout) { return cin >= 1 && cin <= 4 && c
 
 template <int MODE>
 static int launch_direct_fwd_mode(dls_ctx *ctx, cudaStream_t st, const float *x, const float *w, const float *bias, float *out, int B,
-                                  int H, int W, int cin, int cout, int act) {
+                                  int H, int W, int cin, int cout, int act, int stride) {
   const int R = direct_rows(H, W, cin);
   const size_t smem = (size_t)(R + 2) * (W + 2) * cin * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
   const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 8);
   switch (cin) {
-    case 1: conv_direct_fwd_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R); break;
-    case 2: conv_direct_fwd_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R); break;
-    case 3: conv_direct_fwd_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R); break;
-    default: conv_direct_fwd_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R); break;
+    case 1: conv_direct_fwd_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
+    case 2: conv_direct_fwd_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
+    case 3: conv_direct_fwd_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
+    default: conv_direct_fwd_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
   }
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
@@ -253,16 +256,16 @@ static int launch_direct_fwd_mode(dls_ctx *ctx, cudaStream_t st, const float *x,
 }
 
 int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, const float *w, const float *bias, float *out, int B,
-                           int H, int W, int cin, int cout, int act) {
+                           int H, int W, int cin, int cout, int act, int stride) {
   cudaStream_t st = ctx->streams[stream];
-  if (mode == DLS_GEMM_TF32) return launch_direct_fwd_mode<DLS_GEMM_TF32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act);
-  if (mode == DLS_GEMM_BF16) return launch_direct_fwd_mode<DLS_GEMM_BF16>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act);
-  return launch_direct_fwd_mode<DLS_GEMM_FP32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act);
+  if (mode == DLS_GEMM_TF32) return launch_direct_fwd_mode<DLS_GEMM_TF32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride);
+  if (mode == DLS_GEMM_BF16) return launch_direct_fwd_mode<DLS_GEMM_BF16>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride);
+  return launch_direct_fwd_mode<DLS_GEMM_FP32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride);
 }
 
 template <int MODE>
 static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                                 int cout) {
+                                 int cout, int stride) {
   cudaStream_t st = ctx->streams[stream];
   const int R = direct_rows(H, W, cin);
   const int K = 9 * cin;
@@ -275,10 +278,10 @@ static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const
   if (rc) return rc;
   float *partial = (float *)scratch.ptr;
   switch (cin) {
-    case 1: conv_direct_dw_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R); break;
-    case 2: conv_direct_dw_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R); break;
-    case 3: conv_direct_dw_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R); break;
-    default: conv_direct_dw_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R); break;
+    case 1: conv_direct_dw_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
+    case 2: conv_direct_dw_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
+    case 3: conv_direct_dw_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
+    default: conv_direct_dw_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
@@ -292,10 +295,10 @@ static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const
 }
 
 int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                          int cout) {
-  if (mode == DLS_GEMM_TF32) return launch_direct_dw_mode<DLS_GEMM_TF32>(ctx, stream, x, dz, dw, B, H, W, cin, cout);
-  if (mode == DLS_GEMM_BF16) return launch_direct_dw_mode<DLS_GEMM_BF16>(ctx, stream, x, dz, dw, B, H, W, cin, cout);
-  return launch_direct_dw_mode<DLS_GEMM_FP32>(ctx, stream, x, dz, dw, B, H, W, cin, cout);
+                          int cout, int stride) {
+  if (mode == DLS_GEMM_TF32) return launch_direct_dw_mode<DLS_GEMM_TF32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride);
+  if (mode == DLS_GEMM_BF16) return launch_direct_dw_mode<DLS_GEMM_BF16>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride);
+  return launch_direct_dw_mode<DLS_GEMM_FP32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride);
 }
 
 int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
@@ -433,13 +436,8 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
   rc = new_buf(ctx, batch * h * wd * cout, stream, &o);
   if (rc) return rc;
   if (conv_direct_supported((int)cin, (int)cout)) {
-    if (stride != 1) {
-      set_error("dls_conv3x3_forward: the direct first-layer kernel reads its input unsampled (in_stride must be 1)");
-      rc = DLS_ERR_UNSUPPORTED;
-    } else {
-      rc = launch_conv_direct_fwd(ctx, stream, mode, x->ptr, w->ptr, bias ? bias->ptr : nullptr, o->ptr, (int)batch, (int)h, (int)wd,
-                                  (int)cin, (int)cout, act);
-    }
+    rc = launch_conv_direct_fwd(ctx, stream, mode, x->ptr, w->ptr, bias ? bias->ptr : nullptr, o->ptr, (int)batch, (int)h, (int)wd,
+                                (int)cin, (int)cout, act, stride);
   } else {
     const void *xa, *wf, *wb;
     int cp;
@@ -515,12 +513,7 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
   rc = new_buf(ctx, 9 * cin * cout, stream, &o);
   if (rc) return rc;
   if (conv_direct_supported((int)cin, (int)cout)) {
-    if (stride != 1) {
-      set_error("dls_conv3x3_backward_weights: the direct first-layer kernel reads its input unsampled (in_stride must be 1)");
-      rc = DLS_ERR_UNSUPPORTED;
-    } else {
-      rc = launch_conv_direct_dw(ctx, stream, mode, x->ptr, dz->ptr, o->ptr, (int)batch, (int)h, (int)wd, (int)cin, (int)cout);
-    }
+    rc = launch_conv_direct_dw(ctx, stream, mode, x->ptr, dz->ptr, o->ptr, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, stride);
   } else {
     const void *xa, *da;
     int cxp, cdp;

@@ -7,9 +7,9 @@ down-sampling backward gathers cross image boundaries thousands of times, and an
 output tiles (7 waves, grouped raster wrap-around).
 
 Bars.  fp32 mode: 1e-5 relative (north_star's reductions bar) -- this is the run that proves the graph, the gathers, the
-reductions and the split-K bookkeeping at scale.  Tensor-core modes: every gradient within 3 x the mode's stated bound
-(tf32 1e-3, bf16 4e-3; a gradient chains several rounded contractions) of the fp32 oracle, and within 1 x the stated
-bound of the oracle evaluated with the same operand rounding.  The second bar cannot be tightened at these sizes the way
+reductions and the split-K bookkeeping at scale.  Tensor-core modes: every gradient within 1 x the stated bound (tf32 1e-3,
+bf16 4e-3) of the oracle evaluated with the same operand rounding; the distance to the fp32 oracle is reported (C3, a ReLU
+network: mask flips, see the comment in the test) or held to 3 x the stated bound (C4, tanh).  The first bar cannot be tightened at these sizes the way
 the small model tests (2e-4) and the single-contraction tests (2e-6 of sum |a||b|, below and in test_gpu_gemm.py) do:
 two evaluations that differ only in fp32 accumulation order (~1e-6 relative after cancellation) re-round a fraction
 ~1e-6 / ulp of each layer's activations to the neighbouring bf16 / tf32 value, a wide next layer sums thousands of them,
@@ -93,7 +93,12 @@ def test_c3_step_at_the_benched_size(env, mode, tol, compiled):
             if mode != "fp32":
                 e32w, e32b = rel(ow - gw, ow - fw), rel(ob - gb, ob - fb)
                 report.append("%s vs the fp32 oracle: dW rel %.3g, db rel %.3g" % (name, e32w, e32b))
-                if not (e32w <= 3 * tol and e32b <= 3 * tol):
+                # reported, and asserted only as a gross-error check: against UNROUNDED arithmetic a ReLU network does not
+                # stay within a multiple of the per-contraction bound -- a pre-activation perturbed by 2^-11 (tf32) flips the
+                # mask of the units nearest zero, and each flipped unit changes its gradient path by 100 %; measured on a
+                # B200 in tf32: fc2 3e-4, fc1 2.4e-3, conv3 6e-3, conv2 1e-2, conv1 1.8e-2 (growing layer by layer on the
+                # way back), while the same step agrees with the operand-rounded oracle to 7e-4
+                if not (e32w <= 0.25 and e32b <= 0.25):
                     bad.append("%s against the fp32 oracle" % name)
             # no stray element: the worst entry stays within 50 x tol of the gradient's rms (catches one bad tile that
             # a Frobenius norm over 2 M entries would hide)

@@ -129,11 +129,12 @@ def test_downsampled_source_is_read_in_place(env, backend):
     launches0 = be.stats()["kernel_launches"]
     y = be.conv3x3_forward(view, wd).flat_array()
     fwd_launches = be.stats()["kernel_launches"] - launches0
-    dw = be.conv3x3_backward_weights(view, dzd).flat_array()
     y_ref = be.conv3x3_forward(be.tensor(half), be.tensor(wt)).flat_array()
-    dw_ref = be.conv3x3_backward_weights(be.tensor(half), be.tensor(dz)).flat_array()
     assert (y.view(np.uint32) == y_ref.view(np.uint32)).all()
-    assert (dw.view(np.uint32) == dw_ref.view(np.uint32)).all()
+    if be.conv3x3_supported("backward_weights", h, w, cin, cout):
+        dw = be.conv3x3_backward_weights(view, dzd).flat_array()
+        dw_ref = be.conv3x3_backward_weights(be.tensor(half), be.tensor(dz)).flat_array()
+        assert (dw.view(np.uint32) == dw_ref.view(np.uint32)).all()
     assert fwd_launches <= 3                   # stage the sampled operand, pack the weights, the convolution
     r = lambda a: O.round_operand(a, mode)
     want = MO.conv_forward(half, wt, np.zeros(cout, np.float32), r)
@@ -155,7 +156,9 @@ def test_reference_convolution_known_answer(env, backend):
     bias = rng.standard_normal(16).astype(np.float32)
     P = Plugins(backend=be)
     L = Layers(P)
-    out = L.conv2d_3x3(be.tensor(x), P.weight(be.tensor(wt)), P.weight(be.tensor(bias)), "relu").predict().run().flat_array()
+    # the forward value is pinned only while the Do is open (TL:57-68): read it inside
+    out = L.conv2d_3x3(be.tensor(x), P.weight(be.tensor(wt)), P.weight(be.tensor(bias)), "relu").predict().map(
+        lambda t: t.flat_array()).run()
     r = lambda a: O.round_operand(a, mode)
     want = np.maximum(MO.conv_forward(x, wt, bias, r), 0.0)
     scale = MO.conv_forward(np.abs(x), np.abs(wt), np.abs(bias), r) + 1.0
