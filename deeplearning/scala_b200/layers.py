@@ -97,6 +97,101 @@ class Layers:
         """`Tensor.max(x, fill 0)`; the derivative 1[y > 0] is `min(y * FLT_MAX, 1)` (the algebra has no comparison)."""
         return self._unary(a, lambda x: T.maximum(x, x.backend.scalar(0.0)), lambda d, x, y: d * relu_mask(y), pin=True)
 
+    def abs(self, a) -> TensorLayer:
+        """FloatLayers.scala:239-256 per element: negative inputs negate value and delta, everything else (0, +0, NaN)
+        passes through -- the factor is 1 - 2 * 1[x < 0]."""
+        return self._unary(a, T.abs_, lambda d, x, y: d * (1.0 - positive_mask(-x) * 2.0))
+
+    def sqrt(self, a) -> TensorLayer:
+        """FloatLayers.scala:258-272: delta * 0.5 / sqrt(x)."""
+        return self._unary(a, T.sqrt, lambda d, x, y: d * 0.5 / y, pin=True)
+
+    def divide(self, a, b) -> TensorLayer:
+        """FloatLayers.scala:133-148: delta_a = delta / b, delta_b = -delta * a / (b * b), each summed back to its
+        operand's shape like `+` and `*` (TL:110-162)."""
+        def build(tapes):
+            t0, t1 = tapes
+            A, B = t0.data, t1.data
+            s0, s1 = list(A.shape), list(B.shape)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: broadcast_then_sum(d / B, s0)))
+                    t1.backward(do_delta.map(lambda d: broadcast_then_sum(-d * A / (B * B), s1)))
+                return run
+            return A / B, backward
+        return self._lazy([a, b], build)
+
+    def min(self, a, b) -> TensorLayer:
+        """FloatLayers.scala:150-165 per element: the delta goes to operand 0 where a < b, to operand 1 everywhere else
+        (ties and NaN included, as `if (data0 < data1) tape0 else tape1` does)."""
+        return self._select(a, b, T.minimum, lambda A, B: positive_mask(B - A))
+
+    def max(self, a, b) -> TensorLayer:
+        """FloatLayers.scala:167-182 per element: operand 0 where a > b, operand 1 everywhere else."""
+        return self._select(a, b, T.maximum, lambda A, B: positive_mask(A - B))
+
+    def _select(self, a, b, pick, first_mask) -> TensorLayer:
+        def build(tapes):
+            t0, t1 = tapes
+            A, B = t0.data, t1.data
+            s0, s1 = list(A.shape), list(B.shape)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    m = first_mask(A, B)
+                    t0.backward(do_delta.map(lambda d: broadcast_then_sum(d * m, s0)))
+                    t1.backward(do_delta.map(lambda d: broadcast_then_sum(d * (1.0 - m), s1)))
+                return run
+            return pick(A, B), backward
+        return self._lazy([a, b], build)
+
+    def sum(self, a) -> TensorLayer:
+        """`Tensor.sum` (Tensors:673-766) as a layer: one scalar out, and every element receives the scalar delta
+        (d out / d x_i = 1), i.e. the delta broadcast to the operand's shape."""
+        def build(tapes):
+            (t0,) = tapes
+            shape0 = list(t0.data.shape)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: d.broadcast(shape0)))
+                return run
+            return t0.data.sum(), backward
+        return self._pinned([a], build)
+
+    def permute(self, a, dimensions) -> TensorLayer:
+        """`Tensor.permute` (Tensors:1008-1024) as a layer; the delta travels through the inverse permutation."""
+        dimensions = [int(d) for d in dimensions]
+        inverse = [dimensions.index(i) for i in range(len(dimensions))]
+
+        def build(tapes):
+            (t0,) = tapes
+            out_shape = [t0.data.shape[d] for d in dimensions]
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: d.broadcast(out_shape).permute(inverse)))
+                return run
+            return t0.data.permute(dimensions), backward
+        return self._lazy([a], build)
+
+    def broadcast(self, a, new_shape) -> TensorLayer:
+        """`Tensor.broadcast` (Tensors:893-945, left-aligned) as a layer; the delta is summed back over the broadcast
+        dimensions (`sumAs`, TL:124-162)."""
+        new_shape = [int(s) for s in new_shape]
+
+        def build(tapes):
+            (t0,) = tapes
+            shape0 = list(t0.data.shape)
+
+            def backward(_):
+                def run(do_delta: Do):
+                    t0.backward(do_delta.map(lambda d: broadcast_then_sum(d.broadcast(new_shape), shape0)))
+                return run
+            return t0.data.broadcast(new_shape), backward
+        return self._lazy([a], build)
+
     def _unary(self, a, forward, delta, pin: bool = False) -> TensorLayer:
         def build(tapes):
             (t0,) = tapes
@@ -296,6 +391,13 @@ class Layers:
 def relu_mask(y):
     """1[y > 0] for y = max(x, 0) >= 0, spelled with the operators the algebra has (Tensors:546-558)."""
     return T.minimum(y * _BIG, y.backend.scalar(1.0))
+
+
+def positive_mask(t):
+    """1[t > 0] for any finite or infinite t (0 for t <= 0, -0 and NaN-free inputs): clamp at 0, then scale twice so even
+    the smallest subnormal (1.4e-45 * FLT_MAX = 4.8e-7, * FLT_MAX again = 1.6e32) saturates at 1."""
+    zero, one = t.backend.scalar(0.0), t.backend.scalar(1.0)
+    return T.minimum(T.minimum(T.maximum(t, zero) * _BIG, one) * _BIG, one)
 
 
 _MASKS = {}

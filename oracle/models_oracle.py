@@ -168,3 +168,70 @@ def cnn_step(convs, fc1, fc2, x, target, learning_rate, operand_rounding=None):
         new_convs[i] = (sgd(convs[i][0], dw), sgd(convs[i][1], db))
         d = dx
     return loss, new_convs, new_fc1, new_fc2
+
+
+# ---- the remaining differentiable operations of SURVEY 8(f).2 (mirror of FloatLayers.scala:133-274 per element) -------------
+def left_broadcast(a: np.ndarray, shape: Sequence[int]) -> np.ndarray:
+    """Tensor.broadcast (Tensors:893-945): dimensions are aligned on the LEFT, missing trailing ones are added."""
+    a = np.asarray(a)
+    return np.broadcast_to(a.reshape(a.shape + (1,) * (len(shape) - a.ndim)), tuple(shape))
+
+
+def sum_as(d: np.ndarray, shape: Sequence[int]) -> np.ndarray:
+    """TL:124-162: sum a delta back over the dimensions that were broadcast (left-aligned), fp64 accumulation."""
+    d = np.asarray(d, dtype=np.float64)
+    shape = tuple(shape)
+    if d.ndim > len(shape):
+        d = d.sum(axis=tuple(range(len(shape), d.ndim)))
+    axes = tuple(i for i, s in enumerate(shape) if s == 1 and d.shape[i] != 1)
+    if axes:
+        d = d.sum(axis=axes, keepdims=True)
+    return f32(d)
+
+
+OP_RULES = {
+    # name: (forward(a, b) -> y, backward(delta, a, b, y) -> (delta_a, delta_b)); every product / quotient is one fp32 rounding
+    "divide": (lambda a, b: f32(a / b),
+               lambda d, a, b, y: (f32(d / b), f32(f32(f32(-d * a)) / f32(b * b)))),            # FloatLayers:133-148
+    "min": (lambda a, b: np.minimum(a, b),
+            lambda d, a, b, y: (f32(d * (a < b)), f32(d * ~(a < b)))),                          # FloatLayers:150-165
+    "max": (lambda a, b: np.maximum(a, b),
+            lambda d, a, b, y: (f32(d * (a > b)), f32(d * ~(a > b)))),                          # FloatLayers:167-182
+    "abs": (lambda a, b=None: np.abs(a),
+            lambda d, a, b, y: (f32(np.where(a < 0, -d, d)), None)),                            # FloatLayers:239-256
+    "sqrt": (lambda a, b=None: f32(np.sqrt(a.astype(np.float64))),
+             lambda d, a, b, y: (f32(f32(d * F32(0.5)) / y), None)),                            # FloatLayers:258-272
+}
+
+
+def ops_step(a, b, c, learning_rate):
+    """One SGD step of a composite that uses every operation of 8(f).2 once (a, b: [n, m]; c: [n], broadcast on the left):
+         q = a / b;  r = sqrt(abs(q) + 0.5);  m = max(a, broadcast(c));  k = min(b, m);  p = permute(r * k, [1, 0])
+         loss = sum(p * p)
+    Returns (loss, new_a, new_b, new_c, p)."""
+    a, b, c = f32(a), f32(b), f32(c)
+    lr = F32(learning_rate)
+    q = OP_RULES["divide"][0](a, b)
+    ab = OP_RULES["abs"][0](q)
+    s = f32(ab + F32(0.5))
+    r = OP_RULES["sqrt"][0](s)
+    cb = np.ascontiguousarray(left_broadcast(c, a.shape))
+    m = OP_RULES["max"][0](a, cb)
+    k = OP_RULES["min"][0](b, m)
+    rk = f32(r * k)
+    p = np.ascontiguousarray(rk.T)
+    pp = f32(p * p)
+    loss = float(pp.astype(np.float64).sum())
+    # backward: the seed is the scalar 1 (TL:55), `sum` hands it to every element
+    d_pp = np.ones_like(pp)
+    d_p = f32(f32(d_pp * p) + f32(d_pp * p))                 # `*` sends delta * other to each operand (TL:291-340); both are p
+    d_rk = np.ascontiguousarray(d_p.T)                       # inverse permutation
+    d_r, d_k = f32(d_rk * k), f32(d_rk * r)
+    d_b1, d_m = OP_RULES["min"][1](d_k, b, m, k)
+    d_a1, d_cb = OP_RULES["max"][1](d_m, a, cb, m)
+    d_c = sum_as(d_cb, c.shape + (1,) * (a.ndim - c.ndim)).reshape(c.shape)
+    d_s, _ = OP_RULES["sqrt"][1](d_r, s, None, r)
+    d_q, _ = OP_RULES["abs"][1](d_s, q, None, ab)
+    d_a2, d_b2 = OP_RULES["divide"][1](d_q, a, b, q)
+    d_a, d_b = f32(d_a1 + d_a2), f32(d_b1 + d_b2)
+    return loss, f32(a - f32(d_a * lr)), f32(b - f32(d_b * lr)), f32(c - f32(d_c * lr)), p

@@ -101,3 +101,25 @@ def test_data_parallel_shards_sum_to_the_full_batch_step():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(w <= 1e-5 for _, w in results), results
+
+
+def test_elementwise_rule_oracle_matches_finite_differences():
+    """divide / min / max / abs / sqrt / sum / permute / broadcast -- the composite of MO.ops_step, pinned by
+    central finite differences (inputs kept away from the kinks of abs / min / max and from b = 0)."""
+    rng = np.random.RandomState(3)
+    a = (rng.rand(4, 6).astype(np.float32) + 0.5) * np.where(rng.rand(4, 6) < 0.5, -1, 1).astype(np.float32)
+    b = rng.rand(4, 6).astype(np.float32) + 0.7
+    c = (rng.rand(4).astype(np.float32) - 0.5) * 2
+    # keep every comparison decided by a margin larger than the finite-difference step
+    assert np.abs(a - c[:, None]).min() > 0.02 and np.abs(b - np.maximum(a, c[:, None])).min() > 0.02
+    _, na, nb, nc, _ = MO.ops_step(a, b, c, LR)
+    fd_check(lambda: MO.ops_step(a, b, c, LR)[0], [a, b, c], [na, nb, nc], picks=8, eps=2e-3, tol=3e-2)
+
+
+def test_left_broadcast_and_sum_as_are_adjoint():
+    rng = np.random.RandomState(4)
+    v = rng.randn(3).astype(np.float32)
+    d = rng.randn(3, 5, 2).astype(np.float32)
+    lhs = float((MO.left_broadcast(v, d.shape).astype(np.float64) * d).sum())
+    rhs = float((v.astype(np.float64) * MO.sum_as(d, (3,)).astype(np.float64)).sum())
+    assert abs(lhs - rhs) <= 1e-5 * (abs(lhs) + 1)
