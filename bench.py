@@ -403,7 +403,7 @@ def run_reference(args, rank, world):
         sample = what + (" (the whole per-GPU batch)" if batch == full else " (a %d-sample slice of the %d batch)" % (batch, full)) + \
             "; numpy + BLAS on %d host threads, fp64 accumulation; last loss %.6g" % (cores, loss)
         metric, unit, cfg, dtype = METRIC, "samples/s", train_config(workload, world, args.gemm_mode, args.strong), "f32 (fp64 accumulate)"
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong" if (args.strong and workload == "c5") else "weak", "vs_baseline": None, "dtype": dtype, "data": "synthetic",
@@ -515,11 +515,25 @@ def resolve_workload(args, world):
     return w
 
 
+_REAL_STDOUT = None
+
+
 def setup_nccl_logging():
-    """stdout carries exactly one JSON line, but NCCL prints its INFO lines (version banner, `nranks`) to stdout.  Keep the
-    level the caller asked for and only move the text: to the caller's NCCL_DEBUG_FILE if there is one, else to stderr."""
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE") and not os.environ.get("NCCL_DEBUG_FILE"):
-        os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
+    """stdout carries exactly one JSON line, but NCCL prints to the process's stdout at every level from WARN up (the
+    version banner) and at INFO the `nranks` lines the driver looks for.  Nothing is muted or re-levelled: file descriptor 1
+    is pointed at stderr for the rest of the run (so NCCL's and any other native library's stdout text lands on stderr, or in
+    the caller's NCCL_DEBUG_FILE if one is set), and the JSON line is written to the original stdout kept in `_REAL_STDOUT`."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line: str):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(line + "\n")
+    out.flush()
 
 
 def main():
@@ -556,8 +570,7 @@ def main():
     workload = resolve_workload(args, world)
     out = main_c2(args, rank, world, local, dist) if workload == "c2" else main_train(args, workload, rank, world, local, dist)
     if rank == 0:
-        print(json.dumps(out))
-        sys.stdout.flush()
+        emit(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
 
@@ -591,7 +604,7 @@ def main_train(args, workload, rank, world, local, dist):
            "tflops_per_gpu": r["tflops"], "loss": {"first": r["first_loss"], "last": r["last_loss"]}}
     if "exchange" in r:
         out["config"]["exchange_detail"] = r["exchange"]
-        out["nccl"] = {"communicator_ranks": r.get("nccl_ranks"), "log": os.environ.get("NCCL_DEBUG_FILE") or "NCCL default (stdout)"}
+        out["nccl"] = {"communicator_ranks": r.get("nccl_ranks"), "log": os.environ.get("NCCL_DEBUG_FILE") or "stderr (fd 1 is pointed at stderr; stdout carries only this line)"}
     if workload in ("c3", "c5"):
         nbytes = bench_train.c3_algorithmic_bytes(r["batch_per_gpu"])
         achieved = nbytes / (r["ms_per_step"] / 1e3) / 1e9

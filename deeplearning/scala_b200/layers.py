@@ -49,8 +49,11 @@ class Layers:
                 tape = Tape(cached if view is None else view(cached, tapes), backward(cached))
 
                 def release():
-                    cached.release()
+                    # CumulativeTensorLayers flush their accumulators on release, innermost first: a weight's lazy delta
+                    # (`d * 0.5 / y`) is materialised after this layer's Do has closed, so there the pinned value and the
+                    # owned buffers are left to the host collector instead of being freed at this point
                     if not P.cumulative:
+                        cached.release()
                         while owned:
                             owned.pop().release()
                 return tape, release
