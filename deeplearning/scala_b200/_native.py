@@ -42,7 +42,7 @@ class GemmOpts(C.Structure):
 
 
 class ConvOpts(C.Structure):
-    _fields_ = [("mode", C.c_int32), ("activation", C.c_int32), ("in_stride", C.c_int32), ("reserved", C.c_int32)]
+    _fields_ = [("mode", C.c_int32), ("activation", C.c_int32), ("in_stride", C.c_int32), ("dz_stride", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -15,6 +15,8 @@
 // contraction of the mode), fp32 accumulation.
 #include <cuda_bf16.h>
 
+#include <climits>
+
 #include "common.h"
 #include "gemm_tc.h"
 
@@ -34,11 +36,14 @@ __device__ __forceinline__ float round_operand(float x) {
   return x;
 }
 
-// ---- staging: fp32 NHWC [B, H*s, W*s, C] sampled at stride s (the `scale` down-sampling view, Tensors:950-965, read in
-// place) -> operand copy [B, H, W, Cp] (bf16, or tf32-rounded fp32), pad channels zero.  One thread per 4 channels.
+// ---- staging: fp32 NHWC -> operand copy [B, H, W, Cp] (bf16, or tf32-rounded fp32), pad channels zero.  One thread per 4
+// channels.  Two read patterns besides the dense one, both views the reference would evaluate lazily (Tensors:950-965):
+//   stride > 1: the source is [B, H*stride, W*stride, C] sampled at `stride` (a `scale` down-sampling read in place);
+//   up > 1:     the source is [B, H/up, W/up, C] and stands for a tensor that is zero except at (up*y, up*x) -- the delta
+//               that a down-sampling layer hands back (its `scale` up, masked to the sampled positions).
 template <bool TF32>
 __global__ void __launch_bounds__(256) conv_stage_act_kernel(const float *__restrict__ in, void *__restrict__ out, long long pixels,
-                                                             int H, int W, int C, int Cp, int stride) {
+                                                             int H, int W, int C, int Cp, int stride, int up) {
   const int groups = Cp >> 2;
   const long long total = pixels * groups;
   const bool vec = (C & 3) == 0;
@@ -49,15 +54,24 @@ __global__ void __launch_bounds__(256) conv_stage_act_kernel(const float *__rest
     const long long q = p / W;
     const int y = (int)(q % H);
     const long long b = q / H;
-    const float *src = in + (((b * H + y) * stride) * (long long)(W * stride) + (long long)x * stride) * C + c;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (vec) {
-      if (c < C) v = __ldg(reinterpret_cast<const float4 *>(src));
+    const float *src;
+    bool live = c < C;
+    if (up > 1) {
+      live = live && (y % up) == 0 && (x % up) == 0;
+      src = in + ((b * (H / up) + y / up) * (long long)(W / up) + x / up) * C + c;
     } else {
-      if (c < C) v.x = __ldg(src);
-      if (c + 1 < C) v.y = __ldg(src + 1);
-      if (c + 2 < C) v.z = __ldg(src + 2);
-      if (c + 3 < C) v.w = __ldg(src + 3);
+      src = in + (((b * H + y) * stride) * (long long)(W * stride) + (long long)x * stride) * C + c;
+    }
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (live) {
+      if (vec) {
+        v = __ldg(reinterpret_cast<const float4 *>(src));
+      } else {
+        v.x = __ldg(src);
+        if (c + 1 < C) v.y = __ldg(src + 1);
+        if (c + 2 < C) v.z = __ldg(src + 2);
+        if (c + 3 < C) v.w = __ldg(src + 3);
+      }
     }
     if (TF32) {
       v.x = round_tf32_rna(v.x);
@@ -100,23 +114,35 @@ __global__ void __launch_bounds__(256) conv_pack_weights_kernel(const float *__r
 }
 
 // ---- first layer, direct ---------------------------------------------------------------------------------------------------
-// A CTA owns a band of R output rows of one image: the (R + 2) x (W + 2) x CIN input patch (zero ring = the 'same' padding,
-// operands rounded on the way in) sits in shared memory; lane = output channel, so every weight lives in a register, every
-// input value is a shared-memory broadcast and every output pixel leaves as one coalesced 128-byte store.
+// Cin <= 4: 6..16-byte pixel rows are below TMA's 16-byte granule and the layer is HBM bound by two orders of magnitude, so
+// it gets kernels of its own.  A CTA owns a band of R output rows of one image: the (R + 2) x (W + 2) input patch (zero ring
+// = the 'same' padding, channels padded to 4, operands rounded to the contraction mode on the way in) sits in shared memory.
+// The arithmetic is warp-level mma.sync.m16n8k8 (tf32 inputs, fp32 accumulate; a bf16-rounded value is a valid tf32, so one
+// instruction serves both modes): with the CUDA cores the layer needs 27 FFMA + 27 shared-memory loads per pixel and warp and
+// is issue bound at 8x its HBM time; as 16-pixel x 32-channel x 40-tap MMA tiles it needs ~6 instructions per pixel.
+// k index of the implicit im2col row: k = tap * 4 + c (c = 3 and taps 9.. are zero).
 constexpr int kDirectWarps = 8;
+constexpr int kDirectK = 40;                  // 9 taps x 4 padded channels, rounded up to 5 k-steps of 8
 
+__device__ __forceinline__ void mma_tf32_16x8x8(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// patch[r][col][4]: r = 0 .. R+1 <-> input row y0 + r - 1, col = 0 .. W+1 <-> input column col - 1.  The source is
+// [B, H*stride, W*stride, CIN] sampled at `stride` (the `scale` down-sampling view read in place).
 template <int CIN, int MODE>
 __device__ __forceinline__ void direct_fill_patch(float *sx, const float *__restrict__ x, long long b, int y0, int R, int H, int W,
                                                   int stride) {
-  const int row_len = (W + 2) * CIN;
+  const int row_len = (W + 2) * 4;
   const int total = (R + 2) * row_len;
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const int r = i / row_len, rem = i - r * row_len;
-    const int col = rem / CIN, c = rem - col * CIN;
+    const int col = rem >> 2, c = rem & 3;
     const int gy = y0 + r - 1, gx = col - 1;
     float v = 0.f;
-    // the source is [B, H*stride, W*stride, CIN] sampled at `stride` (the `scale` down-sampling view read in place)
-    if (gy >= 0 && gy < H && gx >= 0 && gx < W)
+    if (c < CIN && gy >= 0 && gy < H && gx >= 0 && gx < W)
       v = round_operand<MODE>(__ldg(x + (((b * H + gy) * stride) * (long long)(W * stride) + (long long)gx * stride) * CIN + c));
     sx[i] = v;
   }
@@ -128,109 +154,211 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_fwd_kernel(cons
                                                                             int B, int H, int W, int Cout, int act, int R, int stride) {
   extern __shared__ float sx[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float wr[9 * CIN];
+  const int g = lane >> 2, t = lane & 3;
+  // B fragments of the whole [40 x 32] weight matrix stay in registers: b0 = (k = 8 ks + t, n = 8 nt + g), b1 = (k + 4, n)
+  uint32_t bw[kDirectK / 8][4][2];
 #pragma unroll
-  for (int k = 0; k < 9 * CIN; ++k) wr[k] = lane < Cout ? round_operand<MODE>(__ldg(w + k * Cout + lane)) : 0.f;
-  const float bv = (bias && lane < Cout) ? __ldg(bias + lane) : 0.f;
+  for (int ks = 0; ks < kDirectK / 8; ++ks)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int tap = 2 * ks + j, n = nt * 8 + g;
+        float v = 0.f;
+        if (tap < 9 && t < CIN && n < Cout) v = round_operand<MODE>(__ldg(w + (tap * CIN + t) * Cout + n));
+        bw[ks][nt][j] = __float_as_uint(v);
+      }
+  float bv[4][2];
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) bv[nt][j] = (bias && nt * 8 + 2 * t + j < Cout) ? __ldg(bias + nt * 8 + 2 * t + j) : 0.f;
   const int bands = (H + R - 1) / R;
-  const int row_len = (W + 2) * CIN;
-  for (long long t = blockIdx.x; t < (long long)B * bands; t += gridDim.x) {
-    const long long b = t / bands;
-    const int y0 = (int)(t - b * bands) * R;
+  const int prow = (W + 2) * 4;
+  for (long long band = blockIdx.x; band < (long long)B * bands; band += gridDim.x) {
+    const long long b = band / bands;
+    const int y0 = (int)(band - b * bands) * R;
     const int rows = min(R, H - y0);
     __syncthreads();                          // the previous band has been consumed
     direct_fill_patch<CIN, MODE>(sx, x, b, y0, R, H, W, stride);
     __syncthreads();
-    for (int p = warp; p < rows * W; p += kDirectWarps) {
-      const int yy = p / W, xx = p - yy * W;
-      float a0 = 0.f, a1 = 0.f;
+    const int npx = rows * W;
+    for (int tile = warp; tile * 16 < npx; tile += kDirectWarps) {
+      // A fragment rows: pixels p0 = 16 tile + g and p0 + 8 of the band
+      const int p0 = tile * 16 + g, p1 = p0 + 8;
+      const int q0 = min(p0, npx - 1), q1 = min(p1, npx - 1);
+      const int yy0 = q0 / W, xx0 = q0 - yy0 * W, yy1 = q1 / W, xx1 = q1 - yy1 * W;
+      const float *a0p = sx + ((yy0 + 2) * (W + 2) + xx0 + 2) * 4 + t;
+      const float *a1p = sx + ((yy1 + 2) * (W + 2) + xx1 + 2) * 4 + t;
+      float acc[4][4];
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        // tap (ky, kx) reads input (y - ky + 1, x - kx + 1): patch row yy - ky + 2, patch column xx - kx + 2
-        const float *prow = sx + (yy - ky + 2) * row_len;
+      for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const float *pp = prow + (xx - kx + 2) * CIN;
+        for (int j = 0; j < 4; ++j) acc[nt][j] = 0.f;
 #pragma unroll
-          for (int c = 0; c < CIN; ++c) {
-            const int k = (ky * 3 + kx) * CIN + c;
-            if (k & 1) a1 = fmaf(pp[c], wr[k], a1);
-            else a0 = fmaf(pp[c], wr[k], a0);
+      for (int ks = 0; ks < kDirectK / 8; ++ks) {
+        uint32_t a[4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int tap = 2 * ks + j;             // tap (ky, kx) reads input (y - ky + 1, x - kx + 1)
+          if (tap < 9) {
+            const int off = -((tap / 3) * prow + (tap % 3) * 4);
+            a[2 * j] = __float_as_uint(a0p[off]);
+            a[2 * j + 1] = __float_as_uint(a1p[off]);
+          } else {
+            a[2 * j] = a[2 * j + 1] = 0u;
           }
         }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma_tf32_16x8x8(acc[nt], a, bw[ks][nt]);
       }
-      float v = __fadd_rn(__fadd_rn(a0, a1), bv);
-      if (act == 1) v = tanhf(v);
-      else if (act == 2) v = fmaxf(v, 0.f);
-      if (lane < Cout) out[((b * H + y0 + yy) * (long long)W + xx) * Cout + lane] = v;
+      // C fragment: (pixel p0, channels 8 nt + 2 t, + 1), (pixel p1, same channels)
+      float *o0 = out + ((b * H + y0) * (long long)W + p0) * Cout;
+      float *o1 = out + ((b * H + y0) * (long long)W + p1) * Cout;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int n = nt * 8 + 2 * t;
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[j] = __fadd_rn(acc[nt][j], bv[nt][j & 1]);
+          if (act == 1) v[j] = tanhf(v[j]);
+          else if (act == 2) v[j] = fmaxf(v[j], 0.f);
+        }
+        if ((Cout & 1) == 0) {
+          if (p0 < npx && n < Cout) *reinterpret_cast<float2 *>(o0 + n) = make_float2(v[0], v[1]);
+          if (p1 < npx && n < Cout) *reinterpret_cast<float2 *>(o1 + n) = make_float2(v[2], v[3]);
+        } else {
+          if (p0 < npx && n < Cout) o0[n] = v[0];
+          if (p0 < npx && n + 1 < Cout) o0[n + 1] = v[1];
+          if (p1 < npx && n < Cout) o1[n] = v[2];
+          if (p1 < npx && n + 1 < Cout) o1[n + 1] = v[3];
+        }
+      }
     }
   }
 }
 
-// Weight gradient of the first layer: dW[ky,kx,c,f] = sum over pixels of x[b, y-(ky-1), x-(kx-1), c] * dz[b,y,x,f].
-// Same patch; lane f keeps the 9*CIN partial sums of its output channel in registers over every pixel its warp visits, the
-// warps of a CTA are added through shared memory, and each CTA writes one [9*CIN][32] slab that conv_direct_dw_reduce sums
-// in a fixed order (deterministic).
+// Weight gradient of the first layer: dW[ky,kx,c,f] = sum over pixels of x[b, y-(ky-1), x-(kx-1), c] * dz[b,y,x,f], as
+// D[k, f] += A[k, pixel] * B[pixel, f] with 8 pixels per mma.  `dzs` > 1: the delta arrives SAMPLED -- dz is
+// [B, H/dzs, W/dzs, Cout] and stands for a full-size delta that is zero except at (dzs*y, dzs*x), the gradient of a `scale`
+// down-sampling that follows the layer (Tensors:950-965) -- so only those pixels are visited.  Every warp keeps its
+// [48 x 32] partial in registers over all pixels it visits; the warps of a CTA are added through shared memory and each
+// CTA writes one [36][32] slab that conv_direct_dw_reduce sums in a fixed order (deterministic).
 template <int CIN, int MODE>
 __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const float *__restrict__ x, const float *__restrict__ dz,
                                                                            float *__restrict__ partial, int B, int H, int W, int Cout,
-                                                                           int R, int stride) {
+                                                                           int R, int stride, int dzs) {
   extern __shared__ float sx[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float acc[9 * CIN];
+  const int g = lane >> 2, t = lane & 3;
+  const int prow = (W + 2) * 4;
+  float acc[3][4][4];
 #pragma unroll
-  for (int k = 0; k < 9 * CIN; ++k) acc[k] = 0.f;
+  for (int mt = 0; mt < 3; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[mt][nt][j] = 0.f;
+  // A fragment rows m = 16 mt + g (+ 8): tap = m / 4, channel = m % 4; offset of that tap relative to the pixel's patch cell
+  int aoff[3][2];
+#pragma unroll
+  for (int mt = 0; mt < 3; ++mt)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int m = mt * 16 + g + 8 * h, tap = m >> 2;
+      aoff[mt][h] = tap < 9 ? -((tap / 3) * prow + (tap % 3) * 4) + (m & 3) : INT_MIN;
+    }
   const int bands = (H + R - 1) / R;
-  const int row_len = (W + 2) * CIN;
-  for (long long t = blockIdx.x; t < (long long)B * bands; t += gridDim.x) {
-    const long long b = t / bands;
-    const int y0 = (int)(t - b * bands) * R;
+  const int Hs = H / dzs, Ws = W / dzs;
+  for (long long band = blockIdx.x; band < (long long)B * bands; band += gridDim.x) {
+    const long long b = band / bands;
+    const int y0 = (int)(band - b * bands) * R;   // R % dzs == 0, so y0 % dzs == 0
     const int rows = min(R, H - y0);
     __syncthreads();
     direct_fill_patch<CIN, MODE>(sx, x, b, y0, R, H, W, stride);
     __syncthreads();
-    for (int p = warp; p < rows * W; p += kDirectWarps) {
-      const int yy = p / W, xx = p - yy * W;
-      const float d = lane < Cout ? round_operand<MODE>(__ldg(dz + ((b * H + y0 + yy) * (long long)W + xx) * Cout + lane)) : 0.f;
+    const int nps = (rows / dzs) * Ws;            // delta-carrying pixels of the band
+    const float *dzb = dz + ((b * Hs + y0 / dzs) * (long long)Ws) * Cout;
+    for (int grp = warp; grp * 8 < nps; grp += kDirectWarps) {
+      // k columns of A / rows of B: pixels grp * 8 + t and + 4
+      int pq[2];
+      bool ok[2];
+      const float *ap[2];
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const float *prow = sx + (yy - ky + 2) * row_len;
+      for (int h = 0; h < 2; ++h) {
+        const int q = grp * 8 + t + 4 * h;
+        ok[h] = q < nps;
+        pq[h] = ok[h] ? q : 0;
+        const int ys = pq[h] / Ws, xs = pq[h] - ys * Ws;
+        ap[h] = sx + ((ys * dzs + 2) * (W + 2) + xs * dzs + 2) * 4;
+      }
+      uint32_t bf[4][2];
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const float *pp = prow + (xx - kx + 2) * CIN;
+      for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
-          for (int c = 0; c < CIN; ++c) acc[(ky * 3 + kx) * CIN + c] = fmaf(pp[c], d, acc[(ky * 3 + kx) * CIN + c]);
+        for (int h = 0; h < 2; ++h) {
+          const int n = nt * 8 + g;
+          float v = 0.f;
+          if (ok[h] && n < Cout) v = round_operand<MODE>(__ldg(dzb + (long long)pq[h] * Cout + n));
+          bf[nt][h] = __float_as_uint(v);
         }
+#pragma unroll
+      for (int mt = 0; mt < 3; ++mt) {
+        uint32_t a[4];
+#pragma unroll
+        for (int h = 0; h < 2; ++h)      // a0 = (m, pixel t), a1 = (m + 8, pixel t), a2 = (m, pixel t + 4), a3 = (m + 8, pixel t + 4)
+#pragma unroll
+          for (int r = 0; r < 2; ++r) a[2 * h + r] = aoff[mt][r] != INT_MIN ? __float_as_uint(ap[h][aoff[mt][r]]) : 0u;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma_tf32_16x8x8(acc[mt][nt], a, bf[nt]);
       }
     }
   }
   __syncthreads();
-  float *red = sx;                            // [warps][9*CIN][32]; the launcher sizes the buffer for both uses
+  // C fragment: c0 = (m = 16 mt + g, f = 8 nt + 2 t), c1 = (m, f + 1), c2 = (m + 8, f), c3 = (m + 8, f + 1); rows m < 36 only
+  float *red = sx;                            // [warps][36][32]; the launcher sizes the buffer for both uses
 #pragma unroll
-  for (int k = 0; k < 9 * CIN; ++k) red[(warp * 9 * CIN + k) * 32 + lane] = acc[k];
+  for (int mt = 0; mt < 3; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int m = mt * 16 + g + 8 * (j >> 1), f = nt * 8 + 2 * t + (j & 1);
+        if (m < 36) red[(warp * 36 + m) * 32 + f] = acc[mt][nt][j];
+      }
   __syncthreads();
-  for (int i = threadIdx.x; i < 9 * CIN * 32; i += blockDim.x) {
+  for (int i = threadIdx.x; i < 36 * 32; i += blockDim.x) {
     float s = red[i];
-    for (int wv = 1; wv < kDirectWarps; ++wv) s = __fadd_rn(s, red[wv * 9 * CIN * 32 + i]);
-    partial[(long long)blockIdx.x * 9 * CIN * 32 + i] = s;
+    for (int wv = 1; wv < kDirectWarps; ++wv) s = __fadd_rn(s, red[wv * 36 * 32 + i]);
+    partial[(long long)blockIdx.x * 36 * 32 + i] = s;
   }
 }
 
+// dw[(tap * cin + c) * cout + f] = sum over slabs of partial[slab][tap * 4 + c][f]: one warp per output, the lanes take
+// every 32nd slab and are folded by a fixed shuffle tree (deterministic for a given grid).
 __global__ void __launch_bounds__(256) conv_direct_dw_reduce_kernel(const float *__restrict__ partial, float *__restrict__ dw, int slabs,
-                                                                    int K, int Cout) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < K * Cout; i += gridDim.x * blockDim.x) {
-    const int k = i / Cout, f = i - k * Cout;
-    float s = 0.f;
-    for (int g = 0; g < slabs; ++g) s = __fadd_rn(s, __ldg(partial + ((long long)g * K + k) * 32 + f));
-    dw[i] = s;
-  }
+                                                                    int cin, int cout) {
+  const int lane = threadIdx.x & 31;
+  const int o = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (o >= 9 * cin * cout) return;
+  const int f = o % cout, c = (o / cout) % cin, tap = o / (cout * cin);
+  const float *src = partial + (tap * 4 + c) * 32 + f;
+  float s = 0.f;
+  for (int sl = lane; sl < slabs; sl += 32) s = __fadd_rn(s, __ldg(src + (long long)sl * 36 * 32));
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s = __fadd_rn(s, __shfl_down_sync(0xffffffffu, s, d));
+  if (lane == 0) dw[o] = s;
 }
 
-int direct_rows(int H, int W, int cin) {
-  // band height: a patch of (R + 2) x (W + 2) x cin floats, a few KB, and enough bands to fill the machine
-  int r = 4;
-  while (r > 1 && (long long)(r + 2) * (W + 2) * cin * 4 > 24 * 1024) r >>= 1;
-  return r < H ? r : H;
+int direct_rows(int H, int W, int dzs) {
+  // band height: 8 rows (a 10 x (W + 2) x 4 float patch, 5.4 KB at W = 32: one halo re-read per four rows), fewer for wide
+  // images so the patch stays below 40 KB; a multiple of the delta's sampling factor
+  int r = 8;
+  while (r > 1 && (long long)(r + 2) * (W + 2) * 16 > 40 * 1024) r >>= 1;
+  if (r > H) r = H;
+  if (dzs > 1) r = std::max(dzs, r / dzs * dzs);
+  return r;
 }
 
 }  // namespace
@@ -240,10 +368,10 @@ bool conv_direct_supported(int cin, int cout) { return cin >= 1 && cin <= 4 && c
 template <int MODE>
 static int launch_direct_fwd_mode(dls_ctx *ctx, cudaStream_t st, const float *x, const float *w, const float *bias, float *out, int B,
                                   int H, int W, int cin, int cout, int act, int stride) {
-  const int R = direct_rows(H, W, cin);
-  const size_t smem = (size_t)(R + 2) * (W + 2) * cin * sizeof(float);
+  const int R = direct_rows(H, W, 1);
+  const size_t smem = (size_t)(R + 2) * (W + 2) * 4 * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
-  const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 8);
+  const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 4);
   switch (cin) {
     case 1: conv_direct_fwd_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
     case 2: conv_direct_fwd_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
@@ -265,27 +393,26 @@ int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, c
 
 template <int MODE>
 static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                                 int cout, int stride) {
+                                 int cout, int stride, int dzs) {
   cudaStream_t st = ctx->streams[stream];
-  const int R = direct_rows(H, W, cin);
-  const int K = 9 * cin;
-  const size_t patch = (size_t)(R + 2) * (W + 2) * cin, red = (size_t)kDirectWarps * K * 32;
+  const int R = direct_rows(H, W, dzs);
+  const size_t patch = (size_t)(R + 2) * (W + 2) * 4, red = (size_t)kDirectWarps * 36 * 32;
   const size_t smem = std::max(patch, red) * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
-  const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 4);
+  const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 2);
   Block scratch;
-  int rc = alloc_block(ctx, (size_t)grid * K * 32 * sizeof(float), stream, &scratch);
+  int rc = alloc_block(ctx, (size_t)grid * 36 * 32 * sizeof(float), stream, &scratch);
   if (rc) return rc;
   float *partial = (float *)scratch.ptr;
   switch (cin) {
-    case 1: conv_direct_dw_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
-    case 2: conv_direct_dw_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
-    case 3: conv_direct_dw_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
-    default: conv_direct_dw_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride); break;
+    case 1: conv_direct_dw_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride, dzs); break;
+    case 2: conv_direct_dw_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride, dzs); break;
+    case 3: conv_direct_dw_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride, dzs); break;
+    default: conv_direct_dw_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, dz, partial, B, H, W, cout, R, stride, dzs); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
-    conv_direct_dw_reduce_kernel<<<(K * cout + 255) / 256, 256, 0, st>>>(partial, dw, grid, K, cout);
+    conv_direct_dw_reduce_kernel<<<(9 * cin * cout * 32 + 255) / 256, 256, 0, st>>>(partial, dw, grid, cin, cout);
     e = cudaGetLastError();
   }
   ctx->stats.kernel_launches += 2;
@@ -295,19 +422,19 @@ static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const
 }
 
 int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                          int cout, int stride) {
-  if (mode == DLS_GEMM_TF32) return launch_direct_dw_mode<DLS_GEMM_TF32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride);
-  if (mode == DLS_GEMM_BF16) return launch_direct_dw_mode<DLS_GEMM_BF16>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride);
-  return launch_direct_dw_mode<DLS_GEMM_FP32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride);
+                          int cout, int stride, int dzs) {
+  if (mode == DLS_GEMM_TF32) return launch_direct_dw_mode<DLS_GEMM_TF32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride, dzs);
+  if (mode == DLS_GEMM_BF16) return launch_direct_dw_mode<DLS_GEMM_BF16>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride, dzs);
+  return launch_direct_dw_mode<DLS_GEMM_FP32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride, dzs);
 }
 
 int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
-                          int stride) {
+                          int stride, int up) {
   const long long total = pixels * (Cp / 4);
   if (total == 0) return DLS_OK;
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 16);
-  if (mode == DLS_GEMM_TF32) conv_stage_act_kernel<true><<<grid, 256, 0, ctx->streams[stream]>>>(in, out, pixels, H, W, C, Cp, stride);
-  else conv_stage_act_kernel<false><<<grid, 256, 0, ctx->streams[stream]>>>(in, out, pixels, H, W, C, Cp, stride);
+  if (mode == DLS_GEMM_TF32) conv_stage_act_kernel<true><<<grid, 256, 0, ctx->streams[stream]>>>(in, out, pixels, H, W, C, Cp, stride, up);
+  else conv_stage_act_kernel<false><<<grid, 256, 0, ctx->streams[stream]>>>(in, out, pixels, H, W, C, Cp, stride, up);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;
@@ -338,16 +465,17 @@ inline size_t elem_bytes(int mode) { return mode == DLS_GEMM_TF32 ? 4 : 2; }
 // Staged NHWC operand copy of `buf` read as [batch, h*stride, w*stride, c] and sampled at `stride` (shadow slot 2, kept
 // until the buffer is written again: the forward pass and the weight gradient share the copy of an activation, the
 // backward-data pass and the weight gradient share the copy of a delta).
-int staged_act(dls_ctx *ctx, int stream, int mode, dls_buf *buf, int batch, int h, int w, int c, int stride, const void **ptr, int *cp) {
+int staged_act(dls_ctx *ctx, int stream, int mode, dls_buf *buf, int batch, int h, int w, int c, int stride, int up, const void **ptr,
+               int *cp) {
   Block &sh = buf->shadow[2];
-  const long long tag_r = ((long long)mode << 56) | ((long long)stride << 48) | ((long long)h << 24) | (long long)w;
+  const long long tag_r = ((long long)mode << 60) | ((long long)up << 56) | ((long long)stride << 48) | ((long long)h << 24) | (long long)w;
   const long long tag_c = ((long long)batch << 24) | (long long)c;
   const int p = pad_channels(mode, c);
   if (!(sh.ptr && buf->shadow_rows[2] == tag_r && buf->shadow_cols[2] == tag_c && sh.pool == ctx->capture_pool)) {
     if (sh.ptr) free_block(ctx, sh);
     const long long pixels = (long long)batch * h * w;
     int rc = alloc_block(ctx, (size_t)pixels * p * elem_bytes(mode), stream, &sh);
-    if (!rc) rc = launch_conv_stage_act(ctx, stream, mode, buf->ptr, sh.ptr, pixels, h, w, c, p, stride);
+    if (!rc) rc = launch_conv_stage_act(ctx, stream, mode, buf->ptr, sh.ptr, pixels, h, w, c, p, stride, up);
     if (rc) {
       if (sh.ptr) free_block(ctx, sh);
       return rc;
@@ -396,6 +524,8 @@ int conv_mode(dls_ctx *ctx, const dls_conv_opts *opts) {
 }
 
 bool fits_int(size_t v) { return v > 0 && v < (1u << 24); }
+// first-layer kernels: the (R + 2) x (W + 2) x 4 patch of even a one-row band must fit the default shared-memory window
+bool use_direct(size_t cin, size_t cout, size_t w) { return conv_direct_supported((int)cin, (int)cout) && w <= 512; }
 
 }  // namespace
 
@@ -406,7 +536,7 @@ int dls_conv3x3_supported(dls_ctx *ctx, int pass, size_t h, size_t w, size_t cin
   if (mode < 0) mode = ctx->opts.gemm_mode;
   if (mode != DLS_GEMM_TF32 && mode != DLS_GEMM_BF16) return 0;
   if (!fits_int(h) || !fits_int(w) || !fits_int(cin) || !fits_int(cout)) return 0;
-  if (conv_direct_supported((int)cin, (int)cout)) return pass == DLS_CONV_FORWARD || pass == DLS_CONV_BACKWARD_WEIGHTS;
+  if (use_direct(cin, cout, w)) return pass == DLS_CONV_FORWARD || pass == DLS_CONV_BACKWARD_WEIGHTS;
   if (pass == DLS_CONV_FORWARD) return conv_tc_supported(mode, (int)h, (int)w, pad_channels(mode, (int)cin), (int)cout) ? 1 : 0;
   if (pass == DLS_CONV_BACKWARD_DATA) return conv_tc_supported(mode, (int)h, (int)w, pad_channels(mode, (int)cout), (int)cin) ? 1 : 0;
   if (pass == DLS_CONV_BACKWARD_WEIGHTS) return conv_dw_tc_supported(mode, (int)h, (int)w, (int)cin, (int)cout) ? 1 : 0;
@@ -435,13 +565,13 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
   dls_buf *o = nullptr;
   rc = new_buf(ctx, batch * h * wd * cout, stream, &o);
   if (rc) return rc;
-  if (conv_direct_supported((int)cin, (int)cout)) {
+  if (use_direct(cin, cout, wd)) {
     rc = launch_conv_direct_fwd(ctx, stream, mode, x->ptr, w->ptr, bias ? bias->ptr : nullptr, o->ptr, (int)batch, (int)h, (int)wd,
                                 (int)cin, (int)cout, act, stride);
   } else {
     const void *xa, *wf, *wb;
     int cp;
-    rc = staged_act(ctx, stream, mode, x, (int)batch, (int)h, (int)wd, (int)cin, stride, &xa, &cp);
+    rc = staged_act(ctx, stream, mode, x, (int)batch, (int)h, (int)wd, (int)cin, stride, 1, &xa, &cp);
     if (!rc) rc = staged_weights(ctx, stream, mode, w, (int)cin, (int)cout, &wf, &wb);
     GemmEpilogue epi;
     epi.bias = bias ? bias->ptr : nullptr;
@@ -463,7 +593,9 @@ int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batc
   DLS_CHECK(ctx && dz && w && out, DLS_ERR_INVALID, "dls_conv3x3_backward_data: NULL argument");
   DLS_CHECK(fits_int(batch) && fits_int(h) && fits_int(wd) && fits_int(cin) && fits_int(cout), DLS_ERR_INVALID,
             "dls_conv3x3_backward_data: bad shape");
-  DLS_CHECK(batch * h * wd * cout <= dz->n && 9 * cin * cout <= w->n, DLS_ERR_INVALID,
+  const int dzs = (opts && opts->dz_stride > 1) ? opts->dz_stride : 1;
+  DLS_CHECK(h % dzs == 0 && wd % dzs == 0, DLS_ERR_INVALID, "dls_conv3x3_backward_data: dz_stride must divide the image size");
+  DLS_CHECK(batch * (h / dzs) * (wd / dzs) * cout <= dz->n && 9 * cin * cout <= w->n, DLS_ERR_INVALID,
             "dls_conv3x3_backward_data: a buffer is shorter than its shape");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   const int mode = conv_mode(ctx, opts);
@@ -479,7 +611,7 @@ int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batc
   if (rc) return rc;
   const void *da, *wf, *wb;
   int cp;
-  rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, &da, &cp);
+  rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, dzs, &da, &cp);
   if (!rc) rc = staged_weights(ctx, stream, mode, w, (int)cin, (int)cout, &wf, &wb);
   // dx[b,y,x,c] = sum_{ky,kx,f} dz[b, y+(ky-1), x+(kx-1), f] * w[ky,kx,c,f]: the same kernel with the taps mirrored
   if (!rc) rc = launch_conv_tc(ctx, stream, mode, da, (int)batch, (int)h, (int)wd, cp, wb, (int)cin, o->ptr, -1, GemmEpilogue());
@@ -498,7 +630,9 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
   const int stride = (opts && opts->in_stride > 1) ? opts->in_stride : 1;
   DLS_CHECK(fits_int(batch) && fits_int(h) && fits_int(wd) && fits_int(cin) && fits_int(cout), DLS_ERR_INVALID,
             "dls_conv3x3_backward_weights: bad shape");
-  DLS_CHECK(batch * h * stride * wd * stride * cin <= x->n && batch * h * wd * cout <= dz->n, DLS_ERR_INVALID,
+  const int dzs = (opts && opts->dz_stride > 1) ? opts->dz_stride : 1;
+  DLS_CHECK(h % dzs == 0 && wd % dzs == 0, DLS_ERR_INVALID, "dls_conv3x3_backward_weights: dz_stride must divide the image size");
+  DLS_CHECK(batch * h * stride * wd * stride * cin <= x->n && batch * (h / dzs) * (wd / dzs) * cout <= dz->n, DLS_ERR_INVALID,
             "dls_conv3x3_backward_weights: a buffer is shorter than its shape");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   const int mode = conv_mode(ctx, opts);
@@ -512,13 +646,13 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
   dls_buf *o = nullptr;
   rc = new_buf(ctx, 9 * cin * cout, stream, &o);
   if (rc) return rc;
-  if (conv_direct_supported((int)cin, (int)cout)) {
-    rc = launch_conv_direct_dw(ctx, stream, mode, x->ptr, dz->ptr, o->ptr, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, stride);
+  if (use_direct(cin, cout, wd)) {
+    rc = launch_conv_direct_dw(ctx, stream, mode, x->ptr, dz->ptr, o->ptr, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, stride, dzs);
   } else {
     const void *xa, *da;
     int cxp, cdp;
-    rc = staged_act(ctx, stream, mode, x, (int)batch, (int)h, (int)wd, (int)cin, stride, &xa, &cxp);
-    if (!rc) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, &da, &cdp);
+    rc = staged_act(ctx, stream, mode, x, (int)batch, (int)h, (int)wd, (int)cin, stride, 1, &xa, &cxp);
+    if (!rc) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, dzs, &da, &cdp);
     if (!rc) rc = launch_conv_dw_tc(ctx, stream, mode, xa, cxp, da, cdp, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, o->ptr);
   }
   if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 2, done);

@@ -239,6 +239,10 @@ class Layers:
         """Nearest-neighbour 1/factor resampling of the two middle dims of an NHWC tensor by `Tensor.scale`
         (Tensors:950-965): out[b, y, x, c] = in[b, factor*y, factor*x, c].  Backward routes each delta to the sample it
         was read from (a `scale` back up, masked to the sampled positions)."""
+        spec = getattr(a, "_conv_spec", None)
+        if spec is not None:                                         # conv -> down-sample: one layer, sampled delta (conv2d_3x3)
+            return self.conv2d_3x3(spec[0], spec[1], spec[2], spec[3], downsample=factor)
+
         def build(tapes):
             (t0,) = tapes
             b, h, w, c = t0.data.shape
@@ -310,7 +314,7 @@ class Layers:
             return y, backward, owned
         return self._pinned(inputs, build)
 
-    def conv2d_3x3(self, x, w, bias=None, activation: str = "none") -> TensorLayer:
+    def conv2d_3x3(self, x, w, bias=None, activation: str = "none", downsample: int = 1) -> TensorLayer:
         """'Same' 3x3 convolution of an NHWC tensor with weights [3, 3, Cin, Cout] (the layout and the index convention
         of TensorsSpec:144-210: out[b,y,x,f] = bias[f] + sum x[b, y-(ky-1), x-(kx-1), c] * w[ky,kx,c,f], zero padding from
         the bounds check of `translate`).
@@ -318,9 +322,14 @@ class Layers:
         operand tiles are tap-shifted TMA boxes of the activation, direct kernels for a first layer with Cin <= 4), and a
         preceding `downsample` view is read in place.  Where no such kernel applies (fp32 parity mode, odd shapes) the
         pass is composed the way the reference composes it: the nine translated views written by ONE multi-root gather
-        launch (`Tensor.join`), then out = col[BHW, Cin*9] . wmat[Cin*9, Cout]."""
+        launch (`Tensor.join`), then out = col[BHW, Cin*9] . wmat[Cin*9, Cout].
+        `downsample` = s > 1 is the layer followed by `Layers.downsample(., s)` (which calls this): the value is the same
+        `scale` view of the pinned full-size output, and the delta that comes back -- zero except at the sampled
+        positions -- stays at its sampled size [B, H/s, W/s, Cout] all the way into the backward kernels
+        (`dz_stride`), instead of being scaled back up, masked and written out at full size first."""
         offsets = [(ky - 1, kx - 1) for ky in range(3) for kx in range(3)]
         inputs = [x, w] + ([bias] if bias is not None else [])
+        s = int(downsample)
 
         def build(tapes):
             tx, tw = tapes[0], tapes[1]
@@ -329,6 +338,9 @@ class Layers:
             bsz, h, wd, cin = X.shape
             cout = W.shape[3]
             m = bsz * h * wd
+            if s > 1 and (h % s or wd % s):
+                raise ValueError("conv2d_3x3: downsample %d does not divide the %d x %d image" % (s, h, wd))
+            full, half = [bsz, h, wd, cout], [bsz, h // s, wd // s, cout]
             bias_t = tapes[2].data if bias is not None else None
             owned = []
             lazy = {}
@@ -349,28 +361,37 @@ class Layers:
                 y = be.conv3x3_forward(X, W, bias_t, activation)
             else:
                 y = T.matmul(col(), wmat(), bias=bias_t, bias_mode="col" if bias is not None else "none",
-                             activation=activation).reshape([bsz, h, wd, cout])
+                             activation=activation).reshape(full)
 
             def backward(y_cached):
                 def run(do_delta: Do):
                     memo = {}
 
-                    def dz_of(d):                                    # [B, H, W, Cout], shared by the three consumers
-                        if "dz" not in memo:
-                            d = d.broadcast([bsz, h, wd, cout])
+                    def dz_sampled(d):                               # [B, H/s, W/s, Cout]: the delta where it can be non-zero
+                        if "dzs" not in memo:
+                            d = d.broadcast(half)
+                            ys = y_cached.scale(half) if s > 1 else y_cached
                             if activation == "tanh":
-                                d = d * (1.0 - y_cached * y_cached)
+                                d = d * (1.0 - ys * ys)
                             elif activation == "relu":
-                                d = d * relu_mask(y_cached)
-                            memo["dz"] = d.do_cache()
+                                d = d * relu_mask(ys)
+                            memo["dzs"] = d.do_cache()
+                            owned.append(memo["dzs"])
+                        return memo["dzs"]
+
+                    def dz_of(d):                                    # [B, H, W, Cout], for the passes composed from views
+                        if s == 1:
+                            return dz_sampled(d)
+                        if "dz" not in memo:
+                            memo["dz"] = (dz_sampled(d).scale(full) * sample_mask(be, h, wd, s)).do_cache()
                             owned.append(memo["dz"])
                         return memo["dz"]
 
                     def delta_x(d):
                         if be.conv3x3_supported("backward_data", h, wd, cin, cout):
-                            return be.conv3x3_backward_data(dz_of(d), W)
+                            return be.conv3x3_backward_data(dz_sampled(d), W, dz_stride=s)
                         dcol = T.matmul(dz_of(d).reshape([m, cout]), wmat(), transpose_b=True).reshape([bsz, h, wd, cin, 9])
-                        parts = [s.translate([0, -oy, -ox, 0]) for s, (oy, ox) in zip(dcol.split(4), offsets)]
+                        parts = [p.translate([0, -oy, -ox, 0]) for p, (oy, ox) in zip(dcol.split(4), offsets)]
                         acc = parts[0]
                         for p in parts[1:]:
                             acc = acc + p
@@ -378,17 +399,23 @@ class Layers:
 
                     def delta_w(d):
                         if be.conv3x3_supported("backward_weights", h, wd, cin, cout):
-                            return be.conv3x3_backward_weights(X, dz_of(d))
+                            return be.conv3x3_backward_weights(X, dz_sampled(d), dz_stride=s)
                         dw = T.matmul(col(), dz_of(d).reshape([m, cout]), transpose_a=True)     # [Cin*9, Cout]
                         return dw.reshape([cin, 3, 3, cout]).permute([1, 2, 0, 3])
 
                     tx.backward(do_delta.map(delta_x))
                     tw.backward(do_delta.map(delta_w))
-                    if bias is not None:
-                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d).reshape([m, cout]), 0)))
+                    if bias is not None:                             # the zeros of a sampled delta add nothing
+                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_sampled(d).reshape([m // (s * s), cout]), 0)))
                 return run
             return y, backward, owned
-        return self._pinned(inputs, build)
+
+        view = (lambda cached, tapes: cached.scale([cached.shape[0], cached.shape[1] // s, cached.shape[2] // s, cached.shape[3]])) \
+            if s > 1 else None
+        layer = self._pinned(inputs, build, view)
+        if s == 1:
+            layer._conv_spec = (x, w, bias, activation)              # lets a following `downsample` fold itself into this layer
+        return layer
 
 
 def relu_mask(y):

@@ -344,7 +344,7 @@ class Backend:
         batch, h, wd, cin = x.shape
         cout = w.shape[3]
         src, stride = self._sampled_source(x)
-        opts = N.ConvOpts(mode=self._MODES[mode], activation={"none": 0, "tanh": 1, "relu": 2}[activation], in_stride=stride, reserved=0)
+        opts = N.ConvOpts(mode=self._MODES[mode], activation={"none": 0, "tanh": 1, "relu": 2}[activation], in_stride=stride, dz_stride=0)
 
         def produce():
             bx, bw = src._buffer(), w._buffer()
@@ -355,11 +355,14 @@ class Backend:
             return DeviceBuffer(self, hd, batch * h * wd * cout)
         return ProducedTensor(self, produce, [batch, h, wd, cout], x.padding)
 
-    def conv3x3_backward_data(self, dz: "Tensor", w: "Tensor", mode: Optional[str] = None) -> "NonInlineTensor":
-        """dx[b,y,x,c] = sum dz[b, y+(ky-1), x+(kx-1), f] w[ky,kx,c,f]."""
-        batch, h, wd, cout = dz.shape
+    def conv3x3_backward_data(self, dz: "Tensor", w: "Tensor", mode: Optional[str] = None, dz_stride: int = 1) -> "NonInlineTensor":
+        """dx[b,y,x,c] = sum dz[b, y+(ky-1), x+(kx-1), f] w[ky,kx,c,f].  `dz_stride` = s > 1: `dz` is the SAMPLED delta
+        [batch, h/s, w/s, cout] that a down-sampling after the layer hands back; it stands for the full-size delta that is
+        zero everywhere except at (s*y, s*x), which is never materialised in fp32."""
+        batch, hs, ws, cout = dz.shape
+        h, wd = hs * dz_stride, ws * dz_stride
         cin = w.shape[2]
-        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=1, reserved=0)
+        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=1, dz_stride=dz_stride)
 
         def produce():
             bd, bw = dz._buffer(), w._buffer()
@@ -369,12 +372,12 @@ class Backend:
             return DeviceBuffer(self, hd, batch * h * wd * cin)
         return ProducedTensor(self, produce, [batch, h, wd, cin], dz.padding)
 
-    def conv3x3_backward_weights(self, x: "Tensor", dz: "Tensor", mode: Optional[str] = None) -> "NonInlineTensor":
-        """dw[ky,kx,c,f] = sum over b,y,x of x[b, y-(ky-1), x-(kx-1), c] dz[b,y,x,f]."""
+    def conv3x3_backward_weights(self, x: "Tensor", dz: "Tensor", mode: Optional[str] = None, dz_stride: int = 1) -> "NonInlineTensor":
+        """dw[ky,kx,c,f] = sum over b,y,x of x[b, y-(ky-1), x-(kx-1), c] dz[b,y,x,f]; `dz_stride` as in backward_data."""
         batch, h, wd, cin = x.shape
         cout = dz.shape[3]
         src, stride = self._sampled_source(x)
-        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=stride, reserved=0)
+        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=stride, dz_stride=dz_stride)
 
         def produce():
             bx, bd = src._buffer(), dz._buffer()

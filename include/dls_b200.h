@@ -202,16 +202,18 @@ int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m,
  *   backward_weights  dw[ky,kx,c,f] = sum_{b,y,x} xs[b, y-(ky-1), x-(kx-1), c] * dz[b,y,x,f]
  * with zero padding outside the image.  xs is the [batch,h,w,cin] input; with in_stride = s > 1 it is read in place from a
  * [batch, h*s, w*s, cin] buffer as xs[b,y,x,c] = x[b, s*y, s*x, c] -- the nearest-neighbour `scale` view (Tensors:950-965)
- * that precedes the convolution, never materialised.  Tensor-core modes only (mode = -1 takes the context's gemm_mode):
+ * that precedes the convolution, never materialised; dz_stride is the mirror image for the delta of a down-sampling that
+ * FOLLOWS the layer (its zeros are neither stored nor, in the first-layer kernels, visited).  Tensor-core modes only (mode = -1 takes the context's gemm_mode):
  * operands rounded to bf16 / tf32 like every contraction of the mode, fp32 accumulation; same stated tolerances as
- * dls_matmul_ex.  Cin <= 4 (first layer) runs on direct CUDA-core kernels, everything else as an implicit GEMM on the
+ * dls_matmul_ex.  Cin <= 4 (first layer) runs on direct kernels (warp-level mma over a shared-memory patch), everything else as an implicit GEMM on the
  * tcgen05 tensor cores.  DLS_ERR_UNSUPPORTED (ask dls_conv3x3_supported first) means: compose it from views + dls_matmul. */
 enum dls_conv_pass { DLS_CONV_FORWARD = 0, DLS_CONV_BACKWARD_DATA = 1, DLS_CONV_BACKWARD_WEIGHTS = 2 };
 typedef struct dls_conv_opts {
   int32_t mode;        /* enum dls_gemm_mode, or -1 = context default */
   int32_t activation;  /* enum dls_activation (forward only)          */
   int32_t in_stride;   /* 0 / 1 = dense input; s > 1 = input sampled at stride s (forward, backward_weights) */
-  int32_t reserved;
+  int32_t dz_stride;   /* 0 / 1 = dense delta; s > 1 (backward passes) = dz is [batch, h/s, w/s, cout] and stands for a full-size
+                          delta that is zero except at (s*y, s*x): what a `scale` down-sampling after the layer hands back */
 } dls_conv_opts;
 int dls_conv3x3_supported(dls_ctx *ctx, int pass, size_t h, size_t w, size_t cin, size_t cout, int mode);
 int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, size_t batch, size_t h, size_t wd, size_t cin,

@@ -163,3 +163,75 @@ def test_reference_convolution_known_answer(env, backend):
     want = np.maximum(MO.conv_forward(x, wt, bias, r), 0.0)
     scale = MO.conv_forward(np.abs(x), np.abs(wt), np.abs(bias), r) + 1.0
     assert (np.abs(out.reshape(want.shape) - want) / scale).max() <= 4e-6
+
+
+SAMPLED = [(256, 32, 32, 3, 32, 2), (256, 16, 16, 32, 64, 2), (3, 16, 16, 32, 64, 2), (5, 12, 20, 4, 32, 2), (2, 16, 16, 1, 8, 4),
+           (6, 8, 8, 64, 128, 2)]
+
+
+@pytest.mark.parametrize("shape", SAMPLED, ids=["%dx%dx%dx%d-%d-s%d" % s for s in SAMPLED])
+def test_sampled_delta_equals_the_zero_filled_delta(env, backend, shape):
+    """`dz_stride` = s: the delta that a down-sampling after the layer hands back arrives at its sampled size
+    [B, H/s, W/s, Cout]; both backward passes must give what they give for the full-size delta that is zero except at
+    (s*y, s*x) -- against the oracle on that zero-filled delta, and (tensor-core kernels: same staged operand) bit for
+    bit against the dense call."""
+    MO, O, B = env
+    mode, be = backend
+    batch, h, w, cin, cout, s = shape
+    rng = np.random.RandomState(sum(shape))
+    x = rng.standard_normal((batch, h, w, cin)).astype(np.float32)
+    wt = (rng.standard_normal((3, 3, cin, cout)) * 0.2).astype(np.float32)
+    dzs = rng.standard_normal((batch, h // s, w // s, cout)).astype(np.float32)
+    dz = np.zeros((batch, h, w, cout), dtype=np.float32)
+    dz[:, ::s, ::s, :] = dzs
+    r = lambda a: O.round_operand(a, mode)
+    want_dx, want_dw, _ = MO.conv_backward(x, wt, dz, r)
+    scale_dx, scale_dw, _ = MO.conv_backward(np.abs(x), np.abs(wt), np.abs(dz), r)
+    ran = 0
+    if be.conv3x3_supported("backward_weights", h, w, cin, cout):
+        got = be.conv3x3_backward_weights(be.tensor(x), be.tensor(dzs), dz_stride=s).flat_array().reshape(wt.shape)
+        err = np.abs(got.astype(np.float64) - want_dw.astype(np.float64)) / (scale_dw.astype(np.float64) + 1.0)
+        assert err.max() <= 4e-6, "dW worst element %r: %g" % (np.unravel_index(err.argmax(), err.shape), err.max())
+        ran += 1
+    if be.conv3x3_supported("backward_data", h, w, cin, cout):
+        got = be.conv3x3_backward_data(be.tensor(dzs), be.tensor(wt), dz_stride=s).flat_array().reshape(x.shape)
+        err = np.abs(got.astype(np.float64) - want_dx.astype(np.float64)) / (scale_dx.astype(np.float64) + 1.0)
+        assert err.max() <= 4e-6, "dX worst element %r: %g" % (np.unravel_index(err.argmax(), err.shape), err.max())
+        dense = be.conv3x3_backward_data(be.tensor(dz), be.tensor(wt)).flat_array().reshape(x.shape)
+        assert (got.view(np.uint32) == dense.view(np.uint32)).all()
+        ran += 1
+    if not ran:
+        pytest.skip("no dedicated backward kernel for this shape in %s" % mode)
+
+
+def test_downsample_after_a_convolution_folds_into_the_layer(env, backend):
+    """`Layers.downsample(conv2d_3x3(...))` is one layer: same value as the composition, and one training step moves the
+    weights exactly as the composition's does (loss = sum of the down-sampled outputs)."""
+    MO, O, B = env
+    mode, be = backend
+    from deeplearning.scala_b200.plugins import Plugins
+    from deeplearning.scala_b200.layers import Layers
+    rng = np.random.RandomState(17)
+    x = rng.standard_normal((4, 16, 16, 3)).astype(np.float32)
+    wt = (rng.standard_normal((3, 3, 3, 8)) * 0.3).astype(np.float32)
+    bias = (rng.standard_normal(8) * 0.1).astype(np.float32)
+    seed = rng.standard_normal((4, 8, 8, 8)).astype(np.float32)
+    results = []
+    for fold in (True, False):
+        P = Plugins(backend=be, optimizer_delta=lambda w_, d: d * 0.1)
+        L = Layers(P)
+        w_, b_ = P.weight(be.tensor(wt)), P.weight(be.tensor(bias))
+        conv = L.conv2d_3x3(be.tensor(x), w_, b_, "relu")
+        if not fold:
+            del conv._conv_spec
+        out = L.downsample(conv, 2) * be.tensor(seed)
+        val = out.train().map(lambda t: t.flat_array()).run()
+        P.flush_updates()
+        assert not P.handled_exceptions, P.handled_exceptions
+        results.append((val, w_.data.flat_array(), b_.data.flat_array()))
+    (v1, w1, b1), (v2, w2, b2) = results
+    assert (v1.view(np.uint32) == v2.view(np.uint32)).all()
+    gw1, gw2 = (wt.reshape(-1) - w1).astype(np.float64), (wt.reshape(-1) - w2).astype(np.float64)
+    assert np.abs(gw1 - gw2).max() <= 1e-5 * np.abs(gw2).max()
+    assert np.abs((bias - b1) - (bias - b2)).max() <= 1e-5 * np.abs(bias - b2).max()
+    assert np.abs(gw2).max() > 0
