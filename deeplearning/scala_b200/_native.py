@@ -38,7 +38,7 @@ class CtxOpts(C.Structure):
 
 
 class GemmOpts(C.Structure):
-    _fields_ = [("mode", C.c_int32), ("bias_mode", C.c_int32), ("activation", C.c_int32), ("reserved", C.c_int32)]
+    _fields_ = [("mode", C.c_int32), ("bias_mode", C.c_int32), ("activation", C.c_int32), ("flags", C.c_int32)]
 
 
 class ConvOpts(C.Structure):
@@ -98,6 +98,8 @@ _SIG = {
     "dls_matmul": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, _PP, C.c_int, _PP, _PP]),
     "dls_matmul_ex": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
                                 C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_matmul_gated": (C.c_int, [_P, _P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
+                                   C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),
     "dls_conv3x3_supported": (C.c_int, [_P, C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]),
     "dls_conv3x3_forward": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                       C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),

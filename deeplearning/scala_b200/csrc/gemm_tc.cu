@@ -220,6 +220,50 @@ __device__ __forceinline__ void epi_apply(const uint32_t (&v)[32], float (&f)[32
   }
 }
 
+// x *= act'(g) for the 32 columns of a chunk (`left` = columns that exist from col0 on): the delta of the layer below in the
+// same kernel.  One rounding per node of `delta * (1 - y * y)` / `delta * min(y * FLT_MAX, 1)`, like the elementwise kernels.
+__device__ __forceinline__ void epi_gate(float (&f)[32], const float *__restrict__ g, int left, int mode, bool vec) {
+  float h[32];
+  if (vec) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (4 * j < left) q = __ldg(reinterpret_cast<const float4 *>(g) + j);
+      h[4 * j] = q.x;
+      h[4 * j + 1] = q.y;
+      h[4 * j + 2] = q.z;
+      h[4 * j + 3] = q.w;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) h[j] = j < left ? __ldg(g + j) : 0.f;
+  }
+  if (mode == 1) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = __fmul_rn(f[j], __fsub_rn(1.0f, __fmul_rn(h[j], h[j])));
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = __fmul_rn(f[j], fminf(__fmul_rn(h[j], 3.4028234663852886e38f), 1.0f));
+  }
+}
+
+// the chunk once more as bf16 (round to nearest even), 16 bytes per store; `left` = elements to the end of the copy's row
+__device__ __forceinline__ void epi_copy_bf16(const float (&f)[32], __nv_bfloat16 *dst, long long left) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (8 * q < left) {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(f[8 * q], f[8 * q + 1]), p1 = __floats2bfloat162_rn(f[8 * q + 2], f[8 * q + 3]);
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(f[8 * q + 4], f[8 * q + 5]), p3 = __floats2bfloat162_rn(f[8 * q + 6], f[8 * q + 7]);
+      uint4 o;
+      o.x = *reinterpret_cast<uint32_t *>(&p0);
+      o.y = *reinterpret_cast<uint32_t *>(&p1);
+      o.z = *reinterpret_cast<uint32_t *>(&p2);
+      o.w = *reinterpret_cast<uint32_t *>(&p3);
+      reinterpret_cast<uint4 *>(dst)[q] = o;
+    }
+  }
+}
+
 // CONV selects where the operand tiles come from:
 //   0  plain GEMM: 2-D boxes of A and B.
 //   1  implicit-GEMM 3x3 'same' convolution, forward or backward-data (TensorsSpec:144-210 without the im2col matrix):
@@ -234,7 +278,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
                    const float *__restrict__ bias, int bias_mode, int act, int direct_store, int splits, int kb_per_split,
-                   int c_rows, const ConvGeom cg) {
+                   int c_rows, const ConvGeom cg, const float *__restrict__ gate, int gate_mode, void *__restrict__ copy,
+                   long long copy_ld) {
   // splits > 1 (split-K): work item w = split * n_tiles + tile covers k blocks [split * kb_per_split, ...) and writes its
   // partial tile at row offset split * tiles_m * BM of a [splits * tiles_m * BM, N] scratch matrix (c_rows = its row count);
   // the epilogue (bias / activation) then runs in splitk_reduce_kernel.
@@ -428,6 +473,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float f[32];
         epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
+        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0);
+        if (copy && row < M) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(copy) + (long long)row * copy_ld + col0, copy_ld - col0);
         if (direct_store) {
           if (row < c_rows) {
             float *dst = C + (long long)row * ldc + col0;
@@ -612,10 +659,12 @@ static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *bas
   return DLS_OK;
 }
 
-// out[i] = act(sum_s partial[s * stride + i] + bias), i < m * n: the second half of a split-K contraction.
+// out[i] = act(sum_s partial[s * stride + i] + bias) (* act'(gate[i])), i < m * n: the second half of a split-K contraction;
+// optionally also the bf16 operand copy of the result.
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restrict__ partial, float *__restrict__ out, size_t m,
                                                             size_t n, size_t stride, int splits, const float *__restrict__ bias,
-                                                            int bias_mode, int act) {
+                                                            int bias_mode, int act, const float *__restrict__ gate, int gate_mode,
+                                                            __nv_bfloat16 *__restrict__ copy, long long copy_ld) {
   const size_t total = m * n;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float x = __ldg(partial + i);
@@ -624,7 +673,14 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restr
     else if (bias_mode == 2) x = __fadd_rn(x, __ldg(bias + i % n));
     if (act == 1) x = tanhf(x);
     else if (act == 2) x = fmaxf(x, 0.f);
+    if (gate_mode == 1) {
+      const float h = __ldg(gate + i);
+      x = __fmul_rn(x, __fsub_rn(1.0f, __fmul_rn(h, h)));
+    } else if (gate_mode == 2) {
+      x = __fmul_rn(x, fminf(__fmul_rn(__ldg(gate + i), 3.4028234663852886e38f), 1.0f));
+    }
     out[i] = x;
+    if (copy) copy[(i / n) * copy_ld + i % n] = __float2bfloat16_rn(x);
   }
 }
 
@@ -649,7 +705,7 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
   const int sms = ctx->comm_pending.empty() ? ctx->sm_count : std::max(1, ctx->sm_count - ctx->exchange_sms);
   const int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, sp.splits,
-                                              sp.kb_per_split, sp.c_rows, cg);
+                                              sp.kb_per_split, sp.c_rows, cg, epi.gate, epi.gate_mode, epi.copy, epi.copy_ld);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;
@@ -768,7 +824,8 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
       const size_t total = (size_t)M * N;
       const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->sm_count * 8);
       tc::splitk_reduce_kernel<<<grid, 256, 0, st>>>(dst, C, (size_t)M, (size_t)N, (size_t)m_pad * ld_dst, sp.splits, epi.bias,
-                                                     epi.bias_mode, epi.act);
+                                                     epi.bias_mode, epi.act, epi.gate, epi.gate_mode, (__nv_bfloat16 *)epi.copy,
+                                                     epi.copy_ld);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) rc = cuda_fail(e, "splitk_reduce_kernel", __FILE__, __LINE__);
       ctx->stats.kernel_launches++;

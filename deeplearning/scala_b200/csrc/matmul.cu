@@ -107,6 +107,23 @@ int launch_bias_act(dls_ctx *ctx, int stream, float *c, size_t m, size_t n, cons
   return DLS_OK;
 }
 
+// c *= act'(gate) in place (fp32 parity mode; the tensor-core kernel does it in its epilogue): same nodes, same roundings.
+__global__ void __launch_bounds__(256) gate_kernel(float *__restrict__ c, size_t total, const float *__restrict__ gate, int mode) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const float h = __ldg(gate + i);
+    c[i] = mode == 1 ? __fmul_rn(c[i], __fsub_rn(1.0f, __fmul_rn(h, h))) : __fmul_rn(c[i], fminf(__fmul_rn(h, 3.4028234663852886e38f), 1.0f));
+  }
+}
+
+int launch_gate(dls_ctx *ctx, int stream, float *c, size_t total, const float *gate, int mode) {
+  if (total == 0 || mode == 0) return DLS_OK;
+  const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->sm_count * 8);
+  gate_kernel<<<grid, 256, 0, ctx->streams[stream]>>>(c, total, gate, mode);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
 }  // namespace dls
 
 using namespace dls;
@@ -171,16 +188,21 @@ namespace dls {
 // c[M, N] = act(op(a) op(b) + bias) on `stream` (inputs already waited for): the body of dls_matmul_ex, also the
 // target of trees that the lowering recognised as one dense contraction (Plan::contraction).
 int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k,
-               bool transpose_a, bool transpose_b, int bias_mode, int activation, dls_buf *c) {
+               bool transpose_a, bool transpose_b, int bias_mode, int activation, dls_buf *c, dls_buf *gate, int gate_mode,
+               Block *operand_copy) {
   if (m * n == 0) return DLS_OK;
   const float *bias_ptr = bias_mode ? bias->ptr : nullptr;
+  const float *gate_ptr = gate_mode ? gate->ptr : nullptr;
   if (k == 0) {
     DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
-    return launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
+    int rc = launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
+    if (!rc) rc = launch_gate(ctx, stream, c->ptr, m * n, gate_ptr, gate_mode);
+    return rc;
   }
   if (mode == DLS_GEMM_FP32) {
     int rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, c->ptr, (int)m, (int)n, (int)k, transpose_a, transpose_b);
     if (!rc) rc = launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
+    if (!rc) rc = launch_gate(ctx, stream, c->ptr, m * n, gate_ptr, gate_mode);
     return rc;
   }
   const void *pa, *pb;
@@ -197,6 +219,14 @@ int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_b
   epi.bias = bias_ptr;
   epi.bias_mode = bias_mode;
   epi.act = activation;
+  epi.gate = gate_ptr;
+  epi.gate_mode = gate_mode;
+  if (!rc && operand_copy && mode == DLS_GEMM_BF16) {
+    // the result's own bf16 operand copy, written by the epilogue: [m][n rounded up to 8] like stage_operand's
+    epi.copy_ld = ((long long)n + 7) & ~7LL;
+    rc = alloc_block(ctx, (size_t)m * epi.copy_ld * 2, stream, operand_copy);
+    epi.copy = operand_copy->ptr;
+  }
   if (!rc) rc = launch_gemm_tc(ctx, stream, mode, pa, a_mn, lda, pb, b_mn, ldb, c->ptr, (long long)n, (int)m, (int)n, (int)k, epi);
   if (own.ptr) free_block(ctx, own);
   return rc;
@@ -204,9 +234,9 @@ int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_b
 
 }  // namespace dls
 
-extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k, int transpose_a,
-                             int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
-                             dls_event **done) {
+extern "C" int dls_matmul_gated(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, dls_buf *gate, size_t m, size_t n, size_t k,
+                                int transpose_a, int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps,
+                                dls_buf **out, dls_event **done) {
   DLS_CHECK(ctx && a && b && out, DLS_ERR_INVALID, "dls_matmul: NULL argument");
   DLS_CHECK(m * k <= a->n && k * n <= b->n, DLS_ERR_INVALID, "dls_matmul: operand shorter than its shape");
   DLS_CHECK(m < (1u << 31) && n < (1u << 31) && k < (1u << 31), DLS_ERR_UNSUPPORTED, "dls_matmul: dimension too large");
@@ -219,23 +249,41 @@ extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias
             "dls_matmul: bad epilogue options");
   DLS_CHECK(o.bias_mode == 0 || (bias && bias->n >= (o.bias_mode == 1 ? m : n)), DLS_ERR_INVALID,
             "dls_matmul: bias buffer missing or too short");
+  const int gate_mode = (o.flags >> 8) & 3;
+  DLS_CHECK(gate_mode <= 2 && (gate_mode == 0 || (gate && gate->n >= m * n)), DLS_ERR_INVALID,
+            "dls_matmul_gated: gate buffer missing or shorter than the product");
   std::lock_guard<std::recursive_mutex> lk(ctx->mu);
   DLS_CUDA(cudaSetDevice(ctx->device));
   const int stream = pick_stream(ctx);
-  dls_buf *ins[3] = {a, b, o.bias_mode ? bias : nullptr};
-  int rc = wait_inputs(ctx, stream, ins, 3, deps, n_deps);
+  dls_buf *ins[4] = {a, b, o.bias_mode ? bias : nullptr, gate_mode ? gate : nullptr};
+  int rc = wait_inputs(ctx, stream, ins, 4, deps, n_deps);
   if (rc) return rc;
   dls_buf *c = nullptr;
   rc = new_buf(ctx, m * n, stream, &c);
   if (rc) return rc;
-  rc = run_matmul(ctx, stream, mode, a, b, bias, m, n, k, transpose_a != 0, transpose_b != 0, o.bias_mode, o.activation, c);
-  if (!rc) rc = finish_output(ctx, stream, &c, 1, ins, 3, done);
+  Block copy;
+  rc = run_matmul(ctx, stream, mode, a, b, bias, m, n, k, transpose_a != 0, transpose_b != 0, o.bias_mode, o.activation, c, gate,
+                  gate_mode, (o.flags & DLS_GEMM_EMIT_OPERAND_COPY) ? &copy : nullptr);
+  if (!rc) rc = finish_output(ctx, stream, &c, 1, ins, 4, done);
   if (rc) {
+    if (copy.ptr) free_block(ctx, copy);
     dls_buf_release(c);
     return rc;
   }
+  if (copy.ptr) {               // after finish_output (which drops the stale shadows of a written buffer)
+    copy.stream_mask |= 1u << stream;
+    c->shadow[0] = copy;
+    c->shadow_rows[0] = (long long)m;
+    c->shadow_cols[0] = (long long)n;
+  }
   *out = c;
   return DLS_OK;
+}
+
+extern "C" int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k, int transpose_a,
+                             int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
+                             dls_event **done) {
+  return dls_matmul_gated(ctx, a, b, bias, nullptr, m, n, k, transpose_a, transpose_b, opts, deps, n_deps, out, done);
 }
 
 extern "C" int dls_matmul(dls_ctx *ctx, dls_buf *a, dls_buf *b, size_t m, size_t n, size_t k, int transpose_a, int transpose_b,

@@ -273,8 +273,9 @@ class Layers:
             ta, tb = tapes[0], tapes[1]
             A, B = ta.data, tb.data
             bias_t = tapes[2].data if bias_mode != "none" else None
+            # the value feeds the next contraction (and this layer's weight gradient): its operand copy comes with it
             y = T.matmul(A, B, transpose_a=transpose_a, transpose_b=transpose_b, bias=bias_t, bias_mode=bias_mode,
-                         activation=activation)
+                         activation=activation, emit_operand_copy=True)
             out_shape = list(y.shape)
             owned = []
 
@@ -284,11 +285,20 @@ class Layers:
 
                     def dz_of(d):                                   # shared by the three consumers below
                         if "dz" not in memo:
-                            d = d.broadcast(out_shape)
-                            if activation == "tanh":
-                                d = d * (1.0 - y_cached * y_cached)
-                            elif activation == "relu":
-                                d = d * relu_mask(y_cached)
+                            spec = getattr(d, "_ungated", None)
+                            if (activation != "none" and spec is not None and list(d.shape) == out_shape
+                                    and (d._weak is None or d._weak() is None)):
+                                # `d` is the still unevaluated product of the layer above (its delta_a): issue it with
+                                # this layer's activation derivative in its epilogue -- `d * (1 - y * y)` /
+                                # `d * 1[y > 0]` node for node -- instead of materialising d and launching the tree
+                                d = T.matmul(spec["a"], spec["b"], transpose_a=spec["transpose_a"], transpose_b=spec["transpose_b"],
+                                             mode=spec["mode"], gate=y_cached, gate_mode=activation, emit_operand_copy=True)
+                            else:
+                                d = d.broadcast(out_shape)
+                                if activation == "tanh":
+                                    d = d * (1.0 - y_cached * y_cached)
+                                elif activation == "relu":
+                                    d = d * relu_mask(y_cached)
                             memo["dz"] = d.do_cache()
                             owned.append(memo["dz"])
                         return memo["dz"]

@@ -287,31 +287,46 @@ class Backend:
         return joined.permute(perm)
 
     def matmul(self, a: "Tensor", b: "Tensor", transpose_a: bool = False, transpose_b: bool = False, bias=None,
-               bias_mode: str = "none", activation: str = "none", mode: Optional[str] = None) -> "NonInlineTensor":
+               bias_mode: str = "none", activation: str = "none", mode: Optional[str] = None, gate: Optional["Tensor"] = None,
+               gate_mode: str = "none", emit_operand_copy: bool = False) -> "NonInlineTensor":
         """out = act(op(a) op(b) + bias) as ONE contraction kernel (`dls_matmul_ex`): what the reference can only spell
         as a host-unrolled `split(1) ... reduce(_ + _)` chain (TensorsSpec:337-344, :371-383).  `mode` None = this
         backend's gemm_mode; "fp32" is the CUDA-core kernel (same left-fold rounding as the chain), "tf32" / "bf16" run
-        on the tcgen05 tensor cores with fp32 accumulation."""
+        on the tcgen05 tensor cores with fp32 accumulation.
+        `gate` / `gate_mode` ("tanh" | "relu"): the product is multiplied by the activation derivative of the [m, n]
+        tensor `gate` in the same kernel (`delta * (1 - y * y)` / `delta * 1[y > 0]`, dls_matmul_gated).
+        `emit_operand_copy`: the kernel also leaves the result in the mode's operand type on the output buffer, for a
+        contraction that consumes it next."""
         if len(a.shape) != 2 or len(b.shape) != 2:
             raise ValueError("matmul: operands must be matrices, got %r and %r" % (a.shape, b.shape))
         m, k = (a.shape[1], a.shape[0]) if transpose_a else (a.shape[0], a.shape[1])
         n, k2 = (b.shape[0], b.shape[1]) if transpose_b else (b.shape[1], b.shape[0])
         if k != k2:
             raise ValueError("matmul: inner dimensions differ (%d vs %d)" % (k, k2))
+        gm = {"none": 0, "tanh": 1, "relu": 2}[gate_mode]
+        if gm and (gate is None or gate.size != m * n):
+            raise ValueError("matmul: gate must have %d elements" % (m * n))
         opts = N.GemmOpts(mode={None: -1, "fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}[mode],
                           bias_mode={"none": 0, "row": 1, "col": 2}[bias_mode],
-                          activation={"none": 0, "tanh": 1, "relu": 2}[activation], reserved=0)
+                          activation={"none": 0, "tanh": 1, "relu": 2}[activation], flags=(1 if emit_operand_copy else 0) | (gm << 8))
         if opts.bias_mode and (bias is None or bias.size != (m if bias_mode == "row" else n)):
             raise ValueError("matmul: bias must have %d elements" % (m if bias_mode == "row" else n))
 
         def produce():
             ba, bb = a._buffer(), b._buffer()
             bbias = bias._buffer() if opts.bias_mode else None
+            bgate = gate._buffer() if gm else None
             h = C.c_void_p()
-            N.check(N.lib.dls_matmul_ex(self.ctx, ba.handle, bb.handle, bbias.handle if bbias else None, m, n, k,
-                                        int(transpose_a), int(transpose_b), C.byref(opts), None, 0, C.byref(h), None))
+            N.check(N.lib.dls_matmul_gated(self.ctx, ba.handle, bb.handle, bbias.handle if bbias else None,
+                                           bgate.handle if bgate else None, m, n, k, int(transpose_a), int(transpose_b),
+                                           C.byref(opts), None, 0, C.byref(h), None))
             return DeviceBuffer(self, h, m * n)
-        return ProducedTensor(self, produce, [m, n], a.padding)
+        out = ProducedTensor(self, produce, [m, n], a.padding)
+        if not opts.bias_mode and activation == "none" and not gm:
+            # a consumer that multiplies this product by an activation derivative may re-issue it with the gate fused
+            # (layers.linear backward) as long as nobody has produced it yet
+            out._ungated = dict(a=a, b=b, transpose_a=transpose_a, transpose_b=transpose_b, mode=mode)
+        return out
 
     # -- 'same' 3x3 convolution without an im2col matrix (csrc/conv.cu; TensorsSpec:144-210 spells it with nine translates) --
     _MODES = {None: -1, "fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}

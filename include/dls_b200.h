@@ -188,11 +188,22 @@ typedef struct dls_gemm_opts {
   int32_t mode;        /* enum dls_gemm_mode, or -1 = context default */
   int32_t bias_mode;   /* enum dls_bias_mode   */
   int32_t activation;  /* enum dls_activation  */
-  int32_t reserved;
+  int32_t flags;       /* DLS_GEMM_EMIT_OPERAND_COPY | (enum dls_gate << 8) */
 } dls_gemm_opts;
+/* flags bit 0: the kernel also writes the result once more in the mode's operand type (bf16), kept as the output buffer's
+ * operand copy, so a contraction that consumes the result next starts without a staging pass (BF16 mode; ignored elsewhere). */
+#define DLS_GEMM_EMIT_OPERAND_COPY 1
+/* flags bits 8-9, dls_matmul_gated: out = (op(A) op(B) [+ bias, activation]) * act'(gate), gate an [M, N] fp32 buffer -- the
+ * delta a custom layer's backward sends down, `delta * (1 - y * y)` (tanh; FloatLayers.scala derivative rules restated for
+ * tensors) or `delta * min(y * FLT_MAX, 1)` (= 1[y > 0], relu), evaluated in the epilogue of the contraction that produces
+ * `delta` instead of by a second elementwise launch over the materialised product.  Same nodes, one rounding each. */
+enum dls_gate { DLS_GATE_NONE = 0, DLS_GATE_TANH = 1, DLS_GATE_RELU = 2 };
 int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k, int transpose_a,
                   int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
                   dls_event **done);
+int dls_matmul_gated(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, dls_buf *gate, size_t m, size_t n, size_t k,
+                     int transpose_a, int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps,
+                     dls_buf **out, dls_event **done);
 
 /* ---- 'same' 3x3 convolution of NHWC tensors with [3,3,Cin,Cout] weights, without an im2col matrix.  The reference spells
  * a convolution as nine `translate`d views, `join` and an unrolled matmul (TensorsSpec:144-210 `convolute`,

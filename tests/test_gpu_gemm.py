@@ -122,3 +122,68 @@ def test_sum_axis(backends, shape):
     if k <= 5000:
         fold = O.sum_axis(O.tensor(x), 1).flat_array().reshape(outer, inner)
         assert (np.abs(got - fold) / scale).max() <= 1e-5
+
+
+GATED = [
+    # m, n, k, ta, tb
+    (256, 512, 128, False, False),
+    (300, 520, 200, True, False),      # ragged, A MN-major (the dX layout of a feature-major layer)
+    (500, 128, 10, True, False),       # C1: delta of the hidden layer, K = 10
+    (64, 250, 4096, False, True),      # few tiles, long K: split-K (the gate runs in the reduce pass)
+    (33, 7, 20, False, False),         # N % 4 != 0: direct-store epilogue, scalar gate loads
+]
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tf32", "bf16"])
+@pytest.mark.parametrize("gate_mode", ["tanh", "relu"])
+@pytest.mark.parametrize("shape", GATED, ids=["%dx%dx%d-%s%s" % (s[0], s[1], s[2], "T" if s[3] else "N", "T" if s[4] else "N") for s in GATED])
+def test_gated_product_equals_the_product_then_the_elementwise_tree(backends, mode, gate_mode, shape):
+    """dls_matmul_gated: (a b) * act'(g) in the contraction's epilogue must equal, bit for bit, the plain product followed by
+    the elementwise tree a layer's backward builds (`d * (1 - y * y)`, `d * min(y * FLT_MAX, 1)`)."""
+    O, B = backends
+    m, n, k, ta, tb = shape
+    a, b = operands(m, n, k, ta, tb, seed=m + n + k)
+    rng = np.random.RandomState(7)
+    g = rng.standard_normal((m, n)).astype(np.float32)
+    if gate_mode == "relu":
+        g = np.maximum(g, 0)
+        g[0, :3] = [1e-40, 3e-39, 0.0][:min(3, n)]          # subnormal activations: the mask is fractional there, as in the tree
+    else:
+        g = np.tanh(g)
+    at, bt, gt = B.tensor(a), B.tensor(b), B.tensor(g).do_cache()
+    got = B.matmul(at, bt, transpose_a=ta, transpose_b=tb, mode=mode, gate=gt, gate_mode=gate_mode).flat_array()
+    plain = B.matmul(at, bt, transpose_a=ta, transpose_b=tb, mode=mode).do_cache()
+    if gate_mode == "tanh":
+        tree = plain * (1.0 - gt * gt)
+    else:
+        tree = plain * B.minimum(gt * 3.4028234663852886e38, B.scalar(1.0))
+    want = tree.flat_array()
+    assert (got.view(np.uint32) == want.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("shape", [(256, 512, 128), (300, 520, 200), (64, 248, 4096), (128, 10, 500)],
+                         ids=["256x512x128", "300x520x200", "splitk-64x248x4096", "128x10x500"])
+def test_emitted_operand_copy_is_the_staged_copy(backends, shape):
+    """DLS_GEMM_EMIT_OPERAND_COPY: the bf16 copy written by the epilogue is what the staging pass would have produced -- a
+    contraction consuming the result gives the same bits with one launch fewer, in both operand orientations."""
+    O, B = backends
+    m, n, k = shape
+    be = B.default_backend()
+    a, b = operands(m, n, k, False, False, seed=3)
+    rng = np.random.RandomState(4)
+    w_right = rng.standard_normal((n, 96)).astype(np.float32)       # c [m, n] . w [n, 96]: c is K-major
+    w_left = rng.standard_normal((m, 72)).astype(np.float32)        # c^T [n, m] . w [m, 72]: c is MN-major
+    outs, launches = [], []
+    for emit in (False, True):
+        c = B.matmul(B.tensor(a), B.tensor(b), mode="bf16", activation="tanh", emit_operand_copy=emit).do_cache()
+        wr, wl = B.tensor(w_right).do_cache(), B.tensor(w_left).do_cache()
+        wr.flat_array(), wl.flat_array()
+        n0 = be.stats()["kernel_launches"]
+        r1 = B.matmul(c, wr, mode="bf16").flat_array()
+        n1 = be.stats()["kernel_launches"]
+        r2 = B.matmul(c, wl, transpose_a=True, mode="bf16").flat_array()
+        outs.append((c.flat_array(), r1, r2))
+        launches.append(n1 - n0)
+    for x, y in zip(outs[0], outs[1]):
+        assert (x.view(np.uint32) == y.view(np.uint32)).all()
+    assert launches[1] == launches[0] - 1, launches
