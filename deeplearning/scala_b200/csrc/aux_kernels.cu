@@ -208,6 +208,117 @@ __global__ void __launch_bounds__(kBlock) sum_axis_finish_kernel(const float *__
   if ((threadIdx.x & 31) == 0) out[o * inner + col] = s;
 }
 
+// One-launch forms for the bias gradients of a training step (outer == 1, [k, inner] summed over its rows), where a second
+// launch costs as much as the reduction itself.
+// (a) small matrices (a few thousand elements per 32-column group): a block owns 32 columns, its 8 warps stride the rows,
+//     one shared-memory fold.
+__global__ void __launch_bounds__(kBlock) sum_axis_small_kernel(const float *__restrict__ in, float *__restrict__ out, size_t k,
+                                                                size_t inner) {
+  __shared__ float part[kBlock / 32][33];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const size_t col = (size_t)blockIdx.x * 32 + lane;
+  float a0 = 0.f, a1 = 0.f;
+  if (col < inner) {
+    size_t r = w;
+    for (; r + kBlock / 32 < k; r += 2 * (kBlock / 32)) {
+      a0 += __ldg(in + r * inner + col);
+      a1 += __ldg(in + (r + kBlock / 32) * inner + col);
+    }
+    if (r < k) a0 += __ldg(in + r * inner + col);
+  }
+  part[w][lane] = a0 + a1;
+  __syncthreads();
+  if (w == 0 && col < inner) {
+    float s = part[0][lane];
+#pragma unroll
+    for (int i = 1; i < kBlock / 32; ++i) s += part[i][lane];
+    out[col] = s;
+  }
+}
+
+// (b) tall slabs with inner % 4 == 0 and inner <= 256: sum_axis_slab4's first stage, and the block that draws the last
+//     ticket folds the per-block partial rows in a fixed order (deterministic), so there is no finish launch.
+__global__ void __launch_bounds__(kBlock) sum_axis_slab4_ticket_kernel(const float *__restrict__ in, float *__restrict__ partial,
+                                                                       float *__restrict__ out, unsigned int *counter, size_t k,
+                                                                       size_t inner, size_t rows_per_block) {
+  __shared__ float4 part[kBlock];
+  __shared__ bool is_last;
+  const int inner4 = (int)(inner / 4);
+  const int lanes = kBlock / inner4;
+  const int c4 = threadIdx.x % inner4, rl = threadIdx.x / inner4;
+  const size_t r0 = (size_t)blockIdx.x * rows_per_block, r1 = min(k, r0 + rows_per_block);
+  float4 a[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rl < lanes) {
+    const float4 *p = reinterpret_cast<const float4 *>(in) + c4;
+    size_t r = r0 + rl;
+    for (; r + 3 * (size_t)lanes < r1; r += 4 * (size_t)lanes) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldcs(p + (r + (size_t)u * lanes) * inner4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u].x += v[u].x;
+        a[u].y += v[u].y;
+        a[u].z += v[u].z;
+        a[u].w += v[u].w;
+      }
+    }
+    for (; r < r1; r += lanes) {
+      const float4 v = __ldcs(p + r * inner4);
+      a[0].x += v.x;
+      a[0].y += v.y;
+      a[0].z += v.z;
+      a[0].w += v.w;
+    }
+  }
+  part[threadIdx.x] = make_float4((a[0].x + a[1].x) + (a[2].x + a[3].x), (a[0].y + a[1].y) + (a[2].y + a[3].y),
+                                  (a[0].z + a[1].z) + (a[2].z + a[3].z), (a[0].w + a[1].w) + (a[2].w + a[3].w));
+  __syncthreads();
+  if (rl == 0) {
+    float4 s = part[c4];
+    for (int l = 1; l < lanes; ++l) {
+      const float4 v = part[l * inner4 + c4];
+      s.x += v.x;
+      s.y += v.y;
+      s.z += v.z;
+      s.w += v.w;
+    }
+    reinterpret_cast<float4 *>(partial + (size_t)blockIdx.x * inner)[c4] = s;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rl < lanes) {
+    for (unsigned int b = rl; b < gridDim.x; b += lanes) {
+      const float4 v = __ldcg(reinterpret_cast<const float4 *>(partial + (size_t)b * inner) + c4);
+      t.x += v.x;
+      t.y += v.y;
+      t.z += v.z;
+      t.w += v.w;
+    }
+  }
+  part[threadIdx.x] = t;
+  __syncthreads();
+  if (rl == 0) {
+    float4 s = part[c4];
+    for (int l = 1; l < lanes; ++l) {
+      const float4 v = part[l * inner4 + c4];
+      s.x += v.x;
+      s.y += v.y;
+      s.z += v.z;
+      s.w += v.w;
+    }
+    reinterpret_cast<float4 *>(out)[c4] = s;
+  }
+  if (threadIdx.x == 0) *counter = 0u;   // ready for the next launch on this stream
+}
+
 int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, size_t k, size_t inner, float *out) {
   cudaStream_t st = ctx->streams[stream];
   if (outer * inner == 0) return DLS_OK;
@@ -217,7 +328,19 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
   }
   size_t cap = (size_t)ctx->sm_count * 8;
   const size_t lanes_wanted = (size_t)ctx->sm_count * kBlock * 4;
-  if (inner == 1 && k >= 64) {
+  if (outer == 1 && inner > 1 && k * std::min<size_t>(inner, 32) <= 16384 && inner <= 4096) {
+    sum_axis_small_kernel<<<(unsigned)((inner + 31) / 32), kBlock, 0, st>>>(in, out, k, inner);
+  } else if (outer == 1 && inner % 4 == 0 && inner <= kBlock && k >= 512 && ((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 15) == 0) {
+    size_t blocks = std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count, (k + 63) / 64));
+    const size_t rows_per_block = (k + blocks - 1) / blocks;
+    blocks = (k + rows_per_block - 1) / rows_per_block;
+    Block scratch;
+    int rc = alloc_block(ctx, blocks * inner * sizeof(float), stream, &scratch);
+    if (rc) return rc;
+    sum_axis_slab4_ticket_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(in, (float *)scratch.ptr, out, ctx->red_counter[stream], k, inner,
+                                                                     rows_per_block);
+    free_block(ctx, scratch);
+  } else if (inner == 1 && k >= 64) {
     size_t want = (outer + kBlock / 32 - 1) / (kBlock / 32);
     sum_axis_rows_kernel<<<(int)std::max<size_t>(1, std::min(want, cap)), kBlock, 0, st>>>(in, out, outer, k);
   } else if (inner <= kBlock && k >= 512 && outer * inner * 8 <= lanes_wanted && outer < 65536) {

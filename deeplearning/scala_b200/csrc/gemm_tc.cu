@@ -688,6 +688,13 @@ struct SplitPlan {
   int splits = 1, kb_per_split = 0, c_rows = 0;
 };
 
+// SMs a persistent launch may occupy now: all of them, minus the ones an in-flight collective of the data-parallel exchange
+// pins (one CTA per NCCL channel).  Split-K plans are sized with the same number -- a plan cut for 148 SMs but launched on
+// 144 runs its last four work items as a second wave and takes twice as long.
+static int usable_sms(const dls_ctx *ctx) {
+  return ctx->comm_pending.empty() ? ctx->sm_count : std::max(1, ctx->sm_count - ctx->exchange_sms);
+}
+
 template <bool TF32, bool A_MN, bool B_MN, int CONV = 0>
 static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mc,
                           float *C, int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct, const SplitPlan &sp,
@@ -702,7 +709,7 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * sp.splits;
   // one persistent CTA per SM; SMs hosting an in-flight collective (data-parallel exchange) are left to it
-  const int sms = ctx->comm_pending.empty() ? ctx->sm_count : std::max(1, ctx->sm_count - ctx->exchange_sms);
+  const int sms = usable_sms(ctx);
   const int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, sp.splits,
                                               sp.kb_per_split, sp.c_rows, cg, epi.gate, epi.gate_mode, epi.copy, epi.copy_ld);
@@ -784,8 +791,9 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   SplitPlan sp;
   sp.kb_per_split = num_kb;
   sp.c_rows = M;
-  if (tiles * 2 <= ctx->sm_count && num_kb >= 16 && N % 4 == 0) {
-    int want = std::min(ctx->sm_count / tiles, num_kb / 8);
+  const int sms = tc::usable_sms(ctx);
+  if (tiles * 2 <= sms && num_kb >= 16 && N % 4 == 0) {
+    int want = std::min(sms / tiles, num_kb / 8);
     sp.kb_per_split = (num_kb + want - 1) / want;
     sp.splits = (num_kb + sp.kb_per_split - 1) / sp.kb_per_split;
   }
@@ -953,7 +961,7 @@ int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int c
   const int tiles = (M + BM - 1) / BM;
   const int num_kb = (int)((P + 63) / 64);
   SplitPlan sp;
-  int want = std::max(1, std::min(ctx->sm_count / tiles, num_kb / 8));
+  int want = std::max(1, std::min(usable_sms(ctx) / tiles, num_kb / 8));
   sp.kb_per_split = (num_kb + want - 1) / want;
   sp.splits = (num_kb + sp.kb_per_split - 1) / sp.kb_per_split;
   const int m_pad = tiles * BM;

@@ -20,7 +20,7 @@ from typing import Optional, Sequence
 
 from . import tensors as T
 from .do import Do, sequence
-from .plugins import Plugins, Tape, TensorLayer, broadcast_then_sum
+from .plugins import Plugins, Tape, TensorLayer, TensorWeight, broadcast_then_sum
 
 _BIG = 3.4028234663852886e38
 
@@ -315,11 +315,16 @@ class Layers:
                             return T.matmul(dz, A, transpose_a=True, transpose_b=transpose_a)
                         return T.matmul(A, dz, transpose_a=not transpose_a)
 
-                    ta.backward(do_delta.map(delta_a))
-                    tb.backward(do_delta.map(delta_b))
+                    # weights first: their gradients are complete the moment dz exists, and under data parallelism the
+                    # large ones leave for the all-reduce right away and travel under the rest of the backward pass --
+                    # descending into the layer below first would put every weight gradient at the END of the step
                     if bias_mode != "none":
                         axis = 1 if bias_mode == "row" else 0
                         tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), axis)))
+                    order = [(ta, delta_a, a), (tb, delta_b, b)]
+                    order.sort(key=lambda e: 0 if isinstance(e[2], TensorWeight) else 1)
+                    for tape, delta, _ in order:
+                        tape.backward(do_delta.map(delta))
                 return run
             return y, backward, owned
         return self._pinned(inputs, build)
@@ -413,10 +418,11 @@ class Layers:
                         dw = T.matmul(col(), dz_of(d).reshape([m, cout]), transpose_a=True)     # [Cin*9, Cout]
                         return dw.reshape([cin, 3, 3, cout]).permute([1, 2, 0, 3])
 
-                    tx.backward(do_delta.map(delta_x))
-                    tw.backward(do_delta.map(delta_w))
+                    # weights before the input, for the same reason as in `linear`
                     if bias is not None:                             # the zeros of a sampled delta add nothing
                         tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_sampled(d).reshape([m // (s * s), cout]), 0)))
+                    tw.backward(do_delta.map(delta_w))
+                    tx.backward(do_delta.map(delta_x))
                 return run
             return y, backward, owned
 

@@ -29,7 +29,7 @@ def main():
     dist = None
     exchange = None
     torch.cuda.set_device(local)
-    be = B.Backend(device=local)
+    be = B.Backend(device=local, gemm_mode=os.environ.get("DLS_GEMM_MODE", "bf16"))
     if world > 1:
         import torch.distributed as dist
         from deeplearning.scala_b200.harness import Exchange
