@@ -2,6 +2,7 @@
 // NVSwitch.  New functionality: the reference has no collective (its only multi-device mechanism is the shared
 // command-queue pool, OpenCL:423-448).  libnccl is bound at run time with dlopen so that the library loads on
 // machines without NCCL; DLS_NCCL_LIB overrides the library path.
+#include <climits>
 #include <dlfcn.h>
 #include <stdlib.h>
 #include <string.h>
@@ -19,8 +20,21 @@ typedef int (*fn_comm_destroy)(nccl_comm_t);
 typedef const char *(*fn_get_error_string)(int);
 typedef int (*fn_group)(void);
 typedef int (*fn_all_gather)(const void *, void *, size_t, int, nccl_comm_t, cudaStream_t);
+// ncclConfig_t as NCCL 2.17 laid it out (nccl.h, `ncclConfig_v21700`); later releases append fields and accept this prefix,
+// told apart by `size` / `version`.  Only maxCTAs is set: the cap on the CTAs (= SMs) a collective of THIS communicator
+// occupies.  An environment variable cannot do this reliably: NCCL caches NCCL_MAX_NCHANNELS on first use, and the
+// process may have created other communicators (torch.distributed) before this one.
+struct nccl_config_v21700 {
+  size_t size;
+  unsigned int magic, version;
+  int blocking, cga_cluster_size, min_ctas, max_ctas;
+  const char *net_name;
+  int split_share;
+};
+typedef int (*fn_comm_init_rank_config)(nccl_comm_t *, int, nccl_unique_id, int, nccl_config_v21700 *);
 
 struct NcclApi {
+  fn_comm_init_rank_config comm_init_rank_config = nullptr;
   void *handle = nullptr;
   fn_get_unique_id get_unique_id = nullptr;
   fn_comm_init_rank comm_init_rank = nullptr;
@@ -57,6 +71,7 @@ int load_nccl() {
   g_nccl.group_start = (fn_group)dlsym(h, "ncclGroupStart");
   g_nccl.group_end = (fn_group)dlsym(h, "ncclGroupEnd");
   g_nccl.all_gather = (fn_all_gather)dlsym(h, "ncclAllGather");
+  g_nccl.comm_init_rank_config = (fn_comm_init_rank_config)dlsym(h, "ncclCommInitRankConfig");
   if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.all_reduce || !g_nccl.comm_destroy) {
     dls::set_error("libnccl is missing a required symbol");
     dlclose(h);
@@ -119,14 +134,34 @@ int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size) 
   nccl_unique_id id;
   memcpy(id.internal, id128, 128);
   nccl_comm_t comm = nullptr;
-  int e = g_nccl.comm_init_rank(&comm, world_size, id, rank);
+  // a collective kernel runs one CTA per channel; a persistent one-CTA-per-SM GEMM launched next to it would otherwise
+  // queue the CTAs that find their SM taken behind the whole first wave (measured: the overlap hid almost nothing).  The
+  // gradient buckets are a few MB: four CTAs move them at NVLink speed and leave 144 SMs to the backward kernels.
+  int ctas = 4;
+  if (const char *e = getenv("DLS_EXCHANGE_CTAS")) ctas = atoi(e);
+  if (ctas < 1 || ctas > 64) ctas = 4;
+  int e = -1;
+  if (g_nccl.comm_init_rank_config) {
+    nccl_config_v21700 cfg;
+    cfg.size = sizeof(cfg);
+    cfg.magic = 0xcafebeef;
+    cfg.version = 21700;
+    cfg.blocking = cfg.cga_cluster_size = cfg.min_ctas = cfg.split_share = INT_MIN;   // NCCL_CONFIG_UNDEF_INT
+    cfg.net_name = nullptr;
+    cfg.max_ctas = ctas;
+    e = g_nccl.comm_init_rank_config(&comm, world_size, id, rank, &cfg);
+    if (e) comm = nullptr;
+  }
+  bool capped = e == 0;
+  if (e) e = g_nccl.comm_init_rank(&comm, world_size, id, rank);
   if (e) return nccl_fail(e, "ncclCommInitRank");
   ctx->nccl_comm = comm;
-  {
-    // a collective kernel runs one CTA per channel; a persistent one-CTA-per-SM GEMM launched next to it would otherwise
-    // queue the CTAs that find their SM taken behind the whole first wave (measured: the overlap hid almost nothing)
-    const char *e = getenv("NCCL_MAX_NCHANNELS");
-    const int ch = e ? atoi(e) : 0;
+  if (capped) {
+    ctx->exchange_sms = ctas;
+  } else {
+    // no per-communicator cap in this libnccl: fall back to what the environment promises
+    const char *env = getenv("NCCL_MAX_NCHANNELS");
+    const int ch = env ? atoi(env) : 0;
     ctx->exchange_sms = ch > 0 && ch <= 64 ? ch : 16;
   }
   ctx->comm_rank = rank;

@@ -633,6 +633,117 @@ __global__ void __launch_bounds__(kBlock, 3) ew_gather4_kernel(const __grid_cons
   if (A.reduce) grid_sum_finish(tsum, A.red);
 }
 
+// ---- N2 tiled path: views whose unit-stride dim is NOT the output's inner dim (permute / transpose, Tensors:1008-1030;
+// gather semantics KB:348-411 unchanged) ------------------------------------------------------------------------------
+// With one lane per inner output element such a leaf is read with 4-byte gathers, a 32-byte sector each (measured: 0.26 of
+// HBM peak, DRAM reads 2.2 x algorithmic).  Here a CTA owns a TI x 32 tile of output dims (0, vd), vd = the launch dim
+// along which every leaf is contiguous: the program is evaluated with the LANES ALONG vd (each warp load is one 128-byte
+// line of the leaf), the results cross a padded shared-memory tile, and are stored with the lanes along the output's
+// inner dim (128-byte lines again).  Coordinates, bounds checks and arithmetic are the interpreter's own, per element.
+struct G4TArgs {
+  int32_t vd;                          // launch dim (innermost-first numbering) the lanes follow while loading
+  uint32_t n_tiles;
+  uint32_t dim0, dimv;                 // extents of dims 0 and vd
+  FastDiv tiles_i, tiles_j;            // tile counts along dim 0 and dim vd
+  uint32_t ostride[kMaxRank];          // output element stride per launch dim (ostride[0] == 1)
+};
+
+template <int U, int R>   // U = TI / 8 rows of the tile per thread
+__global__ void __launch_bounds__(kBlock, 3) ew_gather4t_kernel(const __grid_constant__ G4Args A, const __grid_constant__ G4TArgs T) {
+  constexpr int TI = 8 * U;
+  extern __shared__ float g4t_smem[];  // [slot][U][thread], then tile[TI][33]
+  float *tile = g4t_smem + (size_t)A.n_slots * U * kBlock;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (uint32_t tid = blockIdx.x; tid < T.n_tiles; tid += gridDim.x) {
+    int gb[R];
+    uint32_t rest = fast_div(tid, T.tiles_i);
+    const uint32_t ib = tid - rest * T.tiles_i.d;
+    uint32_t q = fast_div(rest, T.tiles_j);
+    const uint32_t jb = rest - q * T.tiles_j.d;
+    rest = q;
+    uint32_t obase = 0;
+#pragma unroll
+    for (int d = 1; d < R; ++d) {
+      if (d == T.vd) {
+        gb[d] = (int)(jb * 32u);
+      } else {
+        q = fast_div(rest, A.dims[d]);
+        gb[d] = (int)(rest - q * A.dims[d].d);
+        rest = q;
+        obase += (uint32_t)gb[d] * T.ostride[d];
+      }
+    }
+    gb[0] = (int)(ib * TI);
+    int g[U][R];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+#pragma unroll
+      for (int d = 0; d < R; ++d) g[u][d] = gb[d];
+      const uint32_t i = (uint32_t)gb[0] + w + 8 * u, j = jb * 32u + lane;
+      if (i < T.dim0 && j < T.dimv) {                  // elements past the edge evaluate the tile's origin (never stored)
+        g[u][0] = (int)i;
+#pragma unroll
+        for (int d = 1; d < R; ++d)
+          if (d == T.vd) g[u][d] = (int)j;
+      }
+    }
+    float acc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) acc[u] = 0.f;
+    for (int pc = 0;; ++pc) {
+      const Instr in = A.code[pc];
+      const int op = in.op;
+      if (op == OP_END) break;
+      float s[U][1];
+      if (in.src == SRC_LEAF) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) g4_leaf<1, R>(A, in.operand, g[u], s[u]);
+      } else if (in.src == SRC_LIT) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) s[u][0] = __uint_as_float(in.operand);
+      } else if (in.src == SRC_SLOT) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) s[u][0] = g4t_smem[(in.operand * U + u) * kBlock + threadIdx.x];
+      }
+      if (op <= OP_RMOD) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) acc[u] = apply_binary(op, acc[u], s[u][0]);
+      } else if (op <= OP_LOG) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) acc[u] = apply_unary(op, acc[u]);
+      } else if (op == OP_SAVE) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) g4t_smem[(in.operand * U + u) * kBlock + threadIdx.x] = acc[u];
+      } else if (op == OP_MAC || op == OP_MSUB) {
+        float f[U][1];
+#pragma unroll
+        for (int u = 0; u < U; ++u) g4_leaf<1, R>(A, in.aux, g[u], f[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const float pr = __fmul_rn(f[u][0], s[u][0]);
+          acc[u] = op == OP_MAC ? __fadd_rn(acc[u], pr) : __fsub_rn(acc[u], pr);
+        }
+      }                                                // OP_STORE: single root, stored below
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) tile[(w + 8 * u) * 33 + lane] = acc[u];
+    __syncthreads();
+    // store: row jj of the tile = TI consecutive inner elements of the output
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int jj = w + 8 * k;
+      const uint32_t j = jb * 32u + jj;
+#pragma unroll
+      for (int h = 0; h < TI / 32; ++h) {
+        const int ii = lane + 32 * h;
+        const uint32_t i = (uint32_t)gb[0] + ii;
+        if (i < T.dim0 && j < T.dimv) A.out[(size_t)obase + (size_t)j * T.ostride[T.vd] + i] = tile[ii * 33 + jj];
+      }
+    }
+    __syncthreads();
+  }
+}
+
 constexpr int kG4SmemLimit = 75 * 1024;   // three CTAs per SM: slots + root staging of the widest im2col (2 x 9 roots x 4 KB)
 
 // ---- host side -------------------------------------------------------------------------------------------------------
@@ -645,6 +756,10 @@ int query_ew_occupancy(dls_ctx *ctx) {
   DLS_G4_ATTR(4, 1, 4) DLS_G4_ATTR(1, 1, 4) DLS_G4_ATTR(4, 2, 4) DLS_G4_ATTR(1, 2, 4)
   DLS_G4_ATTR(4, 1, 8) DLS_G4_ATTR(1, 1, 8) DLS_G4_ATTR(4, 2, 8) DLS_G4_ATTR(1, 2, 8)
 #undef DLS_G4_ATTR
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<8, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
 #define DLS_VEC_ATTR(O, UU) \
   DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<O, UU>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   DLS_VEC_ATTR(0, 1) DLS_VEC_ATTR(0, 2) DLS_VEC_ATTR(0, 4)
@@ -805,6 +920,66 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
     for (int i = 0; i < P.n_params; ++i) A.params[i] = params[i]->ptr;
     memcpy(A.leaves, P.g4leaves.data(), P.g4leaves.size() * sizeof(G4Leaf));
     memcpy(A.code, P.code.data(), P.code.size() * sizeof(Instr));
+    // tiled path: every leaf that depends on the inner output dim is strided along it and contiguous along ONE other launch
+    // dim (a permute / transpose view, possibly under elementwise ops); single root, no fused reduction
+    static const int tiled_off = [] {
+      const char *e = getenv("DLS_G4_TILED");
+      return e && atoi(e) == 0 ? 1 : 0;
+    }();
+    int vd = 0;
+    if (!tiled_off && !reduce_sum && P.n_roots == 1 && r >= 2 && P.n_elems < (1ll << 31)) {
+      bool ok = true, any = false;
+      for (const G4Leaf &L : P.g4leaves) {
+        bool scalar = true;
+        for (int d = 0; d < r; ++d) scalar = scalar && L.ls[d] == 0;
+        for (int c = 0; c < L.n_checks; ++c) scalar = scalar && L.chk[c].shift == 0;
+        if (scalar) continue;                                   // a broadcast value: any lane order reads it equally well
+        int unit = -1;
+        for (int d = 1; d < r; ++d)
+          if (L.ls[d] == 1) unit = d;
+        for (int c = 0; c < L.n_checks; ++c) ok = ok && L.chk[c].shift == 0;   // dyadic rows carry their own address term
+        if (L.ls[0] == 1 || L.ls[0] == 0 || unit < 0 || (vd && unit != vd)) ok = false;
+        if (!ok) break;
+        vd = unit;
+        any = true;
+      }
+      if (!(ok && any && P.out_shape[r - 1 - vd] >= 32 && W >= 16)) vd = 0;
+    }
+    if (vd) {
+      static thread_local G4TArgs T;
+      const int TI = W >= 48 ? 64 : 32;
+      T.vd = vd;
+      T.dim0 = (uint32_t)W;
+      T.dimv = (uint32_t)P.out_shape[r - 1 - vd];
+      const long long ti = (W + TI - 1) / TI, tj = (T.dimv + 31) / 32;
+      T.tiles_i = mk_div(ti);
+      T.tiles_j = mk_div(tj);
+      long long others = 1, os = 1;
+      for (int d = 0; d < kMaxRank; ++d) {
+        T.ostride[d] = d < r ? (uint32_t)os : 0u;
+        if (d < r) {
+          if (d != 0 && d != vd) others *= P.out_shape[r - 1 - d];
+          os *= P.out_shape[r - 1 - d];
+        }
+      }
+      T.n_tiles = (uint32_t)(ti * tj * others);
+      const int Ut = TI / 8;
+      const size_t smem = (size_t)P.n_slots * Ut * kBlock * sizeof(float) + (size_t)TI * 33 * sizeof(float);
+      if (smem <= (size_t)kG4SmemLimit && ti * tj * others < (1ll << 31)) {
+        int per_sm = 0;
+        if (Ut == 8) DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4t_kernel<8, 8>, kBlock, smem));
+        else DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4t_kernel<4, 8>, kBlock, smem));
+        if (per_sm < 1) per_sm = 1;
+        const int grid = (int)std::max<long long>(1, std::min<long long>(T.n_tiles, (long long)ctx->sm_count * per_sm));
+        if (Ut == 8 && r <= 4) ew_gather4t_kernel<8, 4><<<grid, kBlock, smem, st>>>(A, T);
+        else if (Ut == 8) ew_gather4t_kernel<8, 8><<<grid, kBlock, smem, st>>>(A, T);
+        else if (r <= 4) ew_gather4t_kernel<4, 4><<<grid, kBlock, smem, st>>>(A, T);
+        else ew_gather4t_kernel<4, 8><<<grid, kBlock, smem, st>>>(A, T);
+        DLS_CUDA(cudaGetLastError());
+        ctx->stats.kernel_launches++;
+        return DLS_OK;
+      }
+    }
     static const int forced_g4_unroll = [] {
       const char *e = getenv("DLS_G4_UNROLL");
       return e ? atoi(e) : 0;

@@ -161,6 +161,57 @@ def test_permute_bit_exact(backends, perm):
     assert_bits(np.ascontiguousarray(x.transpose(perm)).reshape(-1), got)
 
 
+TILED = [
+    # shape, permutation: sizes that reach the tiled path of the gather kernel (the dim the source is contiguous along has
+    # >= 32 elements, the output's inner dim >= 16), ragged in both tile directions
+    ((70, 45), [1, 0]),
+    ((33, 129), [1, 0]),
+    ((64, 64), [1, 0]),
+    ((3, 40, 50), [0, 2, 1]),
+    ((5, 17, 19, 37), [0, 3, 1, 2]),      # NHWC -> NCHW
+    ((5, 37, 17, 19), [0, 2, 3, 1]),      # NCHW -> NHWC
+    ((36, 7, 48), [2, 1, 0]),
+    ((2, 3, 34, 5, 40), [4, 1, 0, 3, 2]), # rank 5: the general-rank instantiation
+]
+
+
+@pytest.mark.parametrize("shape,perm", TILED, ids=["%s-%s" % ("x".join(map(str, s)), "".join(map(str, p))) for s, p in TILED])
+def test_tiled_permute_bit_exact(backends, shape, perm):
+    """Tensors:1008-1030 `permute` / `transpose` where the source's unit-stride dim is not the output's inner dim: the
+    shared-memory tiled path must place every element exactly where the one-lane-per-element path does."""
+    O, B = backends
+    x = rnd(sum(shape), *shape)
+    want, got, _ = both(backends, lambda M: M.tensor(x).permute(perm))
+    assert_bits(want, got)
+    assert_bits(np.ascontiguousarray(x.transpose(perm)).reshape(-1), got)
+    plan = B.default_backend().describe_plan([B.tensor(x).permute(perm).closure()], [shape[p] for p in perm])
+    assert "gather" in plan
+
+
+def test_tiled_path_under_elementwise_ops_and_padding(backends):
+    """The tiled path evaluates whole programs: a transposed view with a translate (bounds checks, padding) under
+    arithmetic with a second transposed view, a saved sub-expression and a broadcast scalar."""
+    a, b = rnd(31, 70, 45), rnd(32, 70, 45)
+
+    def build(M):
+        ta = M.tensor(a, padding=-3.5).translate([3, -2]).transpose()
+        tb = M.tensor(b).transpose()
+        u = ta * tb + M.scalar(0.25)
+        return M.tanh(u) * u - tb
+    want, got, _ = both(backends, build)
+    assert_ulp(want, got, ULP_TRANSCENDENTAL)
+    want, got, _ = both(backends, lambda M: M.tensor(a, padding=-3.5).translate([3, -2]).transpose() + M.tensor(b).transpose())
+    assert_bits(want, got)
+
+
+def test_mixed_orientation_keeps_the_row_path(backends):
+    """One leaf contiguous along the output's inner dim next to a transposed one: not a pure transposition; whatever path
+    runs, the bits are the oracle's."""
+    a, b = rnd(33, 48, 40), rnd(34, 40, 48)
+    want, got, _ = both(backends, lambda M: M.tensor(a).transpose() + M.tensor(b))
+    assert_bits(want, got)
+
+
 @pytest.mark.parametrize("offset", [[0, 0], [1, -2], [-3, 4], [7, 0], [0, -9], [20, 20]])
 def test_translate_with_padding_bit_exact(backends, offset):
     x = rnd(21, 9, 11)
