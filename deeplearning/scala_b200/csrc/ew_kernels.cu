@@ -452,14 +452,16 @@ struct G4Args {
   Instr code[kG4Code];
 };
 
+// `vd`: the launch dim the V elements of a lane run along (0 = the output's inner dim; the tiled kernel passes the dim its
+// leaves are contiguous along)
 template <int V, int R>
-__device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int *g, float *v) {
+__device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int *g, float *v, const int vd = 0) {
   const G4Leaf &L = A.leaves[li];
   const float *p = A.params[L.param];
   int addr = L.base;
 #pragma unroll
   for (int d = 0; d < R; ++d) addr += g[d] * L.ls[d];   // ls[d] == 0 and g[d] == 0 beyond the launch rank
-  const int step = L.ls[0];
+  const int step = L.ls[vd];
   unsigned valid = (1u << V) - 1u;
   const int nc = L.n_checks;
 #pragma unroll
@@ -472,13 +474,13 @@ __device__ __forceinline__ void g4_leaf(const G4Args &A, unsigned li, const int 
         const int idx = n >= 0 ? n >> C.shift : -((-n) >> C.shift);
         if ((unsigned)idx >= (unsigned)C.extent) valid = 0u;
         addr += idx * C.stride;
-      } else if (C.col != 0) {
+      } else if (C.col != vd || V == 1) {
         const int idx = g[C.col] * C.coef + C.off;
         if ((unsigned)idx >= (unsigned)C.extent) valid = 0u;
       } else {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-          const int idx = (g[0] + e) * C.coef + C.off;
+          const int idx = (g[vd] + e) * C.coef + C.off;
           if ((unsigned)idx >= (unsigned)C.extent) valid &= ~(1u << e);
         }
       }
@@ -648,96 +650,185 @@ struct G4TArgs {
   uint32_t ostride[kMaxRank];          // output element stride per launch dim (ostride[0] == 1)
 };
 
-template <int U, int R>   // U = TI / 8 rows of the tile per thread
-__global__ void __launch_bounds__(kBlock, 3) ew_gather4t_kernel(const __grid_constant__ G4Args A, const __grid_constant__ G4TArgs T) {
-  constexpr int TI = 8 * U;
-  extern __shared__ float g4t_smem[];  // [slot][U][thread], then tile[TI][33]
-  float *tile = g4t_smem + (size_t)A.n_slots * U * kBlock;
+// One leaf for the U tile rows of a thread.  The rows differ only in their dim-0 coordinate (g[0] + u * istep), so the
+// affine address and every bounds check that does not involve dim 0 are evaluated once; `live` masks rows / vectors that
+// lie outside the launch (they read nothing).  No dyadic rows here (the host keeps those programs on the row path).
+template <int V, int U, int R>
+__device__ __forceinline__ void g4t_leaf(const G4Args &A, unsigned li, const int *g, int istep, unsigned live, float (*v)[V], const int vd) {
+  const G4Leaf &L = A.leaves[li];
+  const float *p = A.params[L.param];
+  int addr = L.base;
+#pragma unroll
+  for (int d = 0; d < R; ++d) addr += g[d] * L.ls[d];
+  const int step = L.ls[vd], stepi = L.ls[0] * istep;
+  unsigned common = (1u << V) - 1u, rows = live;
+  const int nc = L.n_checks;
+#pragma unroll
+  for (int c = 0; c < kG4Checks; ++c) {
+    if (c < nc) {
+      const G4Check C = L.chk[c];
+      if (C.col == 0) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int idx = (g[0] + u * istep) * C.coef + C.off;
+          if ((unsigned)idx >= (unsigned)C.extent) rows &= ~(1u << u);
+        }
+      } else if (C.col == vd && V > 1) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+          const int idx = (g[C.col] + e) * C.coef + C.off;
+          if ((unsigned)idx >= (unsigned)C.extent) common &= ~(1u << e);
+        }
+      } else {
+        const int idx = g[C.col] * C.coef + C.off;
+        if ((unsigned)idx >= (unsigned)C.extent) common = 0u;
+      }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int a = addr + u * stepi;
+    const unsigned valid = (rows >> u) & 1u ? common : 0u;
+    if (V == 4 && step == 1 && valid == 15u && (a & 3) == 0) {
+      const float4 q = __ldg(reinterpret_cast<const float4 *>(p + a));
+      v[u][0] = q.x;
+      v[u][V > 1 ? 1 : 0] = q.y;
+      v[u][V > 2 ? 2 : 0] = q.z;
+      v[u][V > 3 ? 3 : 0] = q.w;
+    } else {
+#pragma unroll
+      for (int e = 0; e < V; ++e) v[u][e] = (valid >> e) & 1u ? __ldg(p + a + e * step) : L.padding;
+    }
+  }
+}
+
+// V elements per lane along vd, LJ lanes of a warp side by side along vd (tile width TJ = LJ * V; the other 32 / LJ lane
+// groups take further tile rows), U tile rows per thread: tile = TI x TJ with TI = 8 * (32 / LJ) * U.
+template <int V, int LJ, int U, int R>
+__global__ void __launch_bounds__(kBlock, 4) ew_gather4t_kernel(const __grid_constant__ G4Args A, const __grid_constant__ G4TArgs T) {
+  constexpr int RPW = 32 / LJ;                // tile rows a warp covers per unit
+  constexpr int TI = 8 * RPW * U, TJ = LJ * V;
+  constexpr int RS = TJ + (V == 4 ? 4 : 1);   // row stride of the tile: conflict-free both ways (V == 4 with the XOR below)
+  static_assert(TI % 32 == 0 && TJ % 8 == 0, "tile shape");
+  extern __shared__ float g4t_smem[];         // [slot][U][V][thread], then tile[TI][RS]
+  float *tile = g4t_smem + (size_t)A.n_slots * U * V * kBlock;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int row0 = w * RPW + lane / LJ, colv = (lane % LJ) * V;   // this thread's first tile row / first tile column
+  const int vd = T.vd;
+  const uint32_t ostride_v = T.ostride[vd];
   for (uint32_t tid = blockIdx.x; tid < T.n_tiles; tid += gridDim.x) {
-    int gb[R];
+    int g[R];
     uint32_t rest = fast_div(tid, T.tiles_i);
     const uint32_t ib = tid - rest * T.tiles_i.d;
     uint32_t q = fast_div(rest, T.tiles_j);
     const uint32_t jb = rest - q * T.tiles_j.d;
     rest = q;
     uint32_t obase = 0;
+    const uint32_t i0 = ib * TI + row0, j0 = jb * TJ + colv;
 #pragma unroll
     for (int d = 1; d < R; ++d) {
-      if (d == T.vd) {
-        gb[d] = (int)(jb * 32u);
+      if (d == vd) {
+        g[d] = (int)j0;
       } else {
         q = fast_div(rest, A.dims[d]);
-        gb[d] = (int)(rest - q * A.dims[d].d);
+        g[d] = (int)(rest - q * A.dims[d].d);
         rest = q;
-        obase += (uint32_t)gb[d] * T.ostride[d];
+        obase += (uint32_t)g[d] * T.ostride[d];
       }
     }
-    gb[0] = (int)(ib * TI);
-    int g[U][R];
+    g[0] = (int)i0;
+    unsigned live = 0u;                                // dimv % V == 0: a vector is inside or outside as a whole
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
+    for (int u = 0; u < U; ++u)
+      if (i0 + 8 * RPW * u < T.dim0 && j0 < T.dimv) live |= 1u << u;
+    float acc[U][V];
 #pragma unroll
-      for (int d = 0; d < R; ++d) g[u][d] = gb[d];
-      const uint32_t i = (uint32_t)gb[0] + w + 8 * u, j = jb * 32u + lane;
-      if (i < T.dim0 && j < T.dimv) {                  // elements past the edge evaluate the tile's origin (never stored)
-        g[u][0] = (int)i;
+    for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int d = 1; d < R; ++d)
-          if (d == T.vd) g[u][d] = (int)j;
-      }
-    }
-    float acc[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) acc[u] = 0.f;
+      for (int e = 0; e < V; ++e) acc[u][e] = 0.f;
     for (int pc = 0;; ++pc) {
       const Instr in = A.code[pc];
       const int op = in.op;
       if (op == OP_END) break;
-      float s[U][1];
+      float s[U][V];
       if (in.src == SRC_LEAF) {
-#pragma unroll
-        for (int u = 0; u < U; ++u) g4_leaf<1, R>(A, in.operand, g[u], s[u]);
+        g4t_leaf<V, U, R>(A, in.operand, g, 8 * RPW, live, s, vd);
       } else if (in.src == SRC_LIT) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) s[u][0] = __uint_as_float(in.operand);
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) s[u][e] = __uint_as_float(in.operand);
       } else if (in.src == SRC_SLOT) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) s[u][0] = g4t_smem[(in.operand * U + u) * kBlock + threadIdx.x];
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) s[u][e] = g4t_smem[((in.operand * U + u) * V + e) * kBlock + threadIdx.x];
       }
       if (op <= OP_RMOD) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) acc[u] = apply_binary(op, acc[u], s[u][0]);
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[u][e] = apply_binary(op, acc[u][e], s[u][e]);
       } else if (op <= OP_LOG) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) acc[u] = apply_unary(op, acc[u]);
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[u][e] = apply_unary(op, acc[u][e]);
       } else if (op == OP_SAVE) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) g4t_smem[(in.operand * U + u) * kBlock + threadIdx.x] = acc[u];
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+          for (int e = 0; e < V; ++e) g4t_smem[((in.operand * U + u) * V + e) * kBlock + threadIdx.x] = acc[u][e];
       } else if (op == OP_MAC || op == OP_MSUB) {
-        float f[U][1];
+        float f[U][V];
+        g4t_leaf<V, U, R>(A, in.aux, g, 8 * RPW, live, f, vd);
 #pragma unroll
-        for (int u = 0; u < U; ++u) g4_leaf<1, R>(A, in.aux, g[u], f[u]);
+        for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const float pr = __fmul_rn(f[u][0], s[u][0]);
-          acc[u] = op == OP_MAC ? __fadd_rn(acc[u], pr) : __fsub_rn(acc[u], pr);
-        }
+          for (int e = 0; e < V; ++e) {
+            const float pr = __fmul_rn(f[u][e], s[u][e]);
+            acc[u][e] = op == OP_MAC ? __fadd_rn(acc[u][e], pr) : __fsub_rn(acc[u][e], pr);
+          }
       }                                                // OP_STORE: single root, stored below
     }
+    // tile[i][j]: element (i, j) lives in column j ^ ((i >> 3) & 3) of row i (V == 4), so that both the 16-byte row writes
+    // here and the column reads below touch 32 different banks
 #pragma unroll
-    for (int u = 0; u < U; ++u) tile[(w + 8 * u) * 33 + lane] = acc[u];
+    for (int u = 0; u < U; ++u) {
+      const int il = row0 + 8 * RPW * u;
+      if (V == 4) {
+        float a0 = acc[u][0], a1 = acc[u][V > 1 ? 1 : 0], a2 = acc[u][V > 2 ? 2 : 0], a3 = acc[u][V > 3 ? 3 : 0];
+        const int sw = (il >> 3) & 3;                  // q[e ^ sw] = a[e]
+        if (sw & 1) {
+          float t0 = a0; a0 = a1; a1 = t0;
+          float t1 = a2; a2 = a3; a3 = t1;
+        }
+        if (sw & 2) {
+          float t0 = a0; a0 = a2; a2 = t0;
+          float t1 = a1; a1 = a3; a3 = t1;
+        }
+        *reinterpret_cast<float4 *>(tile + il * RS + colv) = make_float4(a0, a1, a2, a3);
+      } else {
+        tile[il * RS + colv] = acc[u][0];
+      }
+    }
     __syncthreads();
-    // store: row jj of the tile = TI consecutive inner elements of the output
+    // store: row jj of the tile = TI consecutive inner elements of the output; lane (+ 32 h) = inner coordinate
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int jj = w + 8 * k;
-      const uint32_t j = jb * 32u + jj;
-#pragma unroll
-      for (int h = 0; h < TI / 32; ++h) {
-        const int ii = lane + 32 * h;
-        const uint32_t i = (uint32_t)gb[0] + ii;
-        if (i < T.dim0 && j < T.dimv) A.out[(size_t)obase + (size_t)j * T.ostride[T.vd] + i] = tile[ii * 33 + jj];
+    for (int h = 0; h < TI / 32; ++h) {
+      const int ii = lane + 32 * h;
+      const uint32_t i = ib * TI + ii;
+      const int swz = V == 4 ? (ii >> 3) & 3 : 0;
+      const float *trow = tile + ii * RS;
+      float *optr = A.out + (size_t)obase + (size_t)(jb * TJ + w) * ostride_v + i;
+      const bool full = ib * TI + TI <= T.dim0 && jb * TJ + TJ <= T.dimv;
+      if (full) {
+#pragma unroll 8
+        for (int k = 0; k < TJ / 8; ++k) optr[(size_t)(8 * k) * ostride_v] = trow[(w + 8 * k) ^ swz];
+      } else if (i < T.dim0) {
+#pragma unroll 4
+        for (int k = 0; k < TJ / 8; ++k)
+          if (jb * TJ + w + 8 * k < T.dimv) optr[(size_t)(8 * k) * ostride_v] = trow[(w + 8 * k) ^ swz];
       }
     }
     __syncthreads();
@@ -756,10 +847,12 @@ int query_ew_occupancy(dls_ctx *ctx) {
   DLS_G4_ATTR(4, 1, 4) DLS_G4_ATTR(1, 1, 4) DLS_G4_ATTR(4, 2, 4) DLS_G4_ATTR(1, 2, 4)
   DLS_G4_ATTR(4, 1, 8) DLS_G4_ATTR(1, 1, 8) DLS_G4_ATTR(4, 2, 8) DLS_G4_ATTR(1, 2, 8)
 #undef DLS_G4_ATTR
-  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
-  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<8, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
-  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<4, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
-  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
+#define DLS_G4T_ATTR(VV, LL, UU, RR) \
+  DLS_CUDA(cudaFuncSetAttribute(ew_gather4t_kernel<VV, LL, UU, RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG4SmemLimit));
+  DLS_G4T_ATTR(4, 32, 4, 4) DLS_G4T_ATTR(4, 32, 4, 8) DLS_G4T_ATTR(4, 16, 2, 4) DLS_G4T_ATTR(4, 16, 2, 8)
+  DLS_G4T_ATTR(4, 8, 1, 4) DLS_G4T_ATTR(4, 8, 1, 8) DLS_G4T_ATTR(1, 32, 4, 4) DLS_G4T_ATTR(1, 32, 4, 8)
+  DLS_G4T_ATTR(4, 16, 4, 4) DLS_G4T_ATTR(4, 16, 4, 8)
+#undef DLS_G4T_ATTR
 #define DLS_VEC_ATTR(O, UU) \
   DLS_CUDA(cudaFuncSetAttribute(ew_vec_kernel<O, UU>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   DLS_VEC_ATTR(0, 1) DLS_VEC_ATTR(0, 2) DLS_VEC_ATTR(0, 4)
@@ -947,38 +1040,79 @@ int launch_plan(dls_ctx *ctx, int stream, CachedPlan &cp, dls_buf *const *params
     }
     if (vd) {
       static thread_local G4TArgs T;
-      const int TI = W >= 48 ? 64 : 32;
+      // the two innermost launch dims fold into one when every leaf walks them as one (stride of dim 1 = extent x stride of
+      // dim 0, no bounds check on either): NHWC -> NCHW is then a batched [HW, C] transpose with 1024-long output rows
+      int rr = r;
+      long long shape_in[kMaxRank];                    // launch extents, innermost first
+      for (int d = 0; d < kMaxRank; ++d) shape_in[d] = d < r ? P.out_shape[r - 1 - d] : 1;
+      while (rr >= 3 && vd >= 2) {
+        bool fold = true;
+        for (int l = 0; l < (int)P.g4leaves.size() && fold; ++l) {
+          const G4Leaf &L = A.leaves[l];
+          fold = (long long)L.ls[1] == (long long)L.ls[0] * shape_in[0];
+          for (int c = 0; c < L.n_checks; ++c) fold = fold && L.chk[c].col > 1;
+        }
+        if (!fold || shape_in[0] * shape_in[1] >= (1ll << 30)) break;
+        shape_in[0] *= shape_in[1];
+        for (int d = 1; d + 1 < kMaxRank; ++d) shape_in[d] = shape_in[d + 1];
+        shape_in[kMaxRank - 1] = 1;
+        for (int l = 0; l < (int)P.g4leaves.size(); ++l) {
+          G4Leaf &L = A.leaves[l];
+          for (int d = 1; d + 1 < kMaxRank; ++d) L.ls[d] = L.ls[d + 1];
+          L.ls[kMaxRank - 1] = 0;
+          for (int c = 0; c < L.n_checks; ++c) L.chk[c].col -= 1;
+        }
+        --rr;
+        --vd;
+      }
+      const long long W = shape_in[0];                 // shadows the row path's inner extent from here on
+      const int r = rr;
+      for (int d = 0; d < kMaxRank; ++d) A.dims[d] = mk_div(d >= 1 && d < r ? shape_in[d] : 1);
       T.vd = vd;
       T.dim0 = (uint32_t)W;
-      T.dimv = (uint32_t)P.out_shape[r - 1 - vd];
-      const long long ti = (W + TI - 1) / TI, tj = (T.dimv + 31) / 32;
+      T.dimv = (uint32_t)shape_in[vd];
+      // 4 elements per lane along vd (128-bit loads) when that dim allows it: 32 x 128, 64 x 64 / 32 x 64 or 32 x 32 tiles
+      // by its extent; else one element per lane and a 32 x 32 tile
+      const bool v4 = T.dimv % 4 == 0;
+      const int LJ = !v4 ? 32 : T.dimv >= 128 ? 32 : T.dimv >= 64 ? 16 : 8;
+      const int Vt = v4 ? 4 : 1, Ut = !v4 ? 4 : LJ == 32 ? 4 : LJ == 16 ? (W >= 64 ? 4 : 2) : 1;
+      const int TI = 8 * (32 / LJ) * Ut, TJ = LJ * Vt;
+      const long long ti = (W + TI - 1) / TI, tj = (T.dimv + TJ - 1) / TJ;
       T.tiles_i = mk_div(ti);
       T.tiles_j = mk_div(tj);
       long long others = 1, os = 1;
       for (int d = 0; d < kMaxRank; ++d) {
         T.ostride[d] = d < r ? (uint32_t)os : 0u;
         if (d < r) {
-          if (d != 0 && d != vd) others *= P.out_shape[r - 1 - d];
-          os *= P.out_shape[r - 1 - d];
+          if (d != 0 && d != vd) others *= shape_in[d];
+          os *= shape_in[d];
         }
       }
       T.n_tiles = (uint32_t)(ti * tj * others);
-      const int Ut = TI / 8;
-      const size_t smem = (size_t)P.n_slots * Ut * kBlock * sizeof(float) + (size_t)TI * 33 * sizeof(float);
+      const size_t smem = (size_t)P.n_slots * Ut * Vt * kBlock * sizeof(float) + (size_t)TI * (TJ + (Vt == 4 ? 4 : 1)) * sizeof(float);
       if (smem <= (size_t)kG4SmemLimit && ti * tj * others < (1ll << 31)) {
         int per_sm = 0;
-        if (Ut == 8) DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4t_kernel<8, 8>, kBlock, smem));
-        else DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4t_kernel<4, 8>, kBlock, smem));
-        if (per_sm < 1) per_sm = 1;
-        const int grid = (int)std::max<long long>(1, std::min<long long>(T.n_tiles, (long long)ctx->sm_count * per_sm));
-        if (Ut == 8 && r <= 4) ew_gather4t_kernel<8, 4><<<grid, kBlock, smem, st>>>(A, T);
-        else if (Ut == 8) ew_gather4t_kernel<8, 8><<<grid, kBlock, smem, st>>>(A, T);
-        else if (r <= 4) ew_gather4t_kernel<4, 4><<<grid, kBlock, smem, st>>>(A, T);
-        else ew_gather4t_kernel<4, 8><<<grid, kBlock, smem, st>>>(A, T);
+#define DLS_G4T_DO(VV, LL, UU)                                                                                                   \
+  do {                                                                                                                           \
+    DLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ew_gather4t_kernel<VV, LL, UU, 8>, kBlock, smem));           \
+    if (per_sm < 1) per_sm = 1;                                                                                                  \
+    const int grid = (int)std::max<long long>(1, std::min<long long>(T.n_tiles, (long long)ctx->sm_count * per_sm));             \
+    if (r <= 4) ew_gather4t_kernel<VV, LL, UU, 4><<<grid, kBlock, smem, st>>>(A, T);                                              \
+    else ew_gather4t_kernel<VV, LL, UU, 8><<<grid, kBlock, smem, st>>>(A, T);                                                     \
+  } while (0)
+        if (!v4) DLS_G4T_DO(1, 32, 4);
+        else if (LJ == 32) DLS_G4T_DO(4, 32, 4);
+        else if (LJ == 16 && Ut == 4) DLS_G4T_DO(4, 16, 4);
+        else if (LJ == 16) DLS_G4T_DO(4, 16, 2);
+        else DLS_G4T_DO(4, 8, 1);
+#undef DLS_G4T_DO
         DLS_CUDA(cudaGetLastError());
         ctx->stats.kernel_launches++;
         return DLS_OK;
       }
+      // not launched after all: undo the dim folding before the row path reads the arguments
+      memcpy(A.leaves, P.g4leaves.data(), P.g4leaves.size() * sizeof(G4Leaf));
+      for (int d = 0; d < kMaxRank; ++d) A.dims[d] = mk_div(d >= 1 && d < P.out_rank ? P.out_shape[P.out_rank - 1 - d] : 1);
     }
     static const int forced_g4_unroll = [] {
       const char *e = getenv("DLS_G4_UNROLL");

@@ -197,8 +197,10 @@ def test_tiled_path_under_elementwise_ops_and_padding(backends):
         ta = M.tensor(a, padding=-3.5).translate([3, -2]).transpose()
         tb = M.tensor(b).transpose()
         u = ta * tb + M.scalar(0.25)
-        return M.tanh(u) * u - tb
+        return u * u - tb * u                          # `u` is a saved sub-expression (three uses)
     want, got, _ = both(backends, build)
+    assert_bits(want, got)
+    want, got, _ = both(backends, lambda M: M.tanh(M.tensor(a, padding=-3.5).translate([3, -2]).transpose() * M.tensor(b).transpose()))
     assert_ulp(want, got, ULP_TRANSCENDENTAL)
     want, got, _ = both(backends, lambda M: M.tensor(a, padding=-3.5).translate([3, -2]).transpose() + M.tensor(b).transpose())
     assert_bits(want, got)
