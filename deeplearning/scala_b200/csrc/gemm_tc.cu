@@ -519,6 +519,278 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   }
 }
 
+// ---- CTA-pair variant (cta_group::2) for the large plain GEMMs ---------------------------------------------------------
+// A cluster of two CTAs (two SMs of one TPC) owns a 256 x 256 output tile.  CTA r of the pair loads ITS 128 rows of the A
+// tile and ITS 128 rows (of N) of the B tile -- 32 KB per k block instead of the 48 KB a lone CTA needs for half the
+// flops, which is what the single-CTA kernel runs out of (tensor pipe 75 % active at ~96 B/clk/SM from L2) -- and one thread
+// of the leader CTA issues tcgen05.mma.cta_group::2 (M = 256, N = 256), which reads both CTAs' shared memory and writes
+// each CTA's 128 accumulator rows into that CTA's TMEM.  Protocol:
+//   full[s]   lives in the leader: its producer arrives with expect_tx = the pair's 64 KB; both CTAs' TMA loads signal it
+//             (cp.async.bulk.tensor ... .cta_group::2 with the barrier address of CTA 0);
+//   empty[s]  in both CTAs, arrived by the leader's tcgen05.commit multicast, so each producer knows its slot is free;
+//   tfull[a]  in both CTAs (commit multicast): each CTA's four epilogue warps drain their own 128 TMEM lanes;
+//   tempty[a] in the leader, 8 arrivals: the epilogue warps of BOTH CTAs (remote mbarrier.arrive through mapa).
+constexpr int STAGES2 = 6;
+constexpr int STAGE2_BYTES = 2 * BM * 128;                   // A 128 x 128 B + B 128 x 128 B per CTA and k block
+constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+constexpr int BN2 = 256;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// the same barrier / smem offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, uint32_t leader_bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(leader_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate,
+                                          bool tf32) {
+  if (tf32) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+
+template <bool TF32, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+    gemm2_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
+                    const float *__restrict__ bias, int bias_mode, int act, int direct_store, const float *__restrict__ gate,
+                    int gate_mode, void *__restrict__ copy, long long copy_ld) {
+  constexpr int ELEM = TF32 ? 4 : 2;
+  constexpr int BLOCK_K = 128 / ELEM;
+  constexpr int UMMA_K = 32 / ELEM;
+  constexpr int MN_ATOM = 128 / ELEM;
+  static_assert(!(TF32 && (A_MN || B_MN)), "TF32 operands are K-major only");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t *epi_smem = smem + STAGES2 * STAGE2_BYTES;
+  uint64_t *bars = (uint64_t *)(epi_smem + EPI_BYTES);
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES2 + s); };
+  auto tfull_bar = [&](int s) { return bar0 + 8u * (2 * STAGES2 + s); };
+  auto tempty_bar = [&](int s) { return bar0 + 8u * (2 * STAGES2 + 2 + s); };
+  uint32_t *tmem_slot = (uint32_t *)(bars + 2 * STAGES2 + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();          // 0 = leader
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int tiles_m = (M + 2 * BM - 1) / (2 * BM), tiles_n = (N + BN2 - 1) / BN2;
+  const int n_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + BLOCK_K - 1) / BLOCK_K;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES2; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 2 * EPI_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();                                // both CTAs' barriers are initialised before anything signals them
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  // tile t of the pair: 256 rows x 256 columns; this CTA's rows start at m0 + 128 * rank, its B rows at n0 + 128 * rank
+  auto pair_tile = [&](int t, int &m0, int &n0) {
+    constexpr int GROUP = 4;                         // 4 pair-rows (1024 rows) share their B tiles through L2
+    const int per_group = GROUP * tiles_n;
+    const int g = t / per_group;
+    const int first_m = g * GROUP;
+    const int gsz = min(GROUP, tiles_m - first_m);
+    const int r = t - g * per_group;
+    m0 = (first_m + r % gsz) * 2 * BM;
+    n0 = (r / gsz) * BN2;
+  };
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs) =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < n_tiles; t += n_pairs) {
+        int m0, n0;
+        pair_tile(t, m0, n0);
+        const int my_m = m0 + BM * (int)rank, my_n = n0 + (BN2 / 2) * (int)rank;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t a_dst = smem_u32(smem + stage * STAGE2_BYTES);
+          const uint32_t b_dst = a_dst + BM * 128;
+          const uint32_t lbar = map_to_cta(full_bar(stage), 0);
+          const int k0 = kb * BLOCK_K;
+          if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / MN_ATOM; ++j) tma_load_2d_pair(a_dst + j * BLOCK_K * 128, &map_a, lbar, my_m + j * MN_ATOM, k0);
+          } else {
+            tma_load_2d_pair(a_dst, &map_a, lbar, k0, my_m);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < (BN2 / 2) / MN_ATOM; ++j)
+              tma_load_2d_pair(b_dst + j * BLOCK_K * 128, &map_b, lbar, my_n + j * MN_ATOM, k0);
+          } else {
+            tma_load_2d_pair(b_dst, &map_b, lbar, k0, my_n);
+          }
+          if (++stage == STAGES2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA only) =====
+    if (lane == 0 && rank == 0) {
+      const uint32_t fmt = TF32 ? 2u : 1u;
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                             ((uint32_t)(BN2 >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+      const uint32_t a_lbo = A_MN ? BLOCK_K * 128 : 0, b_lbo = B_MN ? BLOCK_K * 128 : 0;
+      const uint32_t a_kstep = A_MN ? UMMA_K * 128 : 32, b_kstep = B_MN ? UMMA_K * 128 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = pair; t < n_tiles; t += n_pairs, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t d_tmem = tmem_base + as * BN2;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_addr = smem_u32(smem + stage * STAGE2_BYTES);
+          const uint32_t b_addr = a_addr + BM * 128;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
+            umma_pair(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u, TF32);
+          }
+          umma_commit_pair(empty_bar(stage));        // frees the slot in BOTH CTAs once these MMAs have read it
+          if (++stage == STAGES2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit_pair(tfull_bar(as));             // accumulator complete -> the epilogue warps of both CTAs
+      }
+    }
+  } else {
+    // ===== epilogue warps (both CTAs): this CTA's 128 rows of the pair tile =====
+    const int quarter = warp & 3;
+    uint8_t *my_smem = epi_smem + (warp - 2) * 2 * EPI_BUF_BYTES;
+    const uint32_t leader_tempty0 = map_to_cta(tempty_bar(0), 0);
+    int it = 0;
+    int buf = 0;
+    for (int t = pair; t < n_tiles; t += n_pairs, ++it) {
+      int m0, n0;
+      pair_tile(t, m0, n0);
+      m0 += BM * (int)rank;
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(tfull_bar(as), aphase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row = m0 + quarter * 32 + lane;
+      float row_bias = 0.f;
+      if (bias_mode == 1 && row < M) row_bias = __ldg(bias + row);
+#pragma unroll 1
+      for (int c = 0; c < BN2 / EPI_CHUNK; ++c) {
+        const int col0 = n0 + c * EPI_CHUNK;
+        if (col0 >= N) break;
+        uint32_t v[32];
+        tmem_ld_32x32(v, tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * BN2 + c * EPI_CHUNK));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        float f[32];
+        epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
+        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0);
+        if (copy && row < M) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(copy) + (long long)row * copy_ld + col0, copy_ld - col0);
+        if (direct_store) {
+          if (row < M) {
+            float *dst = C + (long long)row * ldc + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < N) dst[j] = f[j];
+          }
+        } else {
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          uint8_t *sb = my_smem + buf * EPI_BUF_BYTES + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 q = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+            *reinterpret_cast<float4 *>(sb + ((j ^ (lane & 7)) << 4)) = q;
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0 && m0 + quarter * 32 < M) {
+            tma_store_2d(&map_c, smem_u32(my_smem + buf * EPI_BUF_BYTES), col0, m0 + quarter * 32);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          buf ^= 1;
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(leader_tempty0 + 8u * as);
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();                                // neither CTA leaves while the other may still read its smem / signal it
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
 // ---- fp32 -> bf16 operand staging ------------------------------------------------------------------------------------
 // [rows, cols] fp32 (dense) -> [rows, pitch] bf16 with pitch a multiple of 8 elements so every row starts 16-byte
 // aligned (a TMA requirement).  Round to nearest even.
@@ -718,6 +990,25 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
   return DLS_OK;
 }
 
+template <bool TF32, bool A_MN, bool B_MN>
+static int launch_variant2(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, const CUtensorMap &mb, const CUtensorMap &mc, float *C,
+                           int M, int N, int K, long long ldc, const GemmEpilogue &epi, int direct) {
+  auto kern = gemm2_tc_kernel<TF32, A_MN, B_MN>;
+  static std::atomic<bool> configured[64];
+  const int dev = ctx->device & 63;
+  if (!configured[dev].load(std::memory_order_acquire)) {
+    DLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
+    configured[dev].store(true, std::memory_order_release);
+  }
+  const int tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN2 - 1) / BN2);
+  const int pairs = std::max(1, std::min(tiles, usable_sms(ctx) / 2));
+  kern<<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, epi.gate,
+                                                    epi.gate_mode, epi.copy, epi.copy_ld);
+  DLS_CUDA(cudaGetLastError());
+  ctx->stats.kernel_launches++;
+  return DLS_OK;
+}
+
 }  // namespace tc
 
 int launch_to_bf16(dls_ctx *ctx, int stream, const float *in, void *out, long long rows, long long cols, long long pitch) {
@@ -781,8 +1072,16 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   rc = a_mn ? make_map(&ma, dt, elem, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, mn_atom, block_k)
             : make_map(&ma, dt, elem, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, block_k, BM);
   if (rc) return rc;
+  // CTA-pair kernel (cta_group::2, 256 x 256 tiles) for contractions that fill the machine at least twice with such tiles;
+  // DLS_GEMM_2CTA=0 keeps everything on the single-CTA kernel
+  static const bool pair_off = [] {
+    const char *e = getenv("DLS_GEMM_2CTA");
+    return e && atoi(e) == 0;
+  }();
+  const long long tiles2 = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + BN2 - 1) / BN2);
+  const bool pair_mode = !pair_off && tiles2 >= ctx->sm_count && K >= 4 * block_k;
   rc = b_mn ? make_map(&mb, dt, elem, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, mn_atom, block_k)
-            : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, BN);
+            : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, pair_mode ? BN2 / 2 : BN);
   if (rc) return rc;
   // split-K: a contraction with few output tiles and a long K (the weight gradients of a convolution: M x N = Cin*9 x Cout,
   // K = batch * H * W) would leave most SMs idle; cut K into `splits` ranges, one work item each, then reduce the partials.
@@ -818,7 +1117,13 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   } else {
     mc = ma;   // unused by the kernel in direct-store mode
   }
-  if (!rc) {
+  if (!rc && pair_mode && sp.splits == 1) {
+    if (tf32) rc = launch_variant2<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else if (!a_mn && !b_mn) rc = launch_variant2<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else if (!a_mn && b_mn) rc = launch_variant2<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else if (a_mn && !b_mn) rc = launch_variant2<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else rc = launch_variant2<false, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+  } else if (!rc) {
     if (tf32) rc = launch_variant<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
     else if (!a_mn && !b_mn) rc = launch_variant<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
     else if (!a_mn && b_mn) rc = launch_variant<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
