@@ -187,3 +187,56 @@ def test_emitted_operand_copy_is_the_staged_copy(backends, shape):
     for x, y in zip(outs[0], outs[1]):
         assert (x.view(np.uint32) == y.view(np.uint32)).all()
     assert launches[1] == launches[0] - 1, launches
+
+
+PAIR = [
+    # m, n, k, ta, tb: enough 256 x 256 tiles (>= 148) for the CTA-pair kernel, ragged so that the last pair-row has a peer CTA
+    # whose rows lie entirely outside the matrix, the last tile column is partial, and K has a partial block
+    (2100, 4700, 200, False, True),
+    (2100, 4700, 200, True, False),
+    (4600, 2200, 136, False, False),
+    (3968, 3840, 320, True, True),       # M = 31 x 128: the peer half of the last pair tile is empty
+]
+
+
+@pytest.mark.parametrize("mode", ["bf16", "tf32"])
+@pytest.mark.parametrize("shape", PAIR, ids=["%dx%dx%d-%s%s" % (s[0], s[1], s[2], "T" if s[3] else "N", "T" if s[4] else "N") for s in PAIR])
+def test_cta_pair_kernel_on_ragged_shapes(backends, mode, shape):
+    """gemm2_tc_kernel (cta_group::2): sampled rows of every 128-row slab against the operand-rounded float64 product, with the
+    row bias + tanh epilogue; and the single-CTA kernel must agree with it element for element up to accumulation order."""
+    O, B = backends
+    m, n, k, ta, tb = shape
+    a, b = operands(m, n, k, ta, tb, seed=m + n)
+    rng = np.random.RandomState(5)
+    bias = rng.standard_normal(m).astype(np.float32)
+    got = B.matmul(B.tensor(a), B.tensor(b), transpose_a=ta, transpose_b=tb, mode=mode, bias=B.tensor(bias), bias_mode="row",
+                   activation="tanh").flat_array().reshape(m, n)
+    rows = np.array(sorted({min(m - 1, t * 128 + rng.randint(0, 128)) for t in range((m + 127) // 128)} | {0, m - 1}))
+    ar = O.round_operand(a, mode).astype(np.float64)
+    br = O.round_operand(b, mode).astype(np.float64)
+    A = (ar.T if ta else ar)[rows]
+    Bm = br.T if tb else br
+    pre = A @ Bm + bias[rows, None]
+    scale = np.abs(A) @ np.abs(Bm) + np.abs(bias[rows, None]) + 1.0
+    err = np.abs(np.arctanh(np.clip(got[rows].astype(np.float64), -1 + 1e-7, 1 - 1e-7)) - pre)
+    ok = np.abs(pre) < 3.0                                  # away from the saturated region, where arctanh amplifies one ulp
+    assert (err[ok] / scale[ok]).max() <= 4e-6
+    assert np.isfinite(got).all() and np.abs(got).max() <= 1.0
+
+
+def test_cta_pair_kernel_gate_and_operand_copy(backends):
+    """The pair kernel's epilogue carries the same gate and bf16 operand copy as the single-CTA kernel: bit-identical to
+    product-then-tree, and a consumer of the result gives the same bits with and without the emitted copy."""
+    O, B = backends
+    m, n, k = 2304, 4352, 192
+    a, b = operands(m, n, k, False, False, seed=9)
+    g = np.tanh(np.random.RandomState(8).standard_normal((m, n)).astype(np.float32))
+    at, bt, gt = B.tensor(a).do_cache(), B.tensor(b).do_cache(), B.tensor(g).do_cache()
+    got = B.matmul(at, bt, mode="bf16", gate=gt, gate_mode="tanh", emit_operand_copy=True).do_cache()
+    plain = B.matmul(at, bt, mode="bf16").do_cache()
+    want = (plain * (1.0 - gt * gt)).flat_array()
+    assert (got.flat_array().view(np.uint32) == want.view(np.uint32)).all()
+    w = B.tensor(np.random.RandomState(10).standard_normal((n, 64)).astype(np.float32)).do_cache()
+    r1 = B.matmul(got, w, mode="bf16").flat_array()
+    r2 = B.matmul(B.tensor(want.reshape(m, n)), w, mode="bf16").flat_array()
+    assert (r1.view(np.uint32) == r2.view(np.uint32)).all()
