@@ -100,6 +100,7 @@ _SIG = {
                                 C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),
     "dls_matmul_gated": (C.c_int, [_P, _P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int,
                                    C.POINTER(GemmOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_matmul_sgd": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_int]),
     "dls_conv3x3_supported": (C.c_int, [_P, C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]),
     "dls_conv3x3_forward": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                       C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),

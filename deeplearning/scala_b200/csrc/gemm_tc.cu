@@ -222,13 +222,13 @@ __device__ __forceinline__ void epi_apply(const uint32_t (&v)[32], float (&f)[32
 
 // x *= act'(g) for the 32 columns of a chunk (`left` = columns that exist from col0 on): the delta of the layer below in the
 // same kernel.  One rounding per node of `delta * (1 - y * y)` / `delta * min(y * FLT_MAX, 1)`, like the elementwise kernels.
-__device__ __forceinline__ void epi_gate(float (&f)[32], const float *__restrict__ g, int left, int mode, bool vec) {
+__device__ __forceinline__ void epi_gate(float (&f)[32], const float *g, int left, int mode, bool vec, float scale) {
   float h[32];
   if (vec) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (4 * j < left) q = __ldg(reinterpret_cast<const float4 *>(g) + j);
+      if (4 * j < left) q = *(reinterpret_cast<const float4 *>(g) + j);   // plain loads: in mode 3 the gate is the output buffer
       h[4 * j] = q.x;
       h[4 * j + 1] = q.y;
       h[4 * j + 2] = q.z;
@@ -236,11 +236,14 @@ __device__ __forceinline__ void epi_gate(float (&f)[32], const float *__restrict
     }
   } else {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) h[j] = j < left ? __ldg(g + j) : 0.f;
+    for (int j = 0; j < 32; ++j) h[j] = j < left ? g[j] : 0.f;
   }
   if (mode == 1) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = __fmul_rn(f[j], __fsub_rn(1.0f, __fmul_rn(h[j], h[j])));
+  } else if (mode == 3) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = __fsub_rn(h[j], __fmul_rn(f[j], scale));
   } else {
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = __fmul_rn(f[j], fminf(__fmul_rn(h[j], 3.4028234663852886e38f), 1.0f));
@@ -276,10 +279,10 @@ __device__ __forceinline__ void epi_copy_bf16(const float (&f)[32], __nv_bfloat1
 template <bool TF32, bool A_MN, bool B_MN, int CONV>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
     gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                   const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
+                   const __grid_constant__ CUtensorMap map_c, float *C, int M, int N, int K, long long ldc,
                    const float *__restrict__ bias, int bias_mode, int act, int direct_store, int splits, int kb_per_split,
-                   int c_rows, const ConvGeom cg, const float *__restrict__ gate, int gate_mode, void *__restrict__ copy,
-                   long long copy_ld) {
+                   int c_rows, const ConvGeom cg, const float *gate, int gate_mode, void *__restrict__ copy, long long copy_ld,
+                   float gate_scale) {
   // splits > 1 (split-K): work item w = split * n_tiles + tile covers k blocks [split * kb_per_split, ...) and writes its
   // partial tile at row offset split * tiles_m * BM of a [splits * tiles_m * BM, N] scratch matrix (c_rows = its row count);
   // the epilogue (bias / activation) then runs in splitk_reduce_kernel.
@@ -473,7 +476,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float f[32];
         epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
-        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0);
+        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0, gate_scale);
         if (copy && row < M) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(copy) + (long long)row * copy_ld + col0, copy_ld - col0);
         if (direct_store) {
           if (row < c_rows) {
@@ -584,9 +587,9 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
 template <bool TF32, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
     gemm2_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                    const __grid_constant__ CUtensorMap map_c, float *__restrict__ C, int M, int N, int K, long long ldc,
-                    const float *__restrict__ bias, int bias_mode, int act, int direct_store, const float *__restrict__ gate,
-                    int gate_mode, void *__restrict__ copy, long long copy_ld) {
+                    const __grid_constant__ CUtensorMap map_c, float *C, int M, int N, int K, long long ldc,
+                    const float *__restrict__ bias, int bias_mode, int act, int direct_store, const float *gate, int gate_mode,
+                    void *__restrict__ copy, long long copy_ld, float gate_scale) {
   constexpr int ELEM = TF32 ? 4 : 2;
   constexpr int BLOCK_K = 128 / ELEM;
   constexpr int UMMA_K = 32 / ELEM;
@@ -748,7 +751,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float f[32];
         epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
-        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0);
+        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0, gate_scale);
         if (copy && row < M) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(copy) + (long long)row * copy_ld + col0, copy_ld - col0);
         if (direct_store) {
           if (row < M) {
@@ -933,10 +936,10 @@ static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *bas
 
 // out[i] = act(sum_s partial[s * stride + i] + bias) (* act'(gate[i])), i < m * n: the second half of a split-K contraction;
 // optionally also the bf16 operand copy of the result.
-__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restrict__ partial, float *__restrict__ out, size_t m,
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restrict__ partial, float *out, size_t m,
                                                             size_t n, size_t stride, int splits, const float *__restrict__ bias,
-                                                            int bias_mode, int act, const float *__restrict__ gate, int gate_mode,
-                                                            __nv_bfloat16 *__restrict__ copy, long long copy_ld) {
+                                                            int bias_mode, int act, const float *gate, int gate_mode,
+                                                            __nv_bfloat16 *__restrict__ copy, long long copy_ld, float gate_scale) {
   const size_t total = m * n;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float x = __ldg(partial + i);
@@ -946,10 +949,12 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float *__restr
     if (act == 1) x = tanhf(x);
     else if (act == 2) x = fmaxf(x, 0.f);
     if (gate_mode == 1) {
-      const float h = __ldg(gate + i);
+      const float h = gate[i];
       x = __fmul_rn(x, __fsub_rn(1.0f, __fmul_rn(h, h)));
     } else if (gate_mode == 2) {
-      x = __fmul_rn(x, fminf(__fmul_rn(__ldg(gate + i), 3.4028234663852886e38f), 1.0f));
+      x = __fmul_rn(x, fminf(__fmul_rn(gate[i], 3.4028234663852886e38f), 1.0f));
+    } else if (gate_mode == 3) {
+      x = __fsub_rn(gate[i], __fmul_rn(x, gate_scale));   // plain load: the gate is the output buffer
     }
     out[i] = x;
     if (copy) copy[(i / n) * copy_ld + i % n] = __float2bfloat16_rn(x);
@@ -984,7 +989,8 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
   const int sms = usable_sms(ctx);
   const int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, sp.splits,
-                                              sp.kb_per_split, sp.c_rows, cg, epi.gate, epi.gate_mode, epi.copy, epi.copy_ld);
+                                              sp.kb_per_split, sp.c_rows, cg, epi.gate, epi.gate_mode, epi.copy, epi.copy_ld,
+                                              epi.gate_scale);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;
@@ -1003,7 +1009,7 @@ static int launch_variant2(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma,
   const int tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN2 - 1) / BN2);
   const int pairs = std::max(1, std::min(tiles, usable_sms(ctx) / 2));
   kern<<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ma, mb, mc, C, M, N, K, ldc, epi.bias, epi.bias_mode, epi.act, direct, epi.gate,
-                                                    epi.gate_mode, epi.copy, epi.copy_ld);
+                                                    epi.gate_mode, epi.copy, epi.copy_ld, epi.gate_scale);
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
   return DLS_OK;
@@ -1138,7 +1144,7 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
       const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->sm_count * 8);
       tc::splitk_reduce_kernel<<<grid, 256, 0, st>>>(dst, C, (size_t)M, (size_t)N, (size_t)m_pad * ld_dst, sp.splits, epi.bias,
                                                      epi.bias_mode, epi.act, epi.gate, epi.gate_mode, (__nv_bfloat16 *)epi.copy,
-                                                     epi.copy_ld);
+                                                     epi.copy_ld, epi.gate_scale);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) rc = cuda_fail(e, "splitk_reduce_kernel", __FILE__, __LINE__);
       ctx->stats.kernel_launches++;

@@ -11,8 +11,11 @@ struct GemmEpilogue {
   // gate: the result is multiplied by the activation derivative evaluated on `gate` ([M, N] fp32, same layout as the output):
   //   1: x * (1 - g * g)  (`delta * (1 - y * y)`, tanh)      2: x * min(g * FLT_MAX, 1)  (`delta * 1[y > 0]`, relu)
   // i.e. the elementwise tree a layer's backward would otherwise launch on the materialised product, node for node.
+  //   3: g - x * gate_scale  (`data - delta * learningRate`, TW:63-72: the contraction IS a weight gradient and the epilogue
+  //      applies it; gate = the weight, which is also the output buffer -- every element is read and written by one thread)
   const float *gate = nullptr;
   int gate_mode = 0;
+  float gate_scale = 0.f;
   // copy: a second copy of the result rounded to the contraction mode's operand type ([M][copy_ld] bf16), so the contraction
   // that consumes the result next does not need a staging pass (it becomes the output buffer's operand shadow)
   void *copy = nullptr;
@@ -79,8 +82,8 @@ int launch_transpose_f32(dls_ctx *ctx, int stream, const float *in, float *out, 
 // matmul.cu
 int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k,
                bool transpose_a, bool transpose_b, int bias_mode, int activation, dls_buf *c, dls_buf *gate = nullptr,
-               int gate_mode = 0, Block *operand_copy = nullptr);
-int launch_gate(dls_ctx *ctx, int stream, float *c, size_t total, const float *gate, int mode);
+               int gate_mode = 0, Block *operand_copy = nullptr, float gate_scale = 0.f);
+int launch_gate(dls_ctx *ctx, int stream, float *c, size_t total, const float *gate, int mode, float scale = 0.f);
 int launch_sgemm(dls_ctx *ctx, int stream, const float *A, const float *B, float *C, int M, int N, int K, bool ta, bool tb);
 
 }  // namespace dls

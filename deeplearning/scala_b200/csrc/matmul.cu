@@ -115,7 +115,8 @@ __global__ void __launch_bounds__(256) gate_kernel(float *__restrict__ c, size_t
   }
 }
 
-int launch_gate(dls_ctx *ctx, int stream, float *c, size_t total, const float *gate, int mode) {
+int launch_gate(dls_ctx *ctx, int stream, float *c, size_t total, const float *gate, int mode, float) {
+  DLS_CHECK(mode != 3, DLS_ERR_UNSUPPORTED, "the in-place update epilogue exists in the tensor-core modes only");
   if (total == 0 || mode == 0) return DLS_OK;
   const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->sm_count * 8);
   gate_kernel<<<grid, 256, 0, ctx->streams[stream]>>>(c, total, gate, mode);
@@ -189,20 +190,20 @@ namespace dls {
 // target of trees that the lowering recognised as one dense contraction (Plan::contraction).
 int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m, size_t n, size_t k,
                bool transpose_a, bool transpose_b, int bias_mode, int activation, dls_buf *c, dls_buf *gate, int gate_mode,
-               Block *operand_copy) {
+               Block *operand_copy, float gate_scale) {
   if (m * n == 0) return DLS_OK;
   const float *bias_ptr = bias_mode ? bias->ptr : nullptr;
   const float *gate_ptr = gate_mode ? gate->ptr : nullptr;
   if (k == 0) {
     DLS_CUDA(cudaMemsetAsync(c->ptr, 0, m * n * sizeof(float), ctx->streams[stream]));
     int rc = launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
-    if (!rc) rc = launch_gate(ctx, stream, c->ptr, m * n, gate_ptr, gate_mode);
+    if (!rc) rc = launch_gate(ctx, stream, c->ptr, m * n, gate_ptr, gate_mode, gate_scale);
     return rc;
   }
   if (mode == DLS_GEMM_FP32) {
     int rc = launch_sgemm(ctx, stream, a->ptr, b->ptr, c->ptr, (int)m, (int)n, (int)k, transpose_a, transpose_b);
     if (!rc) rc = launch_bias_act(ctx, stream, c->ptr, m, n, bias_ptr, bias_mode, activation);
-    if (!rc) rc = launch_gate(ctx, stream, c->ptr, m * n, gate_ptr, gate_mode);
+    if (!rc) rc = launch_gate(ctx, stream, c->ptr, m * n, gate_ptr, gate_mode, gate_scale);
     return rc;
   }
   const void *pa, *pb;
@@ -221,6 +222,7 @@ int run_matmul(dls_ctx *ctx, int stream, int mode, dls_buf *a, dls_buf *b, dls_b
   epi.act = activation;
   epi.gate = gate_ptr;
   epi.gate_mode = gate_mode;
+  epi.gate_scale = gate_scale;
   if (!rc && operand_copy && mode == DLS_GEMM_BF16) {
     // the result's own bf16 operand copy, written by the epilogue: [m][n rounded up to 8] like stage_operand's
     epi.copy_ld = ((long long)n + 7) & ~7LL;
@@ -263,7 +265,7 @@ extern "C" int dls_matmul_gated(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *b
   if (rc) return rc;
   Block copy;
   rc = run_matmul(ctx, stream, mode, a, b, bias, m, n, k, transpose_a != 0, transpose_b != 0, o.bias_mode, o.activation, c, gate,
-                  gate_mode, (o.flags & DLS_GEMM_EMIT_OPERAND_COPY) ? &copy : nullptr);
+                  gate_mode, (o.flags & DLS_GEMM_EMIT_OPERAND_COPY) ? &copy : nullptr, 0.f);
   if (!rc) rc = finish_output(ctx, stream, &c, 1, ins, 4, done);
   if (rc) {
     if (copy.ptr) free_block(ctx, copy);
@@ -277,6 +279,39 @@ extern "C" int dls_matmul_gated(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *b
     c->shadow_cols[0] = (long long)n;
   }
   *out = c;
+  return DLS_OK;
+}
+
+extern "C" int dls_matmul_sgd(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *weight, size_t m, size_t n, size_t k, int transpose_a,
+                              int transpose_b, float learning_rate, int mode) {
+  DLS_CHECK(ctx && a && b && weight, DLS_ERR_INVALID, "dls_matmul_sgd: NULL argument");
+  DLS_CHECK(weight != a && weight != b, DLS_ERR_INVALID, "dls_matmul_sgd: the weight is one of the operands");
+  DLS_CHECK(m * k <= a->n && k * n <= b->n && m * n <= weight->n, DLS_ERR_INVALID, "dls_matmul_sgd: a buffer is shorter than its shape");
+  DLS_CHECK(m < (1u << 31) && n < (1u << 31) && k < (1u << 31) && k > 0 && m * n > 0, DLS_ERR_UNSUPPORTED, "dls_matmul_sgd: bad dimension");
+  if (mode < 0) mode = ctx->opts.gemm_mode;
+  DLS_CHECK(mode == DLS_GEMM_TF32 || mode == DLS_GEMM_BF16, DLS_ERR_UNSUPPORTED,
+            "dls_matmul_sgd: tensor-core modes only (materialise the gradient and use dls_sgd_update otherwise)");
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  DLS_CUDA(cudaSetDevice(ctx->device));
+  const int stream = ctx->n_streams == 1 ? 0 : weight->last_stream;
+  dls_buf *ins[3] = {a, b, weight};
+  int rc = wait_inputs(ctx, stream, ins, 3, nullptr, 0);
+  if (!rc) rc = wait_readers(ctx, stream, weight);   // in place: every launch that still reads the old weight comes first
+  if (rc) return rc;
+  Block copy;
+  rc = run_matmul(ctx, stream, mode, a, b, nullptr, m, n, k, transpose_a != 0, transpose_b != 0, 0, 0, weight, weight, 3, &copy,
+                  learning_rate);
+  if (!rc) rc = finish_output(ctx, stream, &weight, 1, ins, 2, nullptr);
+  if (rc) {
+    if (copy.ptr) free_block(ctx, copy);
+    return rc;
+  }
+  if (copy.ptr) {               // the new weight's operand copy: forward and backward-data of the next step need no staging pass
+    copy.stream_mask |= 1u << stream;
+    weight->shadow[0] = copy;
+    weight->shadow_rows[0] = (long long)m;
+    weight->shadow_cols[0] = (long long)n;
+  }
   return DLS_OK;
 }
 

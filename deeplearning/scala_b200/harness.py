@@ -14,7 +14,7 @@ import numpy as np
 
 from . import tensors as T
 from .layers import Layers
-from .plugins import Plugins
+from .plugins import APPLIED, Plugins
 
 
 class Exchange:
@@ -136,8 +136,25 @@ class ExchangeSgd:
         self.exchange, self.learning_rate = exchange, float(learning_rate)
         self.backend = exchange.backend if exchange is not None else (backend or T.default_backend())
 
+    # single GPU: a layer orders its backward-data pass before its weight gradient, because `gradient` may apply the update
+    # in place right away (layers.linear reads this flag)
+    fuse_contractions = os.environ.get("DLS_FUSED_DW_SGD", "1") != "0"
+
+    @property
+    def applies_in_backward(self) -> bool:
+        return self.exchange is None and self.fuse_contractions
+
     def gradient(self, weight, delta: T.Tensor) -> T.Tensor:
         ex = self.exchange
+        spec = getattr(delta, "_ungated", None)
+        if (self.applies_in_backward and not weight.plugins.cumulative and spec is not None and list(delta.shape) == list(weight.data.shape)
+                and (delta._weak is None or delta._weak() is None) and weight.uses == 1 and isinstance(weight.data, T.CachedTensor)
+                and self.backend.fuses_sgd_into_contractions(spec["mode"])):
+            # the gradient is a still unevaluated contraction and this weight was read once this step: issue the
+            # contraction with `data - delta * learningRate` (TW:63-72) as its epilogue, in place -- the gradient never
+            # exists in HBM, and the new weight's bf16 operand copy comes out of the same kernel
+            self.backend.matmul_sgd(spec, weight.data, self.learning_rate)
+            return APPLIED
         d = delta.broadcast(weight.data.shape)
         if ex is not None and d.size * 4 >= ex.peer_bytes:
             cached = ex.allreduce(d)
@@ -159,6 +176,8 @@ class ExchangeSgd:
         from . import _native as N
         ex = self.exchange
         n = len(pending)
+        if n == 0:
+            return
         wbufs = [w.data._buffer() for w, _ in pending]
         gbufs = [g._buffer() for _, g in pending]
         weights = (C.c_void_p * n)(*[b.handle for b in wbufs])

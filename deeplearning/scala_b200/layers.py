@@ -322,7 +322,11 @@ class Layers:
                         axis = 1 if bias_mode == "row" else 0
                         tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_of(d), axis)))
                     order = [(ta, delta_a, a), (tb, delta_b, b)]
-                    order.sort(key=lambda e: 0 if isinstance(e[2], TensorWeight) else 1)
+                    # ... unless the optimizer applies an update the moment it receives the gradient (single GPU: the
+                    # weight-gradient contraction writes `w - lr * dw` in place): then the pass that still reads the old
+                    # weight -- this layer's backward-data -- has to be issued first
+                    last = getattr(self.P.optimizer, "applies_in_backward", False)
+                    order.sort(key=lambda e: (1 if last else 0) if isinstance(e[2], TensorWeight) else (0 if last else 1))
                     for tape, delta, _ in order:
                         tape.backward(do_delta.map(delta))
                 return run

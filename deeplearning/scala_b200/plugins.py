@@ -167,11 +167,17 @@ class TensorLayer(Differentiable):
         return self.forward().map(lambda tape: tape.data)
 
 
+# returned by an optimizer hook that has already applied the update (harness.ExchangeSgd: the weight-gradient contraction
+# wrote `data - delta * learningRate` in its epilogue), so there is nothing left to swap or defer
+APPLIED = object()
+
+
 class TensorWeight(Differentiable):
     """TensorWeightApi (TW:27-74) + allocate (TW:139-153)."""
 
     def __init__(self, plugins: "Plugins", data):
         self.plugins, self.data = plugins, data
+        self.uses, self.uses_step = 0, -1
 
     def forward(self) -> Do:
         def acquire():
@@ -181,6 +187,9 @@ class TensorWeight(Differentiable):
             # result of `train` after running it (CumulativeTensorLayersSpec:96-127).
             current = self.data
             data = T.CachedTensor(current.backend, current._buffer(), list(current.shape), current.padding)
+            step = self.plugins.step_id                                      # how many tapes of this step read the weight
+            self.uses = self.uses + 1 if self.uses_step == step else 1
+            self.uses_step = step
 
             def backward(do_delta: Do):
                 try:
@@ -193,6 +202,8 @@ class TensorWeight(Differentiable):
     def backward(self, original_delta: Do):
         """TW:50-74: delta = optimizer.delta; newData = (data - delta).doCache; release the old buffer; swap."""
         delta = original_delta.map(lambda d: self.plugins.optimizer_delta(self, d)).run()
+        if delta is APPLIED:                                                 # the optimizer hook updated the weight itself
+            return
         if self.plugins.deferred_updates is not None:
             # data-parallel training: the optimizer hook has put an all-reduce of this gradient in flight on the exchange
             # stream; applying `data - delta` now would make the compute stream wait for it.  The swap is postponed to
@@ -212,6 +223,7 @@ class Plugins:
     def __init__(self, cumulative: bool = False, optimizer_delta: Optional[Callable] = None, backend=None,
                  defer_updates: bool = False, optimizer=None):
         self.cumulative = cumulative
+        self.step_id = 0
         # a stateful optimizer (optimizers.Momentum / Adam) updates weights in place, which is only safe at the end of
         # the step: it implies deferred updates
         self.optimizer = optimizer
@@ -248,6 +260,7 @@ class Plugins:
         """Once per training step: a stateful optimizer advances its step counter and publishes this step's
         hyper-parameters to the device.  Skipped while a step is being recorded (host writes cannot be captured; the
         replays call it themselves)."""
+        self.step_id += 1
         if self.optimizer is not None and not self.recording:
             self.optimizer.begin_step(self.backend or T.default_backend())
 

@@ -119,6 +119,7 @@ class Backend:
                                gemm_mode={"fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}[gemm_mode],
                                allocator_cap_bytes=allocator_cap_bytes, plan_cache_capacity=0, reserved=0)
         self.fuse_reductions = fuse_reductions
+        self.gemm_mode = gemm_mode
         self._ctx = None
         self._lock = threading.Lock()
 
@@ -327,6 +328,19 @@ class Backend:
             # (layers.linear backward) as long as nobody has produced it yet
             out._ungated = dict(a=a, b=b, transpose_a=transpose_a, transpose_b=transpose_b, mode=mode)
         return out
+
+    def matmul_sgd(self, spec: dict, weight: "CachedTensor", learning_rate: float) -> None:
+        """weight -= learning_rate * (op(a) op(b)) in place, in the contraction's epilogue (`dls_matmul_sgd`); `spec` is the
+        `_ungated` record of the unevaluated product that would have been the gradient."""
+        a, b = spec["a"], spec["b"]
+        ta, tb = spec["transpose_a"], spec["transpose_b"]
+        m, k = (a.shape[1], a.shape[0]) if ta else (a.shape[0], a.shape[1])
+        n = b.shape[0] if tb else b.shape[1]
+        N.check(N.lib.dls_matmul_sgd(self.ctx, a._buffer().handle, b._buffer().handle, weight._buffer().handle, m, n, k, int(ta), int(tb),
+                                     float(learning_rate), self._MODES[spec["mode"]]))
+
+    def fuses_sgd_into_contractions(self, mode: Optional[str] = None) -> bool:
+        return (mode or self.gemm_mode) in ("tf32", "bf16")
 
     # -- 'same' 3x3 convolution without an im2col matrix (csrc/conv.cu; TensorsSpec:144-210 spells it with nine translates) --
     _MODES = {None: -1, "fp32": N.DLS_GEMM_FP32, "tf32": N.DLS_GEMM_TF32, "bf16": N.DLS_GEMM_BF16}

@@ -204,6 +204,14 @@ int dls_matmul_ex(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, size_t m,
 int dls_matmul_gated(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *bias, dls_buf *gate, size_t m, size_t n, size_t k,
                      int transpose_a, int transpose_b, const dls_gemm_opts *opts, dls_event *const *deps, int n_deps,
                      dls_buf **out, dls_event **done);
+/* weight[M,N] -= learning_rate * (op(A) op(B)), in place, in ONE kernel: the contraction is a weight gradient (TL:124-162 sums
+ * over the batch) and its epilogue is the update `data - delta * learningRate` of TW:63-72 (same two roundings), so the
+ * gradient never exists in HBM -- north_star's "gradient accumulation and the optimizer step fused into one pass over each
+ * weight buffer".  BF16 mode also leaves the new weight's bf16 operand copy.  In place, so only valid once every launch that
+ * reads the old weight has been issued (the caller orders a layer's backward-data pass first).  Tensor-core modes only
+ * (mode = -1: the context's gemm_mode); DLS_ERR_UNSUPPORTED otherwise: materialise the gradient and use dls_sgd_update. */
+int dls_matmul_sgd(dls_ctx *ctx, dls_buf *a, dls_buf *b, dls_buf *weight, size_t m, size_t n, size_t k, int transpose_a,
+                   int transpose_b, float learning_rate, int mode);
 
 /* ---- 'same' 3x3 convolution of NHWC tensors with [3,3,Cin,Cout] weights, without an im2col matrix.  The reference spells
  * a convolution as nine `translate`d views, `join` and an unrolled matmul (TensorsSpec:144-210 `convolute`,
