@@ -140,6 +140,16 @@ class ExchangeSgd:
     # in place right away (layers.linear reads this flag)
     fuse_contractions = os.environ.get("DLS_FUSED_DW_SGD", "1") != "0"
 
+    # the epilogue reads the weight tile with per-lane loads; under a long contraction that hides behind the next tile's main
+    # loop (C4: K = 8192), under a short one (C1 / C3: K = batch = 128 / 256) it is exposed and the one-launch multi-tensor
+    # update at full HBM bandwidth is faster (measured: C1 0.059 -> 0.072 ms with the epilogue update)
+    fuse_min_k = int(os.environ.get("DLS_FUSED_DW_SGD_MIN_K", 1024))
+
+    @staticmethod
+    def _contraction_length(spec) -> int:
+        a = spec["a"]
+        return a.shape[0] if spec["transpose_a"] else a.shape[1]
+
     @property
     def applies_in_backward(self) -> bool:
         return self.exchange is None and self.fuse_contractions
@@ -149,7 +159,7 @@ class ExchangeSgd:
         spec = getattr(delta, "_ungated", None)
         if (self.applies_in_backward and not weight.plugins.cumulative and spec is not None and list(delta.shape) == list(weight.data.shape)
                 and (delta._weak is None or delta._weak() is None) and weight.uses == 1 and isinstance(weight.data, T.CachedTensor)
-                and self.backend.fuses_sgd_into_contractions(spec["mode"])):
+                and self.backend.fuses_sgd_into_contractions(spec["mode"]) and self._contraction_length(spec) >= self.fuse_min_k):
             # the gradient is a still unevaluated contraction and this weight was read once this step: issue the
             # contraction with `data - delta * learningRate` (TW:63-72) as its epilogue, in place -- the gradient never
             # exists in HBM, and the new weight's bf16 operand copy comes out of the same kernel

@@ -240,3 +240,35 @@ def test_cta_pair_kernel_gate_and_operand_copy(backends):
     r1 = B.matmul(got, w, mode="bf16").flat_array()
     r2 = B.matmul(B.tensor(want.reshape(m, n)), w, mode="bf16").flat_array()
     assert (r1.view(np.uint32) == r2.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("mode", ["tf32", "bf16"])
+@pytest.mark.parametrize("shape", [(256, 512, 128, False, True), (300, 520, 200, False, False), (64, 248, 4096, False, True),
+                                   (2304, 4352, 192, True, False), (33, 7, 20, False, False)],
+                         ids=["256x512x128", "ragged", "splitk", "pair", "odd-n"])
+def test_update_epilogue_equals_gradient_then_update(backends, mode, shape):
+    """dls_matmul_sgd: w -= lr * (a b) applied by the contraction's epilogue, in place, equals -- bit for bit -- the
+    materialised product followed by `data - delta * learningRate` (TW:63-72), on every kernel path (single CTA, CTA pair,
+    split-K, direct-store); in bf16 mode the weight's new operand copy is the staged copy of the new value."""
+    O, B = backends
+    m, n, k, ta, tb = shape
+    be = B.default_backend()
+    a, b = operands(m, n, k, ta, tb, seed=m * 3 + n)
+    w0 = np.random.RandomState(12).standard_normal((m, n)).astype(np.float32)
+    lr = 0.0625 + 1e-3
+    at, bt = B.tensor(a).do_cache(), B.tensor(b).do_cache()
+    product = B.matmul(at, bt, transpose_a=ta, transpose_b=tb, mode=mode)
+    spec = dict(product._ungated)
+    want = (B.tensor(w0) - product * lr).flat_array()
+    w = B.tensor(w0).do_cache()
+    be.matmul_sgd(spec, w, lr)
+    got = w.flat_array()
+    assert (got.view(np.uint32) == want.view(np.uint32)).all()
+    if mode == "bf16":
+        probe = B.tensor(np.random.RandomState(13).standard_normal((n, 40)).astype(np.float32)).do_cache()
+        n0 = be.stats()["kernel_launches"]
+        r1 = B.matmul(w, probe, mode="bf16").flat_array()
+        used = be.stats()["kernel_launches"] - n0
+        r2 = B.matmul(B.tensor(want.reshape(m, n)), probe, mode="bf16").flat_array()
+        assert (r1.view(np.uint32) == r2.view(np.uint32)).all()
+        assert used <= 2          # the product (+ a split-K reduce): no staging pass for the weight

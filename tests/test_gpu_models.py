@@ -186,3 +186,31 @@ def test_data_parallel_step_equals_the_full_batch_step(env, kind):
         assert (w0 == w1).all() and (b0 == b1).all()            # replicas stay bit-identical
         assert rel(ow - w0, ow - rw) <= 1e-5
         assert rel(ob - b0, ob - rb) <= 1e-5
+
+
+@pytest.mark.parametrize("mode", ["tf32", "bf16"])
+def test_update_in_the_gradient_contraction_equals_the_separate_update(env, mode):
+    """Long contractions (batch >= 1024) apply `w - lr * dw` in the weight-gradient GEMM's epilogue on a single GPU: two
+    steps must leave exactly the weights the materialise-then-update path leaves."""
+    MO, O, B, H = env
+    sizes, batch = (96, 160, 64, 32), 1024
+    x = np.random.RandomState(21).standard_normal((sizes[0], batch)).astype(np.float32)
+    results = []
+    for fused in (True, False):
+        old = H.ExchangeSgd.fuse_contractions
+        H.ExchangeSgd.fuse_contractions = fused
+        be = B.Backend(gemm_mode=mode)
+        try:
+            model = H.Mlp(sizes, bias=True, last_activation="tanh", backend=be, learning_rate=0.01)
+            n0 = be.stats()["kernel_launches"]
+            losses = [model.step(be.tensor(x), None) for _ in range(2)]
+            launches = be.stats()["kernel_launches"] - n0
+            results.append((losses, [p.copy() for p in model.parameters()], launches))
+        finally:
+            H.ExchangeSgd.fuse_contractions = old
+            be.close()
+    (l1, p1, n1), (l2, p2, n2) = results
+    assert l1 == l2
+    for u, v in zip(p1, p2):
+        assert (u.view(np.uint32) == v.view(np.uint32)).all()
+    assert n1 < n2
