@@ -269,6 +269,10 @@ def test_update_epilogue_equals_gradient_then_update(backends, mode, shape):
         n0 = be.stats()["kernel_launches"]
         r1 = B.matmul(w, probe, mode="bf16").flat_array()
         used = be.stats()["kernel_launches"] - n0
-        r2 = B.matmul(B.tensor(want.reshape(m, n)), probe, mode="bf16").flat_array()
+        fresh = B.tensor(want.reshape(m, n)).do_cache()
+        fresh.flat_array()
+        n0 = be.stats()["kernel_launches"]
+        r2 = B.matmul(fresh, probe, mode="bf16").flat_array()
+        used_fresh = be.stats()["kernel_launches"] - n0
         assert (r1.view(np.uint32) == r2.view(np.uint32)).all()
-        assert used <= 2          # the product (+ a split-K reduce): no staging pass for the weight
+        assert used == used_fresh          # r1 staged the probe but not the weight; r2 staged the weight but not the probe
