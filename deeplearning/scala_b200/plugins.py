@@ -153,7 +153,7 @@ class TensorLayer(Differentiable):
                 # an in-place rule is about to overwrite the weights a lazy forward expression still reads: pin the
                 # forward value first, so `train` yields the data of THIS step like the reference (TL:70-76)
                 data = data.do_cache()
-            if not self.plugins.cumulative:                                  # cumulative layers flush on release: the
+            if not self.plugins.cumulative and self.plugins.flush_in_train:   # cumulative layers flush on release: the
                 self.plugins.flush_updates()                                 # caller flushes after running the Do
             return Do.now(data)
 
@@ -224,6 +224,9 @@ class Plugins:
                  defer_updates: bool = False, optimizer=None):
         self.cumulative = cumulative
         self.step_id = 0
+        # False: `train` leaves the deferred weight updates to the caller's `flush_updates()`, so whatever the caller maps
+        # over the forward data (the loss reduction) is issued BEFORE the end-of-step exchange and update instead of behind it
+        self.flush_in_train = True
         # a stateful optimizer (optimizers.Momentum / Adam) updates weights in place, which is only safe at the end of
         # the step: it implies deferred updates
         self.optimizer = optimizer
