@@ -228,7 +228,9 @@ class Trainer:
                          optimizer=optimizer)
         # `run` / `CompiledStep` flush explicitly after the loss reduction has been issued: the scalar loss does not wait
         # behind the gradient exchange and the update (5-9 us off the tail of a step)
-        self.P.flush_in_train = False
+        # (only with the fused SGD, whose gradients are materialised the moment they arrive: the lazy deltas of the other
+        # optimizers read layer buffers that are released with the Do, so those still flush inside `train`)
+        self.P.flush_in_train = fused is None
         if exchange is not None:
             self.P.before_flush.append(exchange.flush)
         self.L = Layers(self.P)
