@@ -130,7 +130,7 @@ struct Tile {
   int m0, n0;
 };
 // Grouped raster: 8 tile-rows share their B tiles through L2 while the group sweeps N.
-__device__ __forceinline__ Tile tile_coord(int t, int tiles_m, int tiles_n) {
+__device__ __forceinline__ Tile tile_coord(int t, int tiles_m, int tiles_n, int bn = BN) {
   constexpr int GROUP = 8;
   const int per_group = GROUP * tiles_n;
   const int g = t / per_group;
@@ -139,7 +139,7 @@ __device__ __forceinline__ Tile tile_coord(int t, int tiles_m, int tiles_n) {
   const int r = t - g * per_group;
   Tile c;
   c.m0 = (first_m + r % gsz) * BM;
-  c.n0 = (r / gsz) * BN;
+  c.n0 = (r / gsz) * bn;
   return c;
 }
 
@@ -305,7 +305,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   uint32_t *tmem_slot = (uint32_t *)(bars + 2 * STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
+  // plain GEMM: tile width bn = cg.n_mma (256, or 128 for problems with too few 256-wide tiles to fill the machine);
+  // convolution modes: one tile column of cg.n_mma (<= 256) output channels
+  const int bn = CONV ? BN : cg.n_mma;
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + bn - 1) / bn;
   const int n_tiles = tiles_m * tiles_n;
   const int num_kb = CONV == 1 ? 9 * cg.kc_per_tap : (K + BLOCK_K - 1) / BLOCK_K;
   const int n_work = n_tiles * splits;
@@ -342,7 +345,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
-        const Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n);
+        const Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n, bn);
         const int kb0 = (w / n_tiles) * kb_per_split, kb1 = min(num_kb, kb0 + kb_per_split);
         int img0 = 0, row0 = 0;
         if (CONV == 1) pixel_tile(cg, tc.m0 / BM, img0, row0);
@@ -385,7 +388,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             }
             continue;
           }
-          mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+          mbar_expect_tx(full_bar(stage), A_STAGE_BYTES + bn * 128);
           if (A_MN) {
 #pragma unroll
             for (int j = 0; j < BM / MN_ATOM; ++j)
@@ -394,8 +397,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             tma_load_2d(a_dst, &map_a, full_bar(stage), k0, tc.m0);
           }
           if (B_MN) {
-#pragma unroll
-            for (int j = 0; j < BN / MN_ATOM; ++j)
+            for (int j = 0; j < bn / MN_ATOM; ++j)
               tma_load_2d(b_dst + j * BLOCK_K * 128, &map_b, full_bar(stage), tc.n0 + j * MN_ATOM, k0);
           } else {
             tma_load_2d(b_dst, &map_b, full_bar(stage), k0, tc.n0);
@@ -413,7 +415,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       // instruction descriptor (cute::UMMA::InstrDescriptor): D = fp32, A/B format, major-ness, N >> 3, M >> 4
       const uint32_t fmt = TF32 ? 2u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
-                             ((uint32_t)((CONV ? cg.n_mma : BN) >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+                             ((uint32_t)(cg.n_mma >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
       // K-major: 8-row groups are 1024 B apart (SBO), one swizzle atom along K (LBO unused).
       // MN-major: 8 K-rows of 128 B form an atom (SBO = 1024 B), atoms along MN are BLOCK_K * 128 B apart (LBO).
       const uint32_t a_lbo = A_MN ? BLOCK_K * 128 : 0, b_lbo = B_MN ? BLOCK_K * 128 : 0;
@@ -457,7 +459,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
     int it = 0;
     int buf = 0;
     for (int w = blockIdx.x; w < n_work; w += gridDim.x, ++it) {
-      Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n);
+      Tile tc = tile_coord(w % n_tiles, tiles_m, tiles_n, bn);
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       mbar_wait(tfull_bar(as), aphase);
@@ -468,7 +470,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       tc.m0 += (w / n_tiles) * tiles_m * BM;                      // split-K: rows of this split's partial matrix
       const int row = tc.m0 + quarter * 32 + lane;
 #pragma unroll 1
-      for (int c = 0; c < BN / EPI_CHUNK; ++c) {
+      for (int c = 0; c < bn / EPI_CHUNK; ++c) {
         const int col0 = tc.n0 + c * EPI_CHUNK;
         if (col0 >= N) break;                                     // warp uniform
         uint32_t v[32];
@@ -984,7 +986,8 @@ static int launch_variant(dls_ctx *ctx, cudaStream_t st, const CUtensorMap &ma, 
     DLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     configured[dev].store(true, std::memory_order_release);
   }
-  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * sp.splits;
+  const int bn = CONV ? BN : cg.n_mma;
+  const int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn) * sp.splits;
   // one persistent CTA per SM; SMs hosting an in-flight collective (data-parallel exchange) are left to it
   const int sms = usable_sms(ctx);
   const int grid = tiles < sms ? tiles : sms;
@@ -1086,18 +1089,26 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   }();
   const long long tiles2 = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + BN2 - 1) / BN2);
   const bool pair_mode = !pair_off && tiles2 >= ctx->sm_count && K >= 4 * block_k;
+  // too few 256-wide tiles to occupy half the machine and a K too short to split: 128-wide tiles double the CTAs at work
+  // (the weight gradient / backward-data contractions of a dense layer over a small batch are output bound)
+  const int tiles256 = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int num_kb_all = (K + block_k - 1) / block_k;
+  const bool will_split = tiles256 * 2 <= tc::usable_sms(ctx) && num_kb_all >= 16 && N % 4 == 0;
+  const int bn = (!pair_mode && !will_split && N > 128 && tiles256 * 2 <= ctx->sm_count) ? 128 : BN;
   rc = b_mn ? make_map(&mb, dt, elem, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, mn_atom, block_k)
-            : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, pair_mode ? BN2 / 2 : BN);
+            : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, pair_mode ? BN2 / 2 : bn);
   if (rc) return rc;
+  ConvGeom plain;
+  plain.n_mma = bn;
   // split-K: a contraction with few output tiles and a long K (the weight gradients of a convolution: M x N = Cin*9 x Cout,
   // K = batch * H * W) would leave most SMs idle; cut K into `splits` ranges, one work item each, then reduce the partials.
-  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
   const int num_kb = (K + block_k - 1) / block_k;
   SplitPlan sp;
   sp.kb_per_split = num_kb;
   sp.c_rows = M;
   const int sms = tc::usable_sms(ctx);
-  if (tiles * 2 <= sms && num_kb >= 16 && N % 4 == 0) {
+  if (will_split) {
     int want = std::min(sms / tiles, num_kb / 8);
     sp.kb_per_split = (num_kb + want - 1) / want;
     sp.splits = (num_kb + sp.kb_per_split - 1) / sp.kb_per_split;
@@ -1130,11 +1141,11 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
     else if (a_mn && !b_mn) rc = launch_variant2<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
     else rc = launch_variant2<false, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
   } else if (!rc) {
-    if (tf32) rc = launch_variant<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
-    else if (!a_mn && !b_mn) rc = launch_variant<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
-    else if (!a_mn && b_mn) rc = launch_variant<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
-    else if (a_mn && !b_mn) rc = launch_variant<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
-    else rc = launch_variant<false, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp);
+    if (tf32) rc = launch_variant<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else if (!a_mn && !b_mn) rc = launch_variant<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else if (!a_mn && b_mn) rc = launch_variant<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else if (a_mn && !b_mn) rc = launch_variant<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else rc = launch_variant<false, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
   }
   if (!rc && sp.splits > 1) {
     // partial s lives at rows [s * m_pad, s * m_pad + M) of the scratch matrix; when N is not a multiple of 4 the scratch
