@@ -34,7 +34,7 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
   } while (0)
 
 constexpr int kMaxStreams = 32;
-constexpr int kShadows = 4;               // staged operand copies cached per buffer (dls_buf::shadow)
+constexpr int kShadows = 5;               // staged operand copies cached per buffer (dls_buf::shadow)
 constexpr int kReduceMaxBlocks = 4096;   // partial sums per stream-private scratch
 
 struct Block {
@@ -80,9 +80,10 @@ struct dls_buf {
   // [rows, cols] interpretation, kept until the buffer is written again or released, so a tensor that feeds several
   // contractions (an activation in forward and in the weight-gradient GEMM) is staged once.
   // slots 2 and 3 belong to the convolution path (conv.cu): the staged NHWC operand copy of an activation / delta, and
-  // the packed per-tap weight matrices of a [3,3,Cin,Cout] weight.
+  // the packed per-tap weight matrices of a [3,3,Cin,Cout] weight; slot 4: a second conv copy of the same buffer in another
+  // form (a sampled delta: compact for the weight gradient, zero-filled for backward-data).
   dls::Block shadow[dls::kShadows];
-  long long shadow_rows[dls::kShadows] = {0, 0, 0, 0}, shadow_cols[dls::kShadows] = {0, 0, 0, 0};
+  long long shadow_rows[dls::kShadows] = {0, 0, 0, 0, 0}, shadow_cols[dls::kShadows] = {0, 0, 0, 0, 0};
 };
 
 struct dls_graph {

@@ -466,12 +466,12 @@ inline size_t elem_bytes(int mode) { return mode == DLS_GEMM_TF32 ? 4 : 2; }
 // until the buffer is written again: the forward pass and the weight gradient share the copy of an activation, the
 // backward-data pass and the weight gradient share the copy of a delta).
 int staged_act(dls_ctx *ctx, int stream, int mode, dls_buf *buf, int batch, int h, int w, int c, int stride, int up, const void **ptr,
-               int *cp) {
-  Block &sh = buf->shadow[2];
+               int *cp, int slot = 2) {
+  Block &sh = buf->shadow[slot];
   const long long tag_r = ((long long)mode << 60) | ((long long)up << 56) | ((long long)stride << 48) | ((long long)h << 24) | (long long)w;
   const long long tag_c = ((long long)batch << 24) | (long long)c;
   const int p = pad_channels(mode, c);
-  if (!(sh.ptr && buf->shadow_rows[2] == tag_r && buf->shadow_cols[2] == tag_c && sh.pool == ctx->capture_pool)) {
+  if (!(sh.ptr && buf->shadow_rows[slot] == tag_r && buf->shadow_cols[slot] == tag_c && sh.pool == ctx->capture_pool)) {
     if (sh.ptr) free_block(ctx, sh);
     const long long pixels = (long long)batch * h * w;
     int rc = alloc_block(ctx, (size_t)pixels * p * elem_bytes(mode), stream, &sh);
@@ -480,8 +480,8 @@ int staged_act(dls_ctx *ctx, int stream, int mode, dls_buf *buf, int batch, int 
       if (sh.ptr) free_block(ctx, sh);
       return rc;
     }
-    buf->shadow_rows[2] = tag_r;
-    buf->shadow_cols[2] = tag_c;
+    buf->shadow_rows[slot] = tag_r;
+    buf->shadow_cols[slot] = tag_c;
   } else {
     int rc = wait_streams(ctx, stream, sh.stream_mask);
     if (rc) return rc;
@@ -652,8 +652,15 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
     const void *xa, *da;
     int cxp, cdp;
     rc = staged_act(ctx, stream, mode, x, (int)batch, (int)h, (int)wd, (int)cin, stride, 1, &xa, &cxp);
-    if (!rc) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, dzs, &da, &cdp);
-    if (!rc) rc = launch_conv_dw_tc(ctx, stream, mode, xa, cxp, da, cdp, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, o->ptr);
+    // a sampled delta is contracted over its own pixels only: staged compact (slot 4; backward-data keeps the zero-filled
+    // full-size copy in slot 2), the activation read through TMA element strides
+    ConvGeom probe;
+    const bool compact = dzs > 1 && dzs <= 8 && conv_tiling((int)h / dzs, (int)wd / dzs, 64, &probe) && probe.bw * dzs <= 256 &&
+                         probe.bh * dzs <= 256;
+    if (!rc && compact) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h / dzs, (int)wd / dzs, (int)cout, 1, 1, &da, &cdp, 4);
+    else if (!rc) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, dzs, &da, &cdp);
+    if (!rc) rc = launch_conv_dw_tc(ctx, stream, mode, xa, cxp, da, cdp, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, o->ptr,
+                                    compact ? dzs : 1);
   }
   if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 2, done);
   if (rc) {

@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
             for (int j = 0; j < a_atoms; ++j) {
               const int rb = rb0 + j, tap = rb / cg.cblks, cb = rb - tap * cg.cblks;
               const int oy = tap / 3 - 1, ox = tap - (tap / 3) * 3 - 1;
-              tma_load_4d(a_dst + j * BLOCK_K * 128, &map_a, full_bar(stage), cb * MN_ATOM, -ox, py - oy, pi);
+              tma_load_4d(a_dst + j * BLOCK_K * 128, &map_a, full_bar(stage), cb * MN_ATOM, -ox, py * cg.px_stride - oy, pi);
             }
             for (int j = 0; j < b_atoms; ++j) tma_load_2d(b_dst + j * BLOCK_K * 128, &map_b, full_bar(stage), j * MN_ATOM, k0);
             if (++stage == STAGES) {
@@ -914,7 +914,7 @@ static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, co
 // rank-N row-major tensor (dims[0] innermost, strides in bytes for dims 1..rank-1) with a 128B-swizzled box; elements
 // outside the tensor read as zero.
 static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *base, int rank, const uint64_t *dims,
-                       const uint64_t *strides_bytes, const uint32_t *box) {
+                       const uint64_t *strides_bytes, const uint32_t *box, const uint32_t *elem_strides = nullptr) {
   encode_tiled_fn enc = get_encoder();
   DLS_CHECK(enc != nullptr, DLS_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t d[5], s[4];
@@ -922,7 +922,7 @@ static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *bas
   for (int i = 0; i < rank; ++i) {
     d[i] = dims[i];
     b[i] = box[i];
-    e[i] = 1;
+    e[i] = elem_strides ? elem_strides[i] : 1;   // traversal stride: box[i] / e[i] elements are loaded along dim i
     if (i + 1 < rank) s[i] = strides_bytes[i];
   }
   CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void *>(base), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -1259,23 +1259,26 @@ bool conv_dw_tc_supported(int kind, int H, int W, int cin, int cout) {
 }
 
 int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int cxp, const void *dz, int cdp, int batch, int H, int W,
-                      int cin, int cout, float *dw) {
+                      int cin, int cout, float *dw, int dzs) {
   using namespace tc;
   DLS_CHECK(conv_dw_tc_supported(kind, H, W, cin, cout) && cxp % 64 == 0 && cdp % 64 == 0, DLS_ERR_UNSUPPORTED,
             "launch_conv_dw_tc: shape not supported by the implicit-GEMM weight-gradient kernel");
   ConvGeom cg;
-  conv_tiling(H, W, 64, &cg);
+  // the k pixels: all of them, or (sampled delta) the H/dzs x W/dzs grid of delta-carrying ones
+  DLS_CHECK(conv_tiling(H / dzs, W / dzs, 64, &cg), DLS_ERR_UNSUPPORTED, "launch_conv_dw_tc: the sampled pixel grid does not tile");
   cg.cblks = cxp / 64;
   cg.n_mma = (cout + 15) & ~15;
-  const long long P = (long long)batch * H * W;
+  cg.px_stride = dzs;
+  const long long P = (long long)batch * (H / dzs) * (W / dzs);
   DLS_CHECK(P < (1LL << 31), DLS_ERR_UNSUPPORTED, "launch_conv_dw_tc: too many pixels");
   const int M = 9 * cxp, N = cout;
   CUtensorMap ma, mb, mc;
   {
     const uint64_t dims[4] = {(uint64_t)cxp, (uint64_t)W, (uint64_t)H, (uint64_t)batch};
     const uint64_t str[3] = {(uint64_t)cxp * 2, (uint64_t)cxp * 2 * W, (uint64_t)cxp * 2 * W * H};
-    const uint32_t box[4] = {64, (uint32_t)cg.bw, (uint32_t)cg.bh, (uint32_t)cg.bb};
-    int rc = make_map_nd(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, act, 4, dims, str, box);
+    const uint32_t box[4] = {64, (uint32_t)(cg.bw * dzs), (uint32_t)(cg.bh * dzs), (uint32_t)cg.bb};
+    const uint32_t est[4] = {1, (uint32_t)dzs, (uint32_t)dzs, 1};
+    int rc = make_map_nd(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, act, 4, dims, str, box, est);
     if (rc) return rc;
   }
   int rc = make_map(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dz, (uint64_t)cdp, (uint64_t)P, (uint64_t)cdp, 64, 64);

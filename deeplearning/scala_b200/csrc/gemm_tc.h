@@ -32,6 +32,7 @@ struct ConvGeom {
   int n_mma = 0;                  // UMMA N (multiple of 16, <= 256) and rows of the weight box
   int b_bytes = 0;                // bytes of one B stage (n_mma x 128)
   int cblks = 0;                  // CONV 2: 64-channel blocks per tap
+  int px_stride = 1;              // CONV 2: the k pixels are every px_stride-th pixel of the activation (a sampled delta)
 };
 
 // Implicit-GEMM 'same' 3x3 convolution on the tensor cores, out[P, N] fp32 (P = batch*H*W pixels, row-major) =
@@ -48,8 +49,10 @@ int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batc
 // pixels, both operands read MN-major from their staged NHWC copies (act [batch][H][W][cxp], dz [batch*H*W][cdp]; bf16 only,
 // channels padded to 64), A through tap-shifted 4-D boxes; split over the SMs along the pixels + one reduce launch.
 bool conv_dw_tc_supported(int kind, int H, int W, int cin, int cout);
+// dzs > 1: dz is the COMPACT sampled delta [batch * H/dzs * W/dzs][cdp]; only those pixels are contracted, and the activation
+// boxes are read with TMA element strides (dzs along x and y).
 int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int cxp, const void *dz, int cdp, int batch, int H, int W,
-                      int cin, int cout, float *dw);
+                      int cin, int cout, float *dw, int dzs = 1);
 
 // conv.cu
 bool conv_direct_supported(int cin, int cout);
