@@ -351,12 +351,14 @@ __global__ void __launch_bounds__(256) conv_direct_dw_reduce_kernel(const float 
   if (lane == 0) dw[o] = s;
 }
 
-int direct_rows(int H, int W, int dzs) {
-  // band height: 8 rows (a 10 x (W + 2) x 4 float patch, 5.4 KB at W = 32: one halo re-read per four rows), fewer for wide
-  // images so the patch stays below 40 KB; a multiple of the delta's sampling factor
-  int r = 8;
-  while (r > 1 && (long long)(r + 2) * (W + 2) * 16 > 40 * 1024) r >>= 1;
-  if (r > H) r = H;
+int direct_rows(int H, int W, int dzs, int B, int sm_count) {
+  // band height.  The kernels are latency bound (one patch fill, one barrier, then a few mma tiles per warp), so a band is
+  // as tall as fits -- the whole image when its (H + 2) x (W + 2) x 4 float patch stays below 40 KB (18.5 KB at 32 x 32:
+  // 64 forward tiles / 32 sampled-delta groups per band instead of 16 / 8, and no halo rows read twice) -- as long as
+  // there is still a band for every SM; a multiple of the delta's sampling factor
+  auto patch = [&](int r) { return (long long)(r + 2) * (W + 2) * 16; };
+  int r = H;
+  while (r > 1 && (patch(r) > 40 * 1024 || ((long long)B * ((H + r - 1) / r) < sm_count && r > 8))) r = (r + 1) / 2;
   if (dzs > 1) r = std::max(dzs, r / dzs * dzs);
   return r;
 }
@@ -368,7 +370,7 @@ bool conv_direct_supported(int cin, int cout) { return cin >= 1 && cin <= 4 && c
 template <int MODE>
 static int launch_direct_fwd_mode(dls_ctx *ctx, cudaStream_t st, const float *x, const float *w, const float *bias, float *out, int B,
                                   int H, int W, int cin, int cout, int act, int stride) {
-  const int R = direct_rows(H, W, 1);
+  const int R = direct_rows(H, W, 1, B, ctx->sm_count);
   const size_t smem = (size_t)(R + 2) * (W + 2) * 4 * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
   const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 4);
@@ -395,7 +397,7 @@ template <int MODE>
 static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
                                  int cout, int stride, int dzs) {
   cudaStream_t st = ctx->streams[stream];
-  const int R = direct_rows(H, W, dzs);
+  const int R = direct_rows(H, W, dzs, B, ctx->sm_count);
   const size_t patch = (size_t)(R + 2) * (W + 2) * 4, red = (size_t)kDirectWarps * 36 * 32;
   const size_t smem = std::max(patch, red) * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
