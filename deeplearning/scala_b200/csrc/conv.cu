@@ -137,6 +137,27 @@ __device__ __forceinline__ void direct_fill_patch(float *sx, const float *__rest
                                                   int stride) {
   const int row_len = (W + 2) * 4;
   const int total = (R + 2) * row_len;
+  if (stride == 1 && ((W * CIN) & 3) == 0 && ((uintptr_t)x & 15) == 0) {
+    // dense source whose image rows are whole float4s: every thread's 128-bit loads are independent (one round trip to
+    // memory for the whole patch instead of one per element); the ring, the pad channel and rows outside the image are
+    // zeroed first
+    for (int i = threadIdx.x; i < total; i += blockDim.x) sx[i] = 0.f;
+    __syncthreads();
+    const int n4 = (W * CIN) >> 2;
+    for (int i = threadIdx.x; i < (R + 2) * n4; i += blockDim.x) {
+      const int r = i / n4, q = i - r * n4;
+      const int gy = y0 + r - 1;
+      if (gy < 0 || gy >= H) continue;
+      const float4 v = __ldg(reinterpret_cast<const float4 *>(x + ((b * H + gy) * (long long)W) * CIN) + q);
+      const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int flat = 4 * q + k, px = flat / CIN, c = flat - px * CIN;
+        sx[(r * (W + 2) + px + 1) * 4 + c] = round_operand<MODE>(e[k]);
+      }
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const int r = i / row_len, rem = i - r * row_len;
     const int col = rem >> 2, c = rem & 3;
@@ -280,38 +301,53 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const
     __syncthreads();
     const int nps = (rows / dzs) * Ws;            // delta-carrying pixels of the band
     const float *dzb = dz + ((b * Hs + y0 / dzs) * (long long)Ws) * Cout;
-    for (int grp = warp; grp * 8 < nps; grp += kDirectWarps) {
-      // k columns of A / rows of B: pixels grp * 8 + t and + 4
-      int pq[2];
-      bool ok[2];
-      const float *ap[2];
+    // two groups of 8 pixels per trip: all 16 delta loads of a trip are issued before the first mma needs one
+    for (int grp0 = warp; grp0 * 8 < nps; grp0 += 2 * kDirectWarps) {
+      int pq[2][2];
+      bool ok[2][2];
+      uint32_t bf[2][4][2];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int q = grp * 8 + t + 4 * h;
-        ok[h] = q < nps;
-        pq[h] = ok[h] ? q : 0;
-        const int ys = pq[h] / Ws, xs = pq[h] - ys * Ws;
-        ap[h] = sx + ((ys * dzs + 2) * (W + 2) + xs * dzs + 2) * 4;
-      }
-      uint32_t bf[4][2];
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
+      for (int u = 0; u < 2; ++u) {
+        const int grp = grp0 + u * kDirectWarps;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int n = nt * 8 + g;
-          float v = 0.f;
-          if (ok[h] && n < Cout) v = round_operand<MODE>(__ldg(dzb + (long long)pq[h] * Cout + n));
-          bf[nt][h] = __float_as_uint(v);
+          const int q = grp * 8 + t + 4 * h;          // k columns of A / rows of B: pixels grp * 8 + t and + 4
+          ok[u][h] = q < nps;
+          pq[u][h] = ok[u][h] ? q : 0;
         }
 #pragma unroll
-      for (int mt = 0; mt < 3; ++mt) {
-        uint32_t a[4];
+        for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
-        for (int h = 0; h < 2; ++h)      // a0 = (m, pixel t), a1 = (m + 8, pixel t), a2 = (m, pixel t + 4), a3 = (m + 8, pixel t + 4)
+          for (int h = 0; h < 2; ++h) {
+            const int n = nt * 8 + g;
+            float v = 0.f;
+            if (ok[u][h] && n < Cout) v = __ldg(dzb + (long long)pq[u][h] * Cout + n);
+            bf[u][nt][h] = __float_as_uint(v);
+          }
+      }
 #pragma unroll
-          for (int r = 0; r < 2; ++r) a[2 * h + r] = aoff[mt][r] != INT_MIN ? __float_as_uint(ap[h][aoff[mt][r]]) : 0u;
+      for (int u = 0; u < 2; ++u) {
+        if ((grp0 + u * kDirectWarps) * 8 >= nps) break;
+        const float *ap[2];
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) mma_tf32_16x8x8(acc[mt][nt], a, bf[nt]);
+        for (int h = 0; h < 2; ++h) {
+          const int ys = pq[u][h] / Ws, xs = pq[u][h] - ys * Ws;
+          ap[h] = sx + ((ys * dzs + 2) * (W + 2) + xs * dzs + 2) * 4;
+        }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) bf[u][nt][h] = __float_as_uint(round_operand<MODE>(__uint_as_float(bf[u][nt][h])));
+#pragma unroll
+        for (int mt = 0; mt < 3; ++mt) {
+          uint32_t a[4];
+#pragma unroll
+          for (int h = 0; h < 2; ++h)    // a0 = (m, pixel t), a1 = (m + 8, pixel t), a2 = (m, pixel t + 4), a3 = (m + 8, pixel t + 4)
+#pragma unroll
+            for (int r = 0; r < 2; ++r) a[2 * h + r] = aoff[mt][r] != INT_MIN ? __float_as_uint(ap[h][aoff[mt][r]]) : 0u;
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) mma_tf32_16x8x8(acc[mt][nt], a, bf[u][nt]);
+        }
       }
     }
   }
