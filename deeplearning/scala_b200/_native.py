@@ -106,6 +106,8 @@ _SIG = {
                                       C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
     "dls_conv3x3_backward_data": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                             C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_conv3x3_backward_data_gated": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                                  C.c_size_t, C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
     "dls_conv3x3_backward_weights": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                                C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
     "dls_comm_unique_id": (C.c_int, [C.c_char_p]),

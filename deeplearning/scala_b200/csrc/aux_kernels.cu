@@ -253,6 +253,18 @@ __global__ void __launch_bounds__(kBlock) sum_axis_slab4_ticket_kernel(const flo
   if (rl < lanes) {
     const float4 *p = reinterpret_cast<const float4 *>(in) + c4;
     size_t r = r0 + rl;
+    for (; r + 7 * (size_t)lanes < r1; r += 8 * (size_t)lanes) {   // eight independent 128-bit loads in flight per thread
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcs(p + (r + (size_t)u * lanes) * inner4);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        a[u & 3].x += v[u].x;
+        a[u & 3].y += v[u].y;
+        a[u & 3].z += v[u].z;
+        a[u & 3].w += v[u].w;
+      }
+    }
     for (; r + 3 * (size_t)lanes < r1; r += 4 * (size_t)lanes) {
       float4 v[4];
 #pragma unroll
@@ -331,7 +343,8 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
   if (outer == 1 && inner > 1 && k * std::min<size_t>(inner, 32) <= 16384 && inner <= 4096) {
     sum_axis_small_kernel<<<(unsigned)((inner + 31) / 32), kBlock, 0, st>>>(in, out, k, inner);
   } else if (outer == 1 && inner % 4 == 0 && inner <= kBlock && k >= 512 && ((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 15) == 0) {
-    size_t blocks = std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count, (k + 63) / 64));
+    // two blocks per SM: one trip of eight loads per thread covers a block's rows for the bias gradients of a step
+    size_t blocks = std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count * 2, (k + 63) / 64));
     const size_t rows_per_block = (k + blocks - 1) / blocks;
     blocks = (k + rows_per_block - 1) / rows_per_block;
     Block scratch;

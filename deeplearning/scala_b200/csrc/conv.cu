@@ -626,9 +626,13 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
   return DLS_OK;
 }
 
-int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
-                              const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done) {
+int dls_conv3x3_backward_data_gated(dls_ctx *ctx, dls_buf *dz, dls_buf *w, dls_buf *gate, int gate_mode, int gate_stride, size_t batch,
+                                    size_t h, size_t wd, size_t cin, size_t cout, const dls_conv_opts *opts, dls_event *const *deps,
+                                    int n_deps, dls_buf **out, dls_event **done) {
   DLS_CHECK(ctx && dz && w && out, DLS_ERR_INVALID, "dls_conv3x3_backward_data: NULL argument");
+  if (gate_stride < 1) gate_stride = 1;
+  DLS_CHECK(gate_mode >= 0 && gate_mode <= 2 && (gate_mode == 0 || (gate && gate->n >= batch * h * gate_stride * wd * gate_stride * cin)),
+            DLS_ERR_INVALID, "dls_conv3x3_backward_data_gated: gate missing or shorter than [batch, h*gs, w*gs, cin]");
   DLS_CHECK(fits_int(batch) && fits_int(h) && fits_int(wd) && fits_int(cin) && fits_int(cout), DLS_ERR_INVALID,
             "dls_conv3x3_backward_data: bad shape");
   const int dzs = (opts && opts->dz_stride > 1) ? opts->dz_stride : 1;
@@ -641,8 +645,8 @@ int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batc
             "dls_conv3x3_backward_data: shape / mode not covered");
   DLS_CUDA(cudaSetDevice(ctx->device));
   const int stream = pick_stream(ctx);
-  dls_buf *ins[2] = {dz, w};
-  int rc = wait_inputs(ctx, stream, ins, 2, deps, n_deps);
+  dls_buf *ins[3] = {dz, w, gate_mode ? gate : nullptr};
+  int rc = wait_inputs(ctx, stream, ins, 3, deps, n_deps);
   if (rc) return rc;
   dls_buf *o = nullptr;
   rc = new_buf(ctx, batch * h * wd * cin, stream, &o);
@@ -652,14 +656,22 @@ int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batc
   rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, dzs, &da, &cp);
   if (!rc) rc = staged_weights(ctx, stream, mode, w, (int)cin, (int)cout, &wf, &wb);
   // dx[b,y,x,c] = sum_{ky,kx,f} dz[b, y+(ky-1), x+(kx-1), f] * w[ky,kx,c,f]: the same kernel with the taps mirrored
-  if (!rc) rc = launch_conv_tc(ctx, stream, mode, da, (int)batch, (int)h, (int)wd, cp, wb, (int)cin, o->ptr, -1, GemmEpilogue());
-  if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 2, done);
+  GemmEpilogue epi;
+  epi.gate = gate_mode ? gate->ptr : nullptr;
+  epi.gate_mode = gate_mode;
+  if (!rc) rc = launch_conv_tc(ctx, stream, mode, da, (int)batch, (int)h, (int)wd, cp, wb, (int)cin, o->ptr, -1, epi, gate_stride);
+  if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 3, done);
   if (rc) {
     dls_buf_release(o);
     return rc;
   }
   *out = o;
   return DLS_OK;
+}
+
+int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
+                              const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done) {
+  return dls_conv3x3_backward_data_gated(ctx, dz, w, nullptr, 0, 1, batch, h, wd, cin, cout, opts, deps, n_deps, out, done);
 }
 
 int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,

@@ -469,6 +469,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       if (bias_mode == 1 && tc.m0 + quarter * 32 + lane < M) row_bias = __ldg(bias + tc.m0 + quarter * 32 + lane);
       tc.m0 += (w / n_tiles) * tiles_m * BM;                      // split-K: rows of this split's partial matrix
       const int row = tc.m0 + quarter * 32 + lane;
+      long long gate_row = row;                                   // row of the gate tensor that belongs to output row `row`
+      if (CONV == 1 && cg.gate_stride > 1) {
+        const int hw = cg.H * cg.W, b = row / hw, rem = row - b * hw, y = rem / cg.W, x = rem - y * cg.W;
+        gate_row = ((long long)(b * cg.H + y) * cg.gate_stride * cg.W + x) * cg.gate_stride;
+      }
 #pragma unroll 1
       for (int c = 0; c < bn / EPI_CHUNK; ++c) {
         const int col0 = tc.n0 + c * EPI_CHUNK;
@@ -478,7 +483,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         float f[32];
         epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
-        if (gate_mode && row < M) epi_gate(f, gate + (long long)row * N + col0, N - col0, gate_mode, (N & 3) == 0, gate_scale);
+        if (gate_mode && row < M) epi_gate(f, gate + gate_row * N + col0, N - col0, gate_mode, (N & 3) == 0, gate_scale);
         if (copy && row < M) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(copy) + (long long)row * copy_ld + col0, copy_ld - col0);
         if (direct_store) {
           if (row < c_rows) {
@@ -1197,7 +1202,7 @@ bool conv_tc_supported(int kind, int H, int W, int k_channels, int n) {
 }
 
 int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batch, int H, int W, int kp, const void *wts, int N,
-                   float *C, int tap_sign, const GemmEpilogue &epi) {
+                   float *C, int tap_sign, const GemmEpilogue &epi, int gate_stride) {
   using namespace tc;
   DLS_CHECK(conv_tc_supported(kind, H, W, kp, N), DLS_ERR_UNSUPPORTED, "launch_conv_tc: shape not supported by the implicit-GEMM kernel");
   const bool tf32 = kind == DLS_GEMM_TF32;
@@ -1206,6 +1211,7 @@ int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batc
   conv_tiling(H, W, BM, &cg);
   cg.kc_per_tap = kp / block_k;
   cg.tap_sign = tap_sign;
+  cg.gate_stride = gate_stride;
   cg.n_mma = (N + 15) & ~15;
   cg.b_bytes = cg.n_mma * 128;
   const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;

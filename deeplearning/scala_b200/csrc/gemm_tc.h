@@ -32,6 +32,8 @@ struct ConvGeom {
   int n_mma = 0;                  // UMMA N (multiple of 16, <= 256) and rows of the weight box
   int b_bytes = 0;                // bytes of one B stage (n_mma x 128)
   int cblks = 0;                  // CONV 2: 64-channel blocks per tap
+  int gate_stride = 1;            // CONV 1: the epilogue gate is [images, H*gs, W*gs, N] read at (gs*y, gs*x) (a layer's pinned
+                                  // full-size output under the `scale` view that feeds this convolution)
   int px_stride = 1;              // CONV 2: the k pixels are every px_stride-th pixel of the activation (a sampled delta)
 };
 
@@ -43,7 +45,7 @@ struct ConvGeom {
 bool conv_tc_supported(int kind, int H, int W, int k_channels, int n);
 bool conv_tiling(int H, int W, int pixels, ConvGeom *g);
 int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batch, int H, int W, int kp, const void *wts, int N,
-                   float *C, int tap_sign, const GemmEpilogue &epi);
+                   float *C, int tap_sign, const GemmEpilogue &epi, int gate_stride = 1);
 
 // Weight gradient dw[9*cin, cout] fp32 (= [3,3,cin,cout]) = sum over pixels of act[p - tap][c] * dz[p][f]: contraction over the
 // pixels, both operands read MN-major from their staged NHWC copies (act [batch][H][W][cxp], dz [batch*H*W][cdp]; bf16 only,

@@ -228,9 +228,16 @@ class Layers:
             (t0,) = tapes
             shape0 = list(t0.data.shape)
 
+            def back(d):
+                r = d.broadcast(new_shape).reshape(shape0)
+                spec = getattr(d, "_ungated", None)
+                if spec is not None and list(d.shape) == new_shape:   # lets the layer below fuse its activation derivative
+                    r._ungated_flat = dict(spec=spec, source=d)      # into the contraction that produces this delta
+                return r
+
             def backward(_):
                 def run(do_delta: Do):
-                    t0.backward(do_delta.map(lambda d: d.broadcast(new_shape).reshape(shape0)))
+                    t0.backward(do_delta.map(back))
                 return run
             return t0.data.reshape(new_shape), backward
         return self._lazy([a], build)
@@ -388,12 +395,20 @@ class Layers:
 
                     def dz_sampled(d):                               # [B, H/s, W/s, Cout]: the delta where it can be non-zero
                         if "dzs" not in memo:
-                            d = d.broadcast(half)
-                            ys = y_cached.scale(half) if s > 1 else y_cached
-                            if activation == "tanh":
-                                d = d * (1.0 - ys * ys)
-                            elif activation == "relu":
-                                d = d * relu_mask(ys)
+                            fused = None
+                            if activation != "none" and list(d.shape) == half:
+                                fused = fuse_activation_derivative(d, y_cached, activation, s)
+                            if fused is not None:
+                                # `d` was the still unevaluated backward-data pass / delta contraction of the layer above:
+                                # it is issued with `d * act'(y)` -- y read at the sampled positions -- in its epilogue
+                                d = fused
+                            else:
+                                d = d.broadcast(half)
+                                ys = y_cached.scale(half) if s > 1 else y_cached
+                                if activation == "tanh":
+                                    d = d * (1.0 - ys * ys)
+                                elif activation == "relu":
+                                    d = d * relu_mask(ys)
                             memo["dzs"] = d.do_cache()
                             owned.append(memo["dzs"])
                         return memo["dzs"]
@@ -436,6 +451,27 @@ class Layers:
         if s == 1:
             layer._conv_spec = (x, w, bias, activation)              # lets a following `downsample` fold itself into this layer
         return layer
+
+
+def _unevaluated(t) -> bool:
+    return getattr(t, "_weak", None) is None or t._weak() is None
+
+
+def fuse_activation_derivative(d, y, activation: str, y_stride: int):
+    """`d * act'(y)` for a delta `d` that is still an unevaluated product of the layer above, issued as ONE kernel with the
+    derivative in that product's epilogue; None when `d` is anything else.  `y` is the pinned full-size output of the layer
+    this delta belongs to, read at stride `y_stride` (the `scale` view between the two layers)."""
+    be = y.backend
+    conv = getattr(d, "_ungated_conv", None)
+    if conv is not None and _unevaluated(d):
+        return be.conv3x3_backward_data(conv["dz"], conv["w"], mode=conv["mode"], dz_stride=conv["dz_stride"], gate=y,
+                                        gate_mode=activation, gate_stride=y_stride)
+    flat = getattr(d, "_ungated_flat", None)                         # a contraction seen through a `reshape`
+    if flat is not None and y_stride == 1 and _unevaluated(flat["source"]) and _unevaluated(d):
+        spec = flat["spec"]
+        return T.matmul(spec["a"], spec["b"], transpose_a=spec["transpose_a"], transpose_b=spec["transpose_b"], mode=spec["mode"],
+                        gate=y, gate_mode=activation).reshape(list(d.shape))
+    return None
 
 
 def relu_mask(y):

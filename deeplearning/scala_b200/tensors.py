@@ -384,22 +384,32 @@ class Backend:
             return DeviceBuffer(self, hd, batch * h * wd * cout)
         return ProducedTensor(self, produce, [batch, h, wd, cout], x.padding)
 
-    def conv3x3_backward_data(self, dz: "Tensor", w: "Tensor", mode: Optional[str] = None, dz_stride: int = 1) -> "NonInlineTensor":
+    def conv3x3_backward_data(self, dz: "Tensor", w: "Tensor", mode: Optional[str] = None, dz_stride: int = 1,
+                              gate: Optional["Tensor"] = None, gate_mode: str = "none", gate_stride: int = 1) -> "NonInlineTensor":
         """dx[b,y,x,c] = sum dz[b, y+(ky-1), x+(kx-1), f] w[ky,kx,c,f].  `dz_stride` = s > 1: `dz` is the SAMPLED delta
         [batch, h/s, w/s, cout] that a down-sampling after the layer hands back; it stands for the full-size delta that is
-        zero everywhere except at (s*y, s*x), which is never materialised in fp32."""
+        zero everywhere except at (s*y, s*x), which is never materialised in fp32.
+        `gate` / `gate_mode` / `gate_stride`: the result is multiplied by the activation derivative of `gate`
+        [batch, h*gs, w*gs, cin] read at (gs*y, gs*x) in the same kernel -- the delta of the layer below."""
         batch, hs, ws, cout = dz.shape
         h, wd = hs * dz_stride, ws * dz_stride
         cin = w.shape[2]
+        gm = {"none": 0, "tanh": 1, "relu": 2}[gate_mode]
+        if gm and (gate is None or gate.size != batch * h * gate_stride * wd * gate_stride * cin):
+            raise ValueError("conv3x3_backward_data: gate must be [batch, h*gs, w*gs, cin]")
         opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=1, dz_stride=dz_stride)
 
         def produce():
             bd, bw = dz._buffer(), w._buffer()
+            bg = gate._buffer() if gm else None
             hd = C.c_void_p()
-            N.check(N.lib.dls_conv3x3_backward_data(self.ctx, bd.handle, bw.handle, batch, h, wd, cin, cout, C.byref(opts), None, 0,
-                                                    C.byref(hd), None))
+            N.check(N.lib.dls_conv3x3_backward_data_gated(self.ctx, bd.handle, bw.handle, bg.handle if bg else None, gm, gate_stride, batch,
+                                                          h, wd, cin, cout, C.byref(opts), None, 0, C.byref(hd), None))
             return DeviceBuffer(self, hd, batch * h * wd * cin)
-        return ProducedTensor(self, produce, [batch, h, wd, cin], dz.padding)
+        out = ProducedTensor(self, produce, [batch, h, wd, cin], dz.padding)
+        if not gm:                                    # a consumer may re-issue this pass with its activation derivative fused
+            out._ungated_conv = dict(dz=dz, w=w, mode=mode, dz_stride=dz_stride)
+        return out
 
     def conv3x3_backward_weights(self, x: "Tensor", dz: "Tensor", mode: Optional[str] = None, dz_stride: int = 1) -> "NonInlineTensor":
         """dw[ky,kx,c,f] = sum over b,y,x of x[b, y-(ky-1), x-(kx-1), c] dz[b,y,x,f]; `dz_stride` as in backward_data."""

@@ -240,6 +240,12 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
                         dls_event **done);
 int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
                               const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done);
+/* backward_data with the activation derivative of the layer BELOW in its epilogue (enum dls_gate, as dls_matmul_gated):
+ * out = dx * act'(gate[b, gs*y, gs*x, c]), gate = that layer's pinned output [batch, h*gs, w*gs, cin], gs = the factor of the
+ * `scale` down-sampling between the two layers (1: none) -- i.e. the (sampled) delta of the layer below in one kernel. */
+int dls_conv3x3_backward_data_gated(dls_ctx *ctx, dls_buf *dz, dls_buf *w, dls_buf *gate, int gate_mode, int gate_stride,
+                                    size_t batch, size_t h, size_t wd, size_t cin, size_t cout, const dls_conv_opts *opts,
+                                    dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done);
 int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin,
                                  size_t cout, const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
                                  dls_event **done);
