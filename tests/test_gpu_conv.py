@@ -235,3 +235,30 @@ def test_downsample_after_a_convolution_folds_into_the_layer(env, backend):
     assert np.abs(gw1 - gw2).max() <= 1e-5 * np.abs(gw2).max()
     assert np.abs((bias - b1) - (bias - b2)).max() <= 1e-5 * np.abs(bias - b2).max()
     assert np.abs(gw2).max() > 0
+
+
+@pytest.mark.parametrize("case", [(256, 16, 16, 32, 64, 2, 2), (6, 8, 8, 64, 128, 1, 2), (5, 16, 16, 32, 64, 2, 1), (3, 8, 8, 64, 32, 1, 1)],
+                         ids=["c3-conv2", "c3-conv3", "sampled-dz-dense-gate", "dense"])
+@pytest.mark.parametrize("gate_mode", ["relu", "tanh"])
+def test_backward_data_with_the_derivative_of_the_layer_below(env, backend, case, gate_mode):
+    """dls_conv3x3_backward_data_gated: dx * act'(y[b, gs*y, gs*x, c]) in the epilogue equals, bit for bit, the plain pass
+    followed by the elementwise tree on the `scale`d view of y."""
+    MO, O, B = env
+    mode, be = backend
+    batch, h, w, cin, cout, dzs, gs = case
+    if not be.conv3x3_supported("backward_data", h, w, cin, cout):
+        pytest.skip("no dedicated backward-data kernel for this shape in %s" % mode)
+    rng = np.random.RandomState(sum(case))
+    wt = (rng.standard_normal((3, 3, cin, cout)) * 0.2).astype(np.float32)
+    dz = rng.standard_normal((batch, h // dzs, w // dzs, cout)).astype(np.float32)
+    y = rng.standard_normal((batch, h * gs, w * gs, cin)).astype(np.float32)
+    y = np.maximum(y, 0) if gate_mode == "relu" else np.tanh(y)
+    dzt, wtt, yt = be.tensor(dz).do_cache(), be.tensor(wt).do_cache(), be.tensor(y).do_cache()
+    got = be.conv3x3_backward_data(dzt, wtt, dz_stride=dzs, gate=yt, gate_mode=gate_mode, gate_stride=gs).flat_array()
+    plain = be.conv3x3_backward_data(dzt, wtt, dz_stride=dzs).do_cache()
+    ys = yt.scale([batch, h, w, cin]) if gs > 1 else yt
+    if gate_mode == "tanh":
+        want = (plain * (1.0 - ys * ys)).flat_array()
+    else:
+        want = (plain * B.minimum(ys * 3.4028234663852886e38, be.scalar(1.0))).flat_array()
+    assert (got.view(np.uint32) == want.view(np.uint32)).all()
