@@ -27,9 +27,8 @@ class Exchange:
         from . import _native as N
         self.backend, self.rank, self.world_size = backend, rank, world_size
         self._N, self._C = N, C
-        # gradient buckets are a few MB at most: four channels move them at NVLink speed and leave the SMs to the
-        # backward kernels they overlap (measured at 8 GPUs: 1.08 -> 1.04 ms per C5 step)
-        os.environ.setdefault("NCCL_MAX_NCHANNELS", "4")
+        # the communicator is capped at DLS_EXCHANGE_CTAS (default 8) CTAs by dls_comm_init (ncclCommInitRankConfig): the
+        # gradient buckets are a few MB and travel under the rest of the backward pass, which keeps the other SMs
         N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
         self._pending, self._pending_bytes = [], 0
         self._held = []                         # small gradients waiting for the one-launch peer sum at `flush`
