@@ -247,16 +247,20 @@ __global__ void __launch_bounds__(kBlock) sum_axis_slab4_ticket_kernel(const flo
   const int lanes = kBlock / inner4;
   const int c4 = threadIdx.x % inner4, rl = threadIdx.x / inner4;
   const size_t r0 = (size_t)blockIdx.x * rows_per_block, r1 = min(k, r0 + rows_per_block);
-  float4 a[4];
+  // eight independent 128-bit loads in flight per thread and trip; rows past the slab are predicated off, so a slab of up to
+  // 8 x lanes rows is ONE round trip to memory whatever its exact height
+  auto fold8 = [&](const float4 *base, size_t first, size_t limit, size_t step, bool cg) {
+    float4 a[4];
 #pragma unroll
-  for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (rl < lanes) {
-    const float4 *p = reinterpret_cast<const float4 *>(in) + c4;
-    size_t r = r0 + rl;
-    for (; r + 7 * (size_t)lanes < r1; r += 8 * (size_t)lanes) {   // eight independent 128-bit loads in flight per thread
+    for (int u = 0; u < 4; ++u) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t r = first; r < limit; r += 8 * step) {
       float4 v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldcs(p + (r + (size_t)u * lanes) * inner4);
+      for (int u = 0; u < 8; ++u) {
+        const size_t row = r + (size_t)u * step;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < limit) v[u] = cg ? __ldcg(base + row * inner4) : __ldcs(base + row * inner4);
+      }
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         a[u & 3].x += v[u].x;
@@ -265,69 +269,37 @@ __global__ void __launch_bounds__(kBlock) sum_axis_slab4_ticket_kernel(const flo
         a[u & 3].w += v[u].w;
       }
     }
-    for (; r + 3 * (size_t)lanes < r1; r += 4 * (size_t)lanes) {
-      float4 v[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = __ldcs(p + (r + (size_t)u * lanes) * inner4);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        a[u].x += v[u].x;
-        a[u].y += v[u].y;
-        a[u].z += v[u].z;
-        a[u].w += v[u].w;
+    return make_float4((a[0].x + a[1].x) + (a[2].x + a[3].x), (a[0].y + a[1].y) + (a[2].y + a[3].y),
+                       (a[0].z + a[1].z) + (a[2].z + a[3].z), (a[0].w + a[1].w) + (a[2].w + a[3].w));
+  };
+  auto fold_lanes = [&](float4 mine, float *dst) {   // row-lanes of the block -> one row, in lane order
+    part[threadIdx.x] = mine;
+    __syncthreads();
+    if (rl == 0) {
+      float4 s = part[c4];
+      for (int l = 1; l < lanes; ++l) {
+        const float4 v = part[l * inner4 + c4];
+        s.x += v.x;
+        s.y += v.y;
+        s.z += v.z;
+        s.w += v.w;
       }
+      reinterpret_cast<float4 *>(dst)[c4] = s;
     }
-    for (; r < r1; r += lanes) {
-      const float4 v = __ldcs(p + r * inner4);
-      a[0].x += v.x;
-      a[0].y += v.y;
-      a[0].z += v.z;
-      a[0].w += v.w;
-    }
-  }
-  part[threadIdx.x] = make_float4((a[0].x + a[1].x) + (a[2].x + a[3].x), (a[0].y + a[1].y) + (a[2].y + a[3].y),
-                                  (a[0].z + a[1].z) + (a[2].z + a[3].z), (a[0].w + a[1].w) + (a[2].w + a[3].w));
-  __syncthreads();
-  if (rl == 0) {
-    float4 s = part[c4];
-    for (int l = 1; l < lanes; ++l) {
-      const float4 v = part[l * inner4 + c4];
-      s.x += v.x;
-      s.y += v.y;
-      s.z += v.z;
-      s.w += v.w;
-    }
-    reinterpret_cast<float4 *>(partial + (size_t)blockIdx.x * inner)[c4] = s;
-  }
+  };
+  float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rl < lanes) mine = fold8(reinterpret_cast<const float4 *>(in) + c4, r0 + rl, r1, (size_t)lanes, false);
+  fold_lanes(mine, partial + (size_t)blockIdx.x * inner);
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) is_last = atomicAdd(counter, 1u) == gridDim.x - 1;
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (rl < lanes) {
-    for (unsigned int b = rl; b < gridDim.x; b += lanes) {
-      const float4 v = __ldcg(reinterpret_cast<const float4 *>(partial + (size_t)b * inner) + c4);
-      t.x += v.x;
-      t.y += v.y;
-      t.z += v.z;
-      t.w += v.w;
-    }
-  }
-  part[threadIdx.x] = t;
+  mine = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (rl < lanes) mine = fold8(reinterpret_cast<const float4 *>(partial) + c4, (size_t)rl, (size_t)gridDim.x, (size_t)lanes, true);
   __syncthreads();
-  if (rl == 0) {
-    float4 s = part[c4];
-    for (int l = 1; l < lanes; ++l) {
-      const float4 v = part[l * inner4 + c4];
-      s.x += v.x;
-      s.y += v.y;
-      s.z += v.z;
-      s.w += v.w;
-    }
-    reinterpret_cast<float4 *>(out)[c4] = s;
-  }
+  fold_lanes(mine, out);
   if (threadIdx.x == 0) *counter = 0u;   // ready for the next launch on this stream
 }
 
@@ -343,8 +315,8 @@ int launch_sum_axis(dls_ctx *ctx, int stream, const float *in, size_t outer, siz
   if (outer == 1 && inner > 1 && k * std::min<size_t>(inner, 32) <= 16384 && inner <= 4096) {
     sum_axis_small_kernel<<<(unsigned)((inner + 31) / 32), kBlock, 0, st>>>(in, out, k, inner);
   } else if (outer == 1 && inner % 4 == 0 && inner <= kBlock && k >= 512 && ((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 15) == 0) {
-    // two blocks per SM: one trip of eight loads per thread covers a block's rows for the bias gradients of a step
-    size_t blocks = std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count * 2, (k + 63) / 64));
+    // one block per SM: the last block's fold over the per-block partials stays a couple of trips
+    size_t blocks = std::max<size_t>(1, std::min<size_t>((size_t)ctx->sm_count, (k + 63) / 64));
     const size_t rows_per_block = (k + blocks - 1) / blocks;
     blocks = (k + rows_per_block - 1) / rows_per_block;
     Block scratch;

@@ -500,15 +500,51 @@ inline int pad_channels(int mode, int c) {
 }
 inline size_t elem_bytes(int mode) { return mode == DLS_GEMM_TF32 ? 4 : 2; }
 
+// The operand copy of `buf` read as [batch, h, w, c] (sampled at `stride` / zero-filled by `up`) written by the kernel that
+// PRODUCED the buffer instead of by a staging pass: allocate it before the launch, attach it afterwards (finish_output drops
+// the shadows of a written buffer) under the tag staged_act will look for.
+long long act_tag_r(int mode, int up, int stride, int h, int w) {
+  return ((long long)mode << 60) | ((long long)up << 56) | ((long long)stride << 48) | ((long long)h << 24) | (long long)w;
+}
+long long act_tag_c(int batch, int c) { return ((long long)batch << 24) | (long long)c; }
+
+int alloc_emitted(dls_ctx *ctx, int stream, long long pixels, int c, Block *blk) {
+  return alloc_block(ctx, (size_t)pixels * c * 2, stream, blk);
+}
+void attach_emitted(dls_ctx *ctx, int stream, dls_buf *buf, int slot, Block &blk, long long tag_r, long long tag_c) {
+  if (!blk.ptr) return;
+  if (buf->shadow[slot].ptr) free_block(ctx, buf->shadow[slot]);
+  blk.stream_mask |= 1u << stream;
+  buf->shadow[slot] = blk;
+  buf->shadow_rows[slot] = tag_r;
+  buf->shadow_cols[slot] = tag_c;
+  blk = Block();
+}
+
 // Staged NHWC operand copy of `buf` read as [batch, h*stride, w*stride, c] and sampled at `stride` (shadow slot 2, kept
 // until the buffer is written again: the forward pass and the weight gradient share the copy of an activation, the
 // backward-data pass and the weight gradient share the copy of a delta).
 int staged_act(dls_ctx *ctx, int stream, int mode, dls_buf *buf, int batch, int h, int w, int c, int stride, int up, const void **ptr,
                int *cp, int slot = 2) {
   Block &sh = buf->shadow[slot];
-  const long long tag_r = ((long long)mode << 60) | ((long long)up << 56) | ((long long)stride << 48) | ((long long)h << 24) | (long long)w;
-  const long long tag_c = ((long long)batch << 24) | (long long)c;
+  const long long tag_r = act_tag_r(mode, up, stride, h, w);
+  const long long tag_c = act_tag_c(batch, c);
   const int p = pad_channels(mode, c);
+  {
+    // a dense bf16 copy of the whole buffer left by the kernel that produced it (DLS_GEMM_EMIT_OPERAND_COPY or a convolution
+    // epilogue, slot 0, [rows][cols] with cols % 8 == 0) is this operand when no channel padding and no resampling is needed
+    Block &flat = buf->shadow[0];
+    if (mode == DLS_GEMM_BF16 && stride == 1 && up == 1 && p == c && flat.ptr && flat.pool == ctx->capture_pool &&
+        buf->shadow_cols[0] > 0 && buf->shadow_cols[0] % 8 == 0 &&
+        buf->shadow_rows[0] * buf->shadow_cols[0] == (long long)batch * h * w * c) {
+      int rc = wait_streams(ctx, stream, flat.stream_mask);
+      if (rc) return rc;
+      flat.stream_mask |= 1u << stream;
+      *ptr = flat.ptr;
+      *cp = p;
+      return DLS_OK;
+    }
+  }
   if (!(sh.ptr && buf->shadow_rows[slot] == tag_r && buf->shadow_cols[slot] == tag_c && sh.pool == ctx->capture_pool)) {
     if (sh.ptr) free_block(ctx, sh);
     const long long pixels = (long long)batch * h * w;
@@ -603,6 +639,8 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
   dls_buf *o = nullptr;
   rc = new_buf(ctx, batch * h * wd * cout, stream, &o);
   if (rc) return rc;
+  Block emitted;
+  int emit_stride = 0;
   if (use_direct(cin, cout, wd)) {
     rc = launch_conv_direct_fwd(ctx, stream, mode, x->ptr, w->ptr, bias ? bias->ptr : nullptr, o->ptr, (int)batch, (int)h, (int)wd,
                                 (int)cin, (int)cout, act, stride);
@@ -615,12 +653,31 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
     epi.bias = bias ? bias->ptr : nullptr;
     epi.bias_mode = bias ? 2 : 0;
     epi.act = act;
-    if (!rc) rc = launch_conv_tc(ctx, stream, mode, xa, (int)batch, (int)h, (int)wd, cp, wf, (int)cout, o->ptr, +1, epi);
+    // opts->dz_stride (forward: "the value will be consumed sampled at this stride"): s = 1 leaves the dense bf16 copy of the
+    // result (slot 0: the next contraction or convolution starts without a staging pass), s > 1 the copy of the pixels
+    // (s*y, s*x) only -- the staged input of a convolution behind a `scale` down-sampling (slot 2)
+    const int os = opts ? opts->dz_stride : 0;
+    if (!rc && mode == DLS_GEMM_BF16 && os >= 1 && cout % 64 == 0 && h % os == 0 && wd % os == 0)
+      rc = alloc_emitted(ctx, stream, (long long)batch * (h / os) * (wd / os), (int)cout, &emitted);
+    if (!rc)
+      rc = launch_conv_tc(ctx, stream, mode, xa, (int)batch, (int)h, (int)wd, cp, wf, (int)cout, o->ptr, +1, epi, 1,
+                          os == 1 ? emitted.ptr : nullptr, os > 1 ? emitted.ptr : nullptr, nullptr, os > 1 ? os : 1);
+    emit_stride = os;
   }
   if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 3, done);
   if (rc) {
+    if (emitted.ptr) free_block(ctx, emitted);
     dls_buf_release(o);
     return rc;
+  }
+  if (emitted.ptr && emit_stride == 1) {
+    emitted.stream_mask |= 1u << stream;
+    o->shadow[0] = emitted;
+    o->shadow_rows[0] = (long long)(batch * h * wd);
+    o->shadow_cols[0] = (long long)cout;
+  } else if (emitted.ptr) {
+    attach_emitted(ctx, stream, o, 2, emitted, act_tag_r(mode, 1, emit_stride, (int)h / emit_stride, (int)wd / emit_stride),
+                   act_tag_c((int)batch, (int)cout));
   }
   *out = o;
   return DLS_OK;
@@ -659,11 +716,33 @@ int dls_conv3x3_backward_data_gated(dls_ctx *ctx, dls_buf *dz, dls_buf *w, dls_b
   GemmEpilogue epi;
   epi.gate = gate_mode ? gate->ptr : nullptr;
   epi.gate_mode = gate_mode;
-  if (!rc) rc = launch_conv_tc(ctx, stream, mode, da, (int)batch, (int)h, (int)wd, cp, wb, (int)cin, o->ptr, -1, epi, gate_stride);
+  // gated: the result IS the delta of the layer below, whose two backward passes consume it as a convolution operand --
+  // dense (gate_stride 1: one copy, slot 0) or sampled at gate_stride (compact copy for its weight gradient, slot 4, and the
+  // zero-filled full-size copy for its backward-data pass, slot 2), written by this epilogue instead of two staging passes
+  Block plain, upcopy;
+  const bool emit = mode == DLS_GEMM_BF16 && gate_mode && cin % 64 == 0;
+  if (!rc && emit) rc = alloc_emitted(ctx, stream, (long long)batch * h * wd, (int)cin, &plain);
+  if (!rc && emit && gate_stride > 1)
+    rc = alloc_emitted(ctx, stream, (long long)batch * h * gate_stride * wd * gate_stride, (int)cin, &upcopy);
+  if (!rc)
+    rc = launch_conv_tc(ctx, stream, mode, da, (int)batch, (int)h, (int)wd, cp, wb, (int)cin, o->ptr, -1, epi, gate_stride, plain.ptr,
+                        nullptr, upcopy.ptr, gate_stride);
   if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 3, done);
   if (rc) {
+    if (plain.ptr) free_block(ctx, plain);
+    if (upcopy.ptr) free_block(ctx, upcopy);
     dls_buf_release(o);
     return rc;
+  }
+  if (plain.ptr && gate_stride == 1) {
+    plain.stream_mask |= 1u << stream;
+    o->shadow[0] = plain;
+    o->shadow_rows[0] = (long long)(batch * h * wd);
+    o->shadow_cols[0] = (long long)cin;
+  } else if (plain.ptr) {
+    attach_emitted(ctx, stream, o, 4, plain, act_tag_r(mode, 1, 1, (int)h, (int)wd), act_tag_c((int)batch, (int)cin));
+    attach_emitted(ctx, stream, o, 2, upcopy, act_tag_r(mode, gate_stride, 1, (int)h * gate_stride, (int)wd * gate_stride),
+                   act_tag_c((int)batch, (int)cin));
   }
   *out = o;
   return DLS_OK;

@@ -470,9 +470,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
       tc.m0 += (w / n_tiles) * tiles_m * BM;                      // split-K: rows of this split's partial matrix
       const int row = tc.m0 + quarter * 32 + lane;
       long long gate_row = row;                                   // row of the gate tensor that belongs to output row `row`
-      if (CONV == 1 && cg.gate_stride > 1) {
+      long long down_row = -1, up_row = -1;                       // rows of the sampled / zero-filled operand copies
+      if (CONV == 1 && (cg.gate_stride > 1 || cg.copy_down || cg.copy_up)) {
         const int hw = cg.H * cg.W, b = row / hw, rem = row - b * hw, y = rem / cg.W, x = rem - y * cg.W;
         gate_row = ((long long)(b * cg.H + y) * cg.gate_stride * cg.W + x) * cg.gate_stride;
+        const int cs = cg.copy_s;
+        if (cg.copy_down && y % cs == 0 && x % cs == 0) down_row = ((long long)b * (cg.H / cs) + y / cs) * (cg.W / cs) + x / cs;
+        if (cg.copy_up) up_row = ((long long)(b * cg.H + y) * cs * cg.W + x) * cs;
       }
 #pragma unroll 1
       for (int c = 0; c < bn / EPI_CHUNK; ++c) {
@@ -485,6 +489,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
         epi_apply(v, f, bias_mode, act, row_bias, bias, col0, N);
         if (gate_mode && row < M) epi_gate(f, gate + gate_row * N + col0, N - col0, gate_mode, (N & 3) == 0, gate_scale);
         if (copy && row < M) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(copy) + (long long)row * copy_ld + col0, copy_ld - col0);
+        if (CONV == 1 && row < M) {
+          if (cg.copy_plain) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(cg.copy_plain) + (long long)row * N + col0, N - col0);
+          if (down_row >= 0) epi_copy_bf16(f, reinterpret_cast<__nv_bfloat16 *>(cg.copy_down) + down_row * N + col0, N - col0);
+          if (cg.copy_up) {
+            __nv_bfloat16 *u0 = reinterpret_cast<__nv_bfloat16 *>(cg.copy_up) + up_row * N + col0;
+            epi_copy_bf16(f, u0, N - col0);
+            float z[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) z[j] = 0.f;
+            for (int dy = 0; dy < cg.copy_s; ++dy)
+              for (int dx = 0; dx < cg.copy_s; ++dx)
+                if (dy | dx) epi_copy_bf16(z, u0 + ((long long)dy * cg.W * cg.copy_s + dx) * N, N - col0);
+          }
+        }
         if (direct_store) {
           if (row < c_rows) {
             float *dst = C + (long long)row * ldc + col0;
@@ -1202,7 +1220,8 @@ bool conv_tc_supported(int kind, int H, int W, int k_channels, int n) {
 }
 
 int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batch, int H, int W, int kp, const void *wts, int N,
-                   float *C, int tap_sign, const GemmEpilogue &epi, int gate_stride) {
+                   float *C, int tap_sign, const GemmEpilogue &epi, int gate_stride, void *copy_plain, void *copy_down, void *copy_up,
+                   int copy_s) {
   using namespace tc;
   DLS_CHECK(conv_tc_supported(kind, H, W, kp, N), DLS_ERR_UNSUPPORTED, "launch_conv_tc: shape not supported by the implicit-GEMM kernel");
   const bool tf32 = kind == DLS_GEMM_TF32;
@@ -1212,6 +1231,10 @@ int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batc
   cg.kc_per_tap = kp / block_k;
   cg.tap_sign = tap_sign;
   cg.gate_stride = gate_stride;
+  cg.copy_plain = copy_plain;
+  cg.copy_down = copy_down;
+  cg.copy_up = copy_up;
+  cg.copy_s = copy_s;
   cg.n_mma = (N + 15) & ~15;
   cg.b_bytes = cg.n_mma * 128;
   const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;

@@ -34,6 +34,12 @@ struct ConvGeom {
   int cblks = 0;                  // CONV 2: 64-channel blocks per tap
   int gate_stride = 1;            // CONV 1: the epilogue gate is [images, H*gs, W*gs, N] read at (gs*y, gs*x) (a layer's pinned
                                   // full-size output under the `scale` view that feeds this convolution)
+  // CONV 1 epilogue: bf16 operand copies of the result for the convolution that consumes it next (no staging pass there).
+  //   copy_plain: [images, H, W, ld] as is;  copy_down (s = copy_s): only pixels (s*y', s*x') -> [images, H/s, W/s, ld] (the
+  //   input of a layer behind a `scale` down-sampling);  copy_up (s = copy_s): [images, H*s, W*s, ld] with the result at
+  //   (s*y, s*x) and zeros elsewhere (a sampled delta as backward-data reads it).  ld = N (no channel padding).
+  void *copy_plain = nullptr, *copy_down = nullptr, *copy_up = nullptr;
+  int copy_s = 1;
   int px_stride = 1;              // CONV 2: the k pixels are every px_stride-th pixel of the activation (a sampled delta)
 };
 
@@ -45,7 +51,8 @@ struct ConvGeom {
 bool conv_tc_supported(int kind, int H, int W, int k_channels, int n);
 bool conv_tiling(int H, int W, int pixels, ConvGeom *g);
 int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batch, int H, int W, int kp, const void *wts, int N,
-                   float *C, int tap_sign, const GemmEpilogue &epi, int gate_stride = 1);
+                   float *C, int tap_sign, const GemmEpilogue &epi, int gate_stride = 1, void *copy_plain = nullptr,
+                   void *copy_down = nullptr, void *copy_up = nullptr, int copy_s = 1);
 
 // Weight gradient dw[9*cin, cout] fp32 (= [3,3,cin,cout]) = sum over pixels of act[p - tap][c] * dz[p][f]: contraction over the
 // pixels, both operands read MN-major from their staged NHWC copies (act [batch][H][W][cxp], dz [batch*H*W][cdp]; bf16 only,

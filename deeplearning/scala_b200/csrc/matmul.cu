@@ -150,7 +150,10 @@ int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long ro
   const long long tag_rows = transposed ? -rows : rows;
   // a staged copy made outside the capture that is open now (or inside one that has ended) holds data the graph being
   // recorded will not reproduce on replay: only copies staged in the current arena count as fresh
-  if (!(sh.ptr && tag_r == tag_rows && tag_c == cols && sh.pool == ctx->capture_pool)) {
+  // a dense bf16 copy (pitch == cols, cols % 8 == 0) is the same memory under every [rows, cols] reading of the buffer
+  const bool same_flat = mode == DLS_GEMM_BF16 && sh.ptr && tag_c > 0 && tag_c % 8 == 0 && cols % 8 == 0 && tag_r > 0 &&
+                         tag_r * tag_c == rows * cols;
+  if (!(sh.ptr && ((tag_r == tag_rows && tag_c == cols) || same_flat) && sh.pool == ctx->capture_pool)) {
     if (sh.ptr) free_block(ctx, sh);
     int rc;
     if (mode == DLS_GEMM_BF16) {

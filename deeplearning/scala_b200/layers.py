@@ -384,7 +384,7 @@ class Layers:
                 return lazy["wmat"]
 
             if be.conv3x3_supported("forward", h, wd, cin, cout):
-                y = be.conv3x3_forward(X, W, bias_t, activation)
+                y = be.conv3x3_forward(X, W, bias_t, activation, out_stride=s)
             else:
                 y = T.matmul(col(), wmat(), bias=bias_t, bias_mode="col" if bias is not None else "none",
                              activation=activation).reshape(full)
@@ -470,7 +470,7 @@ def fuse_activation_derivative(d, y, activation: str, y_stride: int):
     if flat is not None and y_stride == 1 and _unevaluated(flat["source"]) and _unevaluated(d):
         spec = flat["spec"]
         return T.matmul(spec["a"], spec["b"], transpose_a=spec["transpose_a"], transpose_b=spec["transpose_b"], mode=spec["mode"],
-                        gate=y, gate_mode=activation).reshape(list(d.shape))
+                        gate=y, gate_mode=activation, emit_operand_copy=True).reshape(list(d.shape))
     return None
 
 

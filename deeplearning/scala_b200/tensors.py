@@ -368,12 +368,14 @@ class Backend:
         return x, 1
 
     def conv3x3_forward(self, x: "Tensor", w: "Tensor", bias: Optional["Tensor"] = None, activation: str = "none",
-                        mode: Optional[str] = None) -> "NonInlineTensor":
+                        mode: Optional[str] = None, out_stride: int = 0) -> "NonInlineTensor":
         """out[b,y,x,f] = act(bias[f] + sum x[b, y-(ky-1), x-(kx-1), c] w[ky,kx,c,f]) for NHWC `x` and `w` [3,3,Cin,Cout]."""
         batch, h, wd, cin = x.shape
         cout = w.shape[3]
         src, stride = self._sampled_source(x)
-        opts = N.ConvOpts(mode=self._MODES[mode], activation={"none": 0, "tanh": 1, "relu": 2}[activation], in_stride=stride, dz_stride=0)
+        # out_stride: the value is consumed next by a contraction / convolution (1) or through a `scale` down-sampling by s
+        opts = N.ConvOpts(mode=self._MODES[mode], activation={"none": 0, "tanh": 1, "relu": 2}[activation], in_stride=stride,
+                          dz_stride=out_stride)
 
         def produce():
             bx, bw = src._buffer(), w._buffer()

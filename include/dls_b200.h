@@ -231,8 +231,11 @@ typedef struct dls_conv_opts {
   int32_t mode;        /* enum dls_gemm_mode, or -1 = context default */
   int32_t activation;  /* enum dls_activation (forward only)          */
   int32_t in_stride;   /* 0 / 1 = dense input; s > 1 = input sampled at stride s (forward, backward_weights) */
-  int32_t dz_stride;   /* 0 / 1 = dense delta; s > 1 (backward passes) = dz is [batch, h/s, w/s, cout] and stands for a full-size
-                          delta that is zero except at (s*y, s*x): what a `scale` down-sampling after the layer hands back */
+  int32_t dz_stride;   /* backward passes: 0 / 1 = dense delta; s > 1 = dz is [batch, h/s, w/s, cout] and stands for a full-size
+                          delta that is zero except at (s*y, s*x): what a `scale` down-sampling after the layer hands back.
+                          forward: 0 = nothing; s >= 1 = a hint that the value is consumed next by a contraction (s = 1) or by
+                          a convolution behind a `scale` down-sampling by s: the kernel also leaves that consumer's bf16
+                          operand copy (BF16 mode, cout % 64 == 0), so it starts without a staging pass */
 } dls_conv_opts;
 int dls_conv3x3_supported(dls_ctx *ctx, int pass, size_t h, size_t w, size_t cin, size_t cout, int mode);
 int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, size_t batch, size_t h, size_t wd, size_t cin,
