@@ -172,10 +172,7 @@ __device__ __forceinline__ void direct_fill_patch(float *sx, const float *__rest
 template <int CIN, int MODE>
 __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_fwd_kernel(const float *__restrict__ x, const float *__restrict__ w,
                                                                             const float *__restrict__ bias, float *__restrict__ out,
-                                                                            int B, int H, int W, int Cout, int act, int R, int stride,
-                                                                            __nv_bfloat16 *__restrict__ down, int ds, int dcp) {
-  // down != nullptr: the pixels (ds*y', ds*x') are also written as bf16 [B, H/ds, W/ds, dcp] (channels >= Cout zero): the
-  // staged input of the convolution behind the `scale` down-sampling that follows this layer
+                                                                            int B, int H, int W, int Cout, int act, int R, int stride) {
   extern __shared__ float sx[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
@@ -248,20 +245,6 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_fwd_kernel(cons
           v[j] = __fadd_rn(acc[nt][j], bv[nt][j & 1]);
           if (act == 1) v[j] = tanhf(v[j]);
           else if (act == 2) v[j] = fmaxf(v[j], 0.f);
-        }
-        if (down) {
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int p = h ? p1 : p0, yy = h ? yy1 : yy0, xx = h ? xx1 : xx0;
-            const int gy = y0 + yy;
-            if (p < npx && gy % ds == 0 && xx % ds == 0) {
-              __nv_bfloat16 *drow = down + (((long long)b * (H / ds) + gy / ds) * (W / ds) + xx / ds) * dcp;
-              for (int c0 = n; c0 < dcp; c0 += 32) {   // this lane's two channels of every 32-channel group (pad groups: zero)
-                const float a = c0 < Cout ? v[2 * h] : 0.f, bb = c0 + 1 < Cout ? v[2 * h + 1] : 0.f;
-                *reinterpret_cast<__nv_bfloat162 *>(drow + c0) = __floats2bfloat162_rn(a, bb);
-              }
-            }
-          }
         }
         if ((Cout & 1) == 0) {
           if (p0 < npx && n < Cout) *reinterpret_cast<float2 *>(o0 + n) = make_float2(v[0], v[1]);
@@ -422,16 +405,16 @@ bool conv_direct_supported(int cin, int cout) { return cin >= 1 && cin <= 4 && c
 
 template <int MODE>
 static int launch_direct_fwd_mode(dls_ctx *ctx, cudaStream_t st, const float *x, const float *w, const float *bias, float *out, int B,
-                                  int H, int W, int cin, int cout, int act, int stride, void *down, int ds, int dcp) {
+                                  int H, int W, int cin, int cout, int act, int stride) {
   const int R = direct_rows(H, W, 1, B, ctx->sm_count);
   const size_t smem = (size_t)(R + 2) * (W + 2) * 4 * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
   const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 4);
   switch (cin) {
-    case 1: conv_direct_fwd_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride, (__nv_bfloat16 *)down, ds, dcp); break;
-    case 2: conv_direct_fwd_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride, (__nv_bfloat16 *)down, ds, dcp); break;
-    case 3: conv_direct_fwd_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride, (__nv_bfloat16 *)down, ds, dcp); break;
-    default: conv_direct_fwd_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride, (__nv_bfloat16 *)down, ds, dcp); break;
+    case 1: conv_direct_fwd_kernel<1, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
+    case 2: conv_direct_fwd_kernel<2, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
+    case 3: conv_direct_fwd_kernel<3, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
+    default: conv_direct_fwd_kernel<4, MODE><<<grid, kDirectWarps * 32, smem, st>>>(x, w, bias, out, B, H, W, cout, act, R, stride); break;
   }
   DLS_CUDA(cudaGetLastError());
   ctx->stats.kernel_launches++;
@@ -439,11 +422,11 @@ static int launch_direct_fwd_mode(dls_ctx *ctx, cudaStream_t st, const float *x,
 }
 
 int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, const float *w, const float *bias, float *out, int B,
-                           int H, int W, int cin, int cout, int act, int stride, void *down, int ds, int dcp) {
+                           int H, int W, int cin, int cout, int act, int stride) {
   cudaStream_t st = ctx->streams[stream];
-  if (mode == DLS_GEMM_TF32) return launch_direct_fwd_mode<DLS_GEMM_TF32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride, down, ds, dcp);
-  if (mode == DLS_GEMM_BF16) return launch_direct_fwd_mode<DLS_GEMM_BF16>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride, down, ds, dcp);
-  return launch_direct_fwd_mode<DLS_GEMM_FP32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride, down, ds, dcp);
+  if (mode == DLS_GEMM_TF32) return launch_direct_fwd_mode<DLS_GEMM_TF32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride);
+  if (mode == DLS_GEMM_BF16) return launch_direct_fwd_mode<DLS_GEMM_BF16>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride);
+  return launch_direct_fwd_mode<DLS_GEMM_FP32>(ctx, st, x, w, bias, out, B, H, W, cin, cout, act, stride);
 }
 
 template <int MODE>
@@ -659,17 +642,8 @@ int dls_conv3x3_forward(dls_ctx *ctx, dls_buf *x, dls_buf *w, dls_buf *bias, siz
   Block emitted;
   int emit_stride = 0;
   if (use_direct(cin, cout, wd)) {
-    // the first layer's kernel writes the sampled bf16 input of the next convolution itself (channels padded to that
-    // layer's k block), when the caller says a down-sampling by os follows (opts->dz_stride, see below)
-    const int os = opts ? opts->dz_stride : 0;
-    const int dcp = pad_channels(mode, (int)cout);
-    if (mode == DLS_GEMM_BF16 && os > 1 && cout % 2 == 0 && h % os == 0 && wd % os == 0) {
-      rc = alloc_emitted(ctx, stream, (long long)batch * (h / os) * (wd / os), dcp, &emitted);
-      emit_stride = os;
-    }
-    if (!rc)
-      rc = launch_conv_direct_fwd(ctx, stream, mode, x->ptr, w->ptr, bias ? bias->ptr : nullptr, o->ptr, (int)batch, (int)h, (int)wd,
-                                  (int)cin, (int)cout, act, stride, emitted.ptr, os > 1 ? os : 1, dcp);
+    rc = launch_conv_direct_fwd(ctx, stream, mode, x->ptr, w->ptr, bias ? bias->ptr : nullptr, o->ptr, (int)batch, (int)h, (int)wd,
+                                (int)cin, (int)cout, act, stride);
   } else {
     const void *xa, *wf, *wb;
     int cp;

@@ -66,7 +66,7 @@ int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int c
 // conv.cu
 bool conv_direct_supported(int cin, int cout);
 int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, const float *w, const float *bias, float *out, int B,
-                           int H, int W, int cin, int cout, int act, int stride, void *down = nullptr, int ds = 1, int dcp = 0);
+                           int H, int W, int cin, int cout, int act, int stride);
 int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
                           int cout, int stride, int dzs);
 int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
