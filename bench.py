@@ -286,10 +286,14 @@ def gemm_probe(be, peaks, reps=10):
                 if mode == "bf16":
                     rec["frac"] = tf / peaks["bf16"]
                     rec["peak"] = peaks["bf16"]
-                out["gemm_tc_kernel %s %dx%dx%d" % (mode, m, n, k)] = rec
+                else:                                        # cuBLAS TF32 8192^3 on this pool, builder-measured
+                    rec["frac"] = tf / 733.9                 # (tools/tf32_peak_probe.py, profiles/r2_cublas_peaks.jsonl)
+                    rec["peak"] = 733.9
+                    rec["peak_source"] = "builder-measured cuBLAS tf32 burst (MEASURED_PEAKS.json has no tf32 entry)"
+                out["gemm2_tc_kernel (CTA pair) %s %dx%dx%d" % (mode, m, n, k)] = rec
                 del keep
             except Exception as exc:                         # noqa: BLE001
-                out["gemm_tc_kernel %s %dx%dx%d" % (mode, m, n, k)] = {"error": repr(exc)}
+                out["gemm2_tc_kernel (CTA pair) %s %dx%dx%d" % (mode, m, n, k)] = {"error": repr(exc)}
         del a, b
     return out
 
