@@ -53,6 +53,7 @@ struct PeerArgs {
   uint32_t stage_floats;
   int n_seg, rank, world;
   float lr;
+  int split_local;                  // 1: CTAs kPeerGrid .. 2 * kPeerGrid - 1 do phase 2, the first kPeerGrid skip it
 };
 
 struct PeerState {
@@ -116,10 +117,17 @@ __device__ __forceinline__ float4 sgd4(float4 w, float4 s, float lr) {   // data
 }
 
 __global__ void __launch_bounds__(kPeerBlock) peer_step_kernel(const __grid_constant__ PeerArgs A) {
-  const uint32_t b = blockIdx.x, tid = threadIdx.x;
+  // A launch with exchanged segments runs 2 * kPeerGrid CTAs: the first kPeerGrid run the exchange (phases 1, 3, 4), the
+  // other kPeerGrid only the updates that need no exchange (phase 2) -- the large weight whose gradient NCCL already summed is
+  // 25 MB of traffic, and a CTA that did its share of it before looking at its flags put ~6 us in front of the exchange's
+  // own latency chain.  Without exchanged segments (single GPU) kPeerGrid CTAs do phase 2 and nothing else.
+  const bool does_local = blockIdx.x >= kPeerGrid || A.split_local == 0;
+  const bool does_exchange = blockIdx.x < kPeerGrid;
+  const uint32_t b = blockIdx.x % kPeerGrid, tid = threadIdx.x;
+
   // does this CTA own a chunk of an exchanged segment?  (uniform over the CTA, identical on every rank)
   bool mine = false;
-  for (int s = 0; s < A.n_seg; ++s) {
+  for (int s = 0; does_exchange && s < A.n_seg; ++s) {
     const PeerSeg &S = A.seg[s];
     if (!S.exchange) continue;
     const uint32_t chunks = (S.n + kPeerChunk - 1) / kPeerChunk;
@@ -148,7 +156,7 @@ __global__ void __launch_bounds__(kPeerBlock) peer_step_kernel(const __grid_cons
   }
 
   // phase 2: updates that need no exchange
-  for (int s = 0; s < A.n_seg; ++s) {
+  for (int s = 0; does_local && s < A.n_seg; ++s) {
     const PeerSeg &S = A.seg[s];
     if (S.exchange || !S.w) continue;
     const uint32_t chunks = (S.n + kPeerChunk - 1) / kPeerChunk;
@@ -185,7 +193,7 @@ __global__ void __launch_bounds__(kPeerBlock) peer_step_kernel(const __grid_cons
         *A.error = 1 + (int)tid;
         break;
       }
-      __nanosleep(64);
+      __nanosleep(20);
     }
   }
   __syncthreads();
@@ -372,7 +380,13 @@ int dls_peer_sgd_step(dls_ctx *ctx, dls_buf *const *weights, dls_buf *const *gra
   }
   auto launch = [&]() -> int {
     if (A.n_seg == 0) return DLS_OK;
-    peer_step_kernel<<<kPeerGrid, kPeerBlock, 0, ctx->streams[0]>>>(A);
+    bool any_ex = false, any_local = false;
+    for (int i = 0; i < A.n_seg; ++i) {
+      any_ex |= A.seg[i].exchange != 0;
+      any_local |= A.seg[i].exchange == 0 && A.seg[i].w != nullptr;
+    }
+    A.split_local = any_ex && any_local ? 1 : 0;
+    peer_step_kernel<<<A.split_local ? 2 * kPeerGrid : kPeerGrid, kPeerBlock, 0, ctx->streams[0]>>>(A);
     DLS_CUDA(cudaGetLastError());
     ctx->stats.kernel_launches++;
     A.n_seg = 0;
