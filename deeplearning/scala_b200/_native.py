@@ -110,6 +110,8 @@ _SIG = {
                                                   C.c_size_t, C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
     "dls_conv3x3_backward_weights": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                                C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP]),
+    "dls_conv3x3_backward_weights_bias": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                                    C.POINTER(ConvOpts), _PP, C.c_int, _PP, _PP, _PP]),
     "dls_comm_unique_id": (C.c_int, [C.c_char_p]),
     "dls_comm_init": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_int]),
     "dls_allreduce_sum": (C.c_int, [_P, _P, C.c_size_t, _PP, C.c_int, _PP]),

@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(256) conv_pack_weights_kernel(const float *__r
 // is issue bound at 8x its HBM time; as 16-pixel x 32-channel x 40-tap MMA tiles it needs ~6 instructions per pixel.
 // k index of the implicit im2col row: k = tap * 4 + c (c = 3 and taps 9.. are zero).
 constexpr int kDirectWarps = 8;
-constexpr int kDirectK = 40;                  // 9 taps x 4 padded channels, rounded up to 5 k-steps of 8
+constexpr int kDirectK = 40;
+constexpr int kSlabRows = 37;                // 36 im2col rows of the weight gradient + one row for the bias gradient                  // 9 taps x 4 padded channels, rounded up to 5 k-steps of 8
 
 __device__ __forceinline__ void mma_tf32_16x8x8(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
   asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
@@ -275,6 +276,7 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const
   const int g = lane >> 2, t = lane & 3;
   const int prow = (W + 2) * 4;
   float acc[3][4][4];
+  float db[4] = {0.f, 0.f, 0.f, 0.f};         // sum of the (unrounded) delta over this lane's pixels, channel 8 nt + g
 #pragma unroll
   for (int mt = 0; mt < 3; ++mt)
 #pragma unroll
@@ -322,6 +324,7 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const
             const int n = nt * 8 + g;
             float v = 0.f;
             if (ok[u][h] && n < Cout) v = __ldg(dzb + (long long)pq[u][h] * Cout + n);
+            db[nt] += v;
             bf[u][nt][h] = __float_as_uint(v);
           }
       }
@@ -361,30 +364,47 @@ __global__ void __launch_bounds__(kDirectWarps * 32) conv_direct_dw_kernel(const
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int m = mt * 16 + g + 8 * (j >> 1), f = nt * 8 + 2 * t + (j & 1);
-        if (m < 36) red[(warp * 36 + m) * 32 + f] = acc[mt][nt][j];
+        if (m < 36) red[(warp * kSlabRows + m) * 32 + f] = acc[mt][nt][j];
       }
+  // bias gradient: fold the four lanes (t) that share a channel, lane t == 0 holds the warp's sum for channel 8 nt + g
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    float v = db[nt];
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    if (t == 0) red[(warp * kSlabRows + 36) * 32 + nt * 8 + g] = v;
+  }
   __syncthreads();
-  for (int i = threadIdx.x; i < 36 * 32; i += blockDim.x) {
+  for (int i = threadIdx.x; i < kSlabRows * 32; i += blockDim.x) {
     float s = red[i];
-    for (int wv = 1; wv < kDirectWarps; ++wv) s = __fadd_rn(s, red[wv * 36 * 32 + i]);
-    partial[(long long)blockIdx.x * 36 * 32 + i] = s;
+    for (int wv = 1; wv < kDirectWarps; ++wv) s = __fadd_rn(s, red[wv * kSlabRows * 32 + i]);
+    partial[(long long)blockIdx.x * kSlabRows * 32 + i] = s;
   }
 }
 
 // dw[(tap * cin + c) * cout + f] = sum over slabs of partial[slab][tap * 4 + c][f]: one warp per output, the lanes take
 // every 32nd slab and are folded by a fixed shuffle tree (deterministic for a given grid).
-__global__ void __launch_bounds__(256) conv_direct_dw_reduce_kernel(const float *__restrict__ partial, float *__restrict__ dw, int slabs,
-                                                                    int cin, int cout) {
+__global__ void __launch_bounds__(256) conv_direct_dw_reduce_kernel(const float *__restrict__ partial, float *__restrict__ dw,
+                                                                    float *__restrict__ dbias, int slabs, int cin, int cout) {
   const int lane = threadIdx.x & 31;
   const int o = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (o >= 9 * cin * cout) return;
-  const int f = o % cout, c = (o / cout) % cin, tap = o / (cout * cin);
-  const float *src = partial + (tap * 4 + c) * 32 + f;
+  const int n_dw = 9 * cin * cout;
+  if (o >= n_dw + (dbias ? cout : 0)) return;
+  const float *src;
+  if (o < n_dw) {
+    const int f = o % cout, c = (o / cout) % cin, tap = o / (cout * cin);
+    src = partial + (tap * 4 + c) * 32 + f;
+  } else {
+    src = partial + 36 * 32 + (o - n_dw);            // row 36 of every slab: the bias gradient
+  }
   float s = 0.f;
-  for (int sl = lane; sl < slabs; sl += 32) s = __fadd_rn(s, __ldg(src + (long long)sl * 36 * 32));
+  for (int sl = lane; sl < slabs; sl += 32) s = __fadd_rn(s, __ldg(src + (long long)sl * kSlabRows * 32));
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) s = __fadd_rn(s, __shfl_down_sync(0xffffffffu, s, d));
-  if (lane == 0) dw[o] = s;
+  if (lane == 0) {
+    if (o < n_dw) dw[o] = s;
+    else dbias[o - n_dw] = s;
+  }
 }
 
 int direct_rows(int H, int W, int dzs, int B, int sm_count) {
@@ -430,16 +450,16 @@ int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, c
 }
 
 template <int MODE>
-static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                                 int cout, int stride, int dzs) {
+static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const float *dz, float *dw, float *dbias, int B, int H, int W,
+                                 int cin, int cout, int stride, int dzs) {
   cudaStream_t st = ctx->streams[stream];
   const int R = direct_rows(H, W, dzs, B, ctx->sm_count);
-  const size_t patch = (size_t)(R + 2) * (W + 2) * 4, red = (size_t)kDirectWarps * 36 * 32;
+  const size_t patch = (size_t)(R + 2) * (W + 2) * 4, red = (size_t)kDirectWarps * kSlabRows * 32;
   const size_t smem = std::max(patch, red) * sizeof(float);
   const long long bands = (long long)B * ((H + R - 1) / R);
   const int grid = (int)std::min<long long>(bands, (long long)ctx->sm_count * 2);
   Block scratch;
-  int rc = alloc_block(ctx, (size_t)grid * 36 * 32 * sizeof(float), stream, &scratch);
+  int rc = alloc_block(ctx, (size_t)grid * kSlabRows * 32 * sizeof(float), stream, &scratch);
   if (rc) return rc;
   float *partial = (float *)scratch.ptr;
   switch (cin) {
@@ -450,7 +470,7 @@ static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const
   }
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) {
-    conv_direct_dw_reduce_kernel<<<(9 * cin * cout * 32 + 255) / 256, 256, 0, st>>>(partial, dw, grid, cin, cout);
+    conv_direct_dw_reduce_kernel<<<((9 * cin + 1) * cout * 32 + 255) / 256, 256, 0, st>>>(partial, dw, dbias, grid, cin, cout);
     e = cudaGetLastError();
   }
   ctx->stats.kernel_launches += 2;
@@ -460,10 +480,10 @@ static int launch_direct_dw_mode(dls_ctx *ctx, int stream, const float *x, const
 }
 
 int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                          int cout, int stride, int dzs) {
-  if (mode == DLS_GEMM_TF32) return launch_direct_dw_mode<DLS_GEMM_TF32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride, dzs);
-  if (mode == DLS_GEMM_BF16) return launch_direct_dw_mode<DLS_GEMM_BF16>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride, dzs);
-  return launch_direct_dw_mode<DLS_GEMM_FP32>(ctx, stream, x, dz, dw, B, H, W, cin, cout, stride, dzs);
+                          int cout, int stride, int dzs, float *dbias) {
+  if (mode == DLS_GEMM_TF32) return launch_direct_dw_mode<DLS_GEMM_TF32>(ctx, stream, x, dz, dw, dbias, B, H, W, cin, cout, stride, dzs);
+  if (mode == DLS_GEMM_BF16) return launch_direct_dw_mode<DLS_GEMM_BF16>(ctx, stream, x, dz, dw, dbias, B, H, W, cin, cout, stride, dzs);
+  return launch_direct_dw_mode<DLS_GEMM_FP32>(ctx, stream, x, dz, dw, dbias, B, H, W, cin, cout, stride, dzs);
 }
 
 int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
@@ -753,9 +773,12 @@ int dls_conv3x3_backward_data(dls_ctx *ctx, dls_buf *dz, dls_buf *w, size_t batc
   return dls_conv3x3_backward_data_gated(ctx, dz, w, nullptr, 0, 1, batch, h, wd, cin, cout, opts, deps, n_deps, out, done);
 }
 
-int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
-                                 const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done) {
+int dls_conv3x3_backward_weights_bias(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
+                                      const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
+                                      dls_buf **out_bias, dls_event **done) {
   DLS_CHECK(ctx && x && dz && out, DLS_ERR_INVALID, "dls_conv3x3_backward_weights: NULL argument");
+  DLS_CHECK(!out_bias || use_direct(cin, cout, wd), DLS_ERR_UNSUPPORTED,
+            "dls_conv3x3_backward_weights_bias: only the first-layer kernel (Cin <= 4) sums the bias gradient on the way");
   const int stride = (opts && opts->in_stride > 1) ? opts->in_stride : 1;
   DLS_CHECK(fits_int(batch) && fits_int(h) && fits_int(wd) && fits_int(cin) && fits_int(cout), DLS_ERR_INVALID,
             "dls_conv3x3_backward_weights: bad shape");
@@ -772,11 +795,16 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
   dls_buf *ins[2] = {x, dz};
   int rc = wait_inputs(ctx, stream, ins, 2, deps, n_deps);
   if (rc) return rc;
-  dls_buf *o = nullptr;
+  dls_buf *o = nullptr, *ob = nullptr;
   rc = new_buf(ctx, 9 * cin * cout, stream, &o);
-  if (rc) return rc;
+  if (!rc && out_bias) rc = new_buf(ctx, cout, stream, &ob);
+  if (rc) {
+    if (o) dls_buf_release(o);
+    return rc;
+  }
   if (use_direct(cin, cout, wd)) {
-    rc = launch_conv_direct_dw(ctx, stream, mode, x->ptr, dz->ptr, o->ptr, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, stride, dzs);
+    rc = launch_conv_direct_dw(ctx, stream, mode, x->ptr, dz->ptr, o->ptr, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, stride, dzs,
+                               ob ? ob->ptr : nullptr);
   } else {
     const void *xa, *da;
     int cxp, cdp;
@@ -791,13 +819,21 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
     if (!rc) rc = launch_conv_dw_tc(ctx, stream, mode, xa, cxp, da, cdp, (int)batch, (int)h, (int)wd, (int)cin, (int)cout, o->ptr,
                                     compact ? dzs : 1);
   }
-  if (!rc) rc = finish_output(ctx, stream, &o, 1, ins, 2, done);
+  dls_buf *outs[2] = {o, ob};
+  if (!rc) rc = finish_output(ctx, stream, outs, ob ? 2 : 1, ins, 2, done);
   if (rc) {
     dls_buf_release(o);
+    if (ob) dls_buf_release(ob);
     return rc;
   }
   *out = o;
+  if (out_bias) *out_bias = ob;
   return DLS_OK;
+}
+
+int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin, size_t cout,
+                                 const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out, dls_event **done) {
+  return dls_conv3x3_backward_weights_bias(ctx, x, dz, batch, h, wd, cin, cout, opts, deps, n_deps, out, nullptr, done);
 }
 
 }  // extern "C"

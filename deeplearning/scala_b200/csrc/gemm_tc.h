@@ -68,7 +68,7 @@ bool conv_direct_supported(int cin, int cout);
 int launch_conv_direct_fwd(dls_ctx *ctx, int stream, int mode, const float *x, const float *w, const float *bias, float *out, int B,
                            int H, int W, int cin, int cout, int act, int stride);
 int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, const float *dz, float *dw, int B, int H, int W, int cin,
-                          int cout, int stride, int dzs);
+                          int cout, int stride, int dzs, float *dbias = nullptr);
 int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
                           int stride, int up);
 int launch_conv_pack_weights(dls_ctx *ctx, int stream, int mode, const float *w, void *wf, void *wb, int cin, int cout, int cinp,

@@ -431,7 +431,18 @@ class Layers:
                             acc = acc + p
                         return acc
 
+                    # first layer (Cin <= 4): one kernel pass over the delta gives the weight AND the bias gradient
+                    both_ok = bias is not None and cin <= 4 and cout <= 32 and wd <= 512 and \
+                        be.conv3x3_supported("backward_weights", h, wd, cin, cout)
+
+                    def dw_db(d):
+                        if "dw_db" not in memo:
+                            memo["dw_db"] = be.conv3x3_backward_weights_bias(X, dz_sampled(d), dz_stride=s)
+                        return memo["dw_db"]
+
                     def delta_w(d):
+                        if both_ok:
+                            return dw_db(d)[0]
                         if be.conv3x3_supported("backward_weights", h, wd, cin, cout):
                             return be.conv3x3_backward_weights(X, dz_sampled(d), dz_stride=s)
                         dw = T.matmul(col(), dz_of(d).reshape([m, cout]), transpose_a=True)     # [Cin*9, Cout]
@@ -439,7 +450,8 @@ class Layers:
 
                     # weights before the input, for the same reason as in `linear`
                     if bias is not None:                             # the zeros of a sampled delta add nothing
-                        tapes[2].backward(do_delta.map(lambda d: T.sum_axis(dz_sampled(d).reshape([m // (s * s), cout]), 0)))
+                        tapes[2].backward(do_delta.map(lambda d: dw_db(d)[1] if both_ok else
+                                                       T.sum_axis(dz_sampled(d).reshape([m // (s * s), cout]), 0)))
                     tw.backward(do_delta.map(delta_w))
                     tx.backward(do_delta.map(delta_x))
                 return run

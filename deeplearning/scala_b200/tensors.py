@@ -428,6 +428,27 @@ class Backend:
             return DeviceBuffer(self, hd, 9 * cin * cout)
         return ProducedTensor(self, produce, [3, 3, cin, cout], x.padding)
 
+    def conv3x3_backward_weights_bias(self, x: "Tensor", dz: "Tensor", mode: Optional[str] = None, dz_stride: int = 1):
+        """(dw, db) from ONE pass over dz: the first-layer kernel (Cin <= 4) sums the bias gradient on the way
+        (`dls_conv3x3_backward_weights_bias`); whichever of the two tensors is needed first runs the kernel."""
+        batch, h, wd, cin = x.shape
+        cout = dz.shape[3]
+        src, stride = self._sampled_source(x)
+        opts = N.ConvOpts(mode=self._MODES[mode], activation=0, in_stride=stride, dz_stride=dz_stride)
+        made = {}
+
+        def run():
+            if "dw" not in made:
+                bx, bd = src._buffer(), dz._buffer()
+                hd, hb = C.c_void_p(), C.c_void_p()
+                N.check(N.lib.dls_conv3x3_backward_weights_bias(self.ctx, bx.handle, bd.handle, batch, h, wd, cin, cout, C.byref(opts),
+                                                                None, 0, C.byref(hd), C.byref(hb), None))
+                made["dw"], made["db"] = DeviceBuffer(self, hd, 9 * cin * cout), DeviceBuffer(self, hb, cout)
+            return made
+        dw = ProducedTensor(self, lambda: run()["dw"], [3, 3, cin, cout], x.padding)
+        db = ProducedTensor(self, lambda: run()["db"], [cout], x.padding)
+        return dw, db
+
     def sum_axis(self, t: "Tensor", axis: int) -> "NonInlineTensor":
         """Sum away one dimension: what TensorLayers.sumAs spells as `split(axis).reduce(_ + _)` (TL:124-162), as one
         row / column reduction kernel (`dls_sum_axis`) instead of a host-unrolled chain of `shape[axis]` additions."""

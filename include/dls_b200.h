@@ -253,6 +253,12 @@ int dls_conv3x3_backward_weights(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t b
                                  size_t cout, const dls_conv_opts *opts, dls_event *const *deps, int n_deps, dls_buf **out,
                                  dls_event **done);
 
+/* backward_weights that also returns the bias gradient sum_{b,y,x} dz[b,y,x,f] (fp32 sums of the unrounded delta) from the same
+ * pass over dz.  First-layer kernels (Cin <= 4) only: DLS_ERR_UNSUPPORTED elsewhere (use dls_sum_axis). */
+int dls_conv3x3_backward_weights_bias(dls_ctx *ctx, dls_buf *x, dls_buf *dz, size_t batch, size_t h, size_t wd, size_t cin,
+                                      size_t cout, const dls_conv_opts *opts, dls_event *const *deps, int n_deps,
+                                      dls_buf **out, dls_buf **out_bias, dls_event **done);
+
 /* ---- data-parallel exchange (new functionality: the reference has no collective) */
 int dls_comm_unique_id(uint8_t *id128);                              /* 128-byte NCCL unique id (rank 0)   */
 int dls_comm_init(dls_ctx *ctx, const uint8_t *id128, int rank, int world_size);

@@ -262,3 +262,27 @@ def test_backward_data_with_the_derivative_of_the_layer_below(env, backend, case
     else:
         want = (plain * B.minimum(ys * 3.4028234663852886e38, be.scalar(1.0))).flat_array()
     assert (got.view(np.uint32) == want.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("shape", [(256, 32, 32, 3, 32, 2), (5, 12, 20, 4, 32, 1), (4, 16, 16, 1, 8, 2)],
+                         ids=["c3-conv1-sampled", "dense", "one-channel-sampled"])
+def test_first_layer_weight_and_bias_gradient_in_one_pass(env, backend, shape):
+    """dls_conv3x3_backward_weights_bias: the first-layer kernel returns dW and the bias gradient from one pass over the
+    delta; dW as from the plain entry, db = the fp32 column sums of the unrounded delta (1e-5 relative, the reductions bar)."""
+    MO, O, B = env
+    mode, be = backend
+    batch, h, w, cin, cout, s = shape
+    rng = np.random.RandomState(sum(shape))
+    x = rng.standard_normal((batch, h, w, cin)).astype(np.float32)
+    dzs = rng.standard_normal((batch, h // s, w // s, cout)).astype(np.float32)
+    xt, dt = be.tensor(x).do_cache(), be.tensor(dzs).do_cache()
+    n0 = be.stats()["kernel_launches"]
+    dw, db = be.conv3x3_backward_weights_bias(xt, dt, dz_stride=s)
+    got_db = db.flat_array()
+    got_dw = dw.flat_array()
+    assert be.stats()["kernel_launches"] - n0 == 2                      # the pass + its fixed-order reduce, once for both
+    ref_dw = be.conv3x3_backward_weights(xt, dt, dz_stride=s).flat_array()
+    assert (got_dw.view(np.uint32) == ref_dw.view(np.uint32)).all()
+    want_db = dzs.astype(np.float64).sum(axis=(0, 1, 2))
+    scale = np.abs(dzs).astype(np.float64).sum(axis=(0, 1, 2))
+    assert (np.abs(got_db - want_db) / scale).max() <= 1e-6
