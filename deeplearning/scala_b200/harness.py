@@ -29,7 +29,18 @@ class Exchange:
         self._N, self._C = N, C
         # the communicator is capped at DLS_EXCHANGE_CTAS (default 8) CTAs by dls_comm_init (ncclCommInitRankConfig): the
         # gradient buckets are a few MB and travel under the rest of the backward pass, which keeps the other SMs
-        N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
+        # NCCL reads NCCL_PROTO when it tunes a NEW communicator: with few CTAs it would pick the LL protocol for the 8 MB
+        # bucket (half of every 8 bytes is a flag: 113 us at 8 GPUs, which puts the collective on the step's critical path);
+        # LL128 carries 120 of 128 bytes.  Only for this communicator, only if the user has not chosen: the variable is
+        # restored right after.
+        proto, had = os.environ.get("DLS_EXCHANGE_PROTO", "LL128"), os.environ.get("NCCL_PROTO")
+        if had is None and proto:
+            os.environ["NCCL_PROTO"] = proto
+        try:
+            N.check(N.lib.dls_comm_init(backend.ctx, unique_id, rank, world_size))
+        finally:
+            if had is None and proto:
+                os.environ.pop("NCCL_PROTO", None)
         self._pending, self._pending_bytes = [], 0
         self._held = []                         # small gradients waiting for the one-launch peer sum at `flush`
         self._over_nccl = set()                 # ids of the gradient buffers this step sent through NCCL
