@@ -29,11 +29,10 @@ class Exchange:
         self._N, self._C = N, C
         # the communicator is capped at DLS_EXCHANGE_CTAS (default 8) CTAs by dls_comm_init (ncclCommInitRankConfig): the
         # gradient buckets are a few MB and travel under the rest of the backward pass, which keeps the other SMs
-        # NCCL reads NCCL_PROTO when it tunes a NEW communicator: with few CTAs it would pick the LL protocol for the 8 MB
-        # bucket (half of every 8 bytes is a flag: 113 us at 8 GPUs, which puts the collective on the step's critical path);
-        # LL128 carries 120 of 128 bytes.  Only for this communicator, only if the user has not chosen: the variable is
-        # restored right after.
-        proto, had = os.environ.get("DLS_EXCHANGE_PROTO", "LL128"), os.environ.get("NCCL_PROTO")
+        # NCCL reads NCCL_PROTO when it tunes a NEW communicator, so DLS_EXCHANGE_PROTO can pin the protocol of this one only
+        # (the variable is restored right after).  Default: NCCL's own choice -- measured at 8 GPUs on the C5 step (ms):
+        # NCCL's choice (LL) 0.268, Simple 0.269, LL128 0.289.
+        proto, had = os.environ.get("DLS_EXCHANGE_PROTO", ""), os.environ.get("NCCL_PROTO")
         if had is None and proto:
             os.environ["NCCL_PROTO"] = proto
         try:
