@@ -44,47 +44,58 @@ __device__ __forceinline__ float round_operand(float x) {
 template <bool TF32>
 __global__ void __launch_bounds__(256) conv_stage_act_kernel(const float *__restrict__ in, void *__restrict__ out, long long pixels,
                                                              int H, int W, int C, int Cp, int stride, int up) {
-  const int groups = Cp >> 2;
+  // one thread per 8 channels (bf16: one 16-byte store; tf32: two), two 128-bit loads when the source channels allow
+  const int groups = Cp >> 3;
   const long long total = pixels * groups;
   const bool vec = (C & 3) == 0;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const long long p = i / groups;
-    const int c = (int)(i - p * groups) << 2;
+    const int c = (int)(i - p * groups) << 3;
     const int x = (int)(p % W);
     const long long q = p / W;
     const int y = (int)(q % H);
     const long long b = q / H;
     const float *src;
-    bool live = c < C;
+    bool live = true;
     if (up > 1) {
-      live = live && (y % up) == 0 && (x % up) == 0;
+      live = (y % up) == 0 && (x % up) == 0;
       src = in + ((b * (H / up) + y / up) * (long long)(W / up) + x / up) * C + c;
     } else {
       src = in + (((b * H + y) * stride) * (long long)(W * stride) + (long long)x * stride) * C + c;
     }
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.f;
     if (live) {
       if (vec) {
-        v = __ldg(reinterpret_cast<const float4 *>(src));
+        if (c < C) {
+          const float4 q0 = __ldg(reinterpret_cast<const float4 *>(src));
+          v[0] = q0.x; v[1] = q0.y; v[2] = q0.z; v[3] = q0.w;
+        }
+        if (c + 4 < C) {
+          const float4 q1 = __ldg(reinterpret_cast<const float4 *>(src) + 1);
+          v[4] = q1.x; v[5] = q1.y; v[6] = q1.z; v[7] = q1.w;
+        }
       } else {
-        v.x = __ldg(src);
-        if (c + 1 < C) v.y = __ldg(src + 1);
-        if (c + 2 < C) v.z = __ldg(src + 2);
-        if (c + 3 < C) v.w = __ldg(src + 3);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (c + k < C) v[k] = __ldg(src + k);
       }
     }
     if (TF32) {
-      v.x = round_tf32_rna(v.x);
-      v.y = round_tf32_rna(v.y);
-      v.z = round_tf32_rna(v.z);
-      v.w = round_tf32_rna(v.w);
-      reinterpret_cast<float4 *>(out)[i] = v;
+      float4 o0 = make_float4(round_tf32_rna(v[0]), round_tf32_rna(v[1]), round_tf32_rna(v[2]), round_tf32_rna(v[3]));
+      float4 o1 = make_float4(round_tf32_rna(v[4]), round_tf32_rna(v[5]), round_tf32_rna(v[6]), round_tf32_rna(v[7]));
+      reinterpret_cast<float4 *>(out)[2 * i] = o0;
+      reinterpret_cast<float4 *>(out)[2 * i + 1] = o1;
     } else {
-      __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-      uint2 o;
-      o.x = *reinterpret_cast<uint32_t *>(&lo);
-      o.y = *reinterpret_cast<uint32_t *>(&hi);
-      reinterpret_cast<uint2 *>(out)[i] = o;
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(v[0], v[1]), p1 = __floats2bfloat162_rn(v[2], v[3]);
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(v[4], v[5]), p3 = __floats2bfloat162_rn(v[6], v[7]);
+      uint4 o;
+      o.x = *reinterpret_cast<uint32_t *>(&p0);
+      o.y = *reinterpret_cast<uint32_t *>(&p1);
+      o.z = *reinterpret_cast<uint32_t *>(&p2);
+      o.w = *reinterpret_cast<uint32_t *>(&p3);
+      reinterpret_cast<uint4 *>(out)[i] = o;
     }
   }
 }
@@ -488,7 +499,7 @@ int launch_conv_direct_dw(dls_ctx *ctx, int stream, int mode, const float *x, co
 
 int launch_conv_stage_act(dls_ctx *ctx, int stream, int mode, const float *in, void *out, long long pixels, int H, int W, int C, int Cp,
                           int stride, int up) {
-  const long long total = pixels * (Cp / 4);
+  const long long total = pixels * (Cp / 8);
   if (total == 0) return DLS_OK;
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)ctx->sm_count * 16);
   if (mode == DLS_GEMM_TF32) conv_stage_act_kernel<true><<<grid, 256, 0, ctx->streams[stream]>>>(in, out, pixels, H, W, C, Cp, stride, up);
