@@ -7,11 +7,13 @@ import time
 import torch
 
 
-def run(dtype, tf32):
+def run(dtype, tf32, uniform=False):
     torch.backends.cuda.matmul.allow_tf32 = tf32
     n = 8192
-    a = torch.randn(n, n, device="cuda", dtype=dtype)
-    b = torch.randn(n, n, device="cuda", dtype=dtype)
+    # operand statistics matter on a power-limited part: zero-mean (randn) operands toggle more bits than uniform [0, 1)
+    make = (lambda: torch.rand(n, n, device="cuda", dtype=torch.float32).to(dtype)) if uniform else \
+        (lambda: torch.randn(n, n, device="cuda", dtype=dtype))
+    a, b = make(), make()
     for _ in range(5):
         torch.matmul(a, b)
     torch.cuda.synchronize()
@@ -35,7 +37,7 @@ def run(dtype, tf32):
     e1.synchronize()
     sustained = e0.elapsed_time(e1) / reps
     flop = 2.0 * n ** 3
-    return {"dtype": ("tf32" if tf32 else str(dtype).split(".")[-1]), "n": n, "burst_ms": round(best, 4),
+    return {"dtype": ("tf32" if tf32 else str(dtype).split(".")[-1]), "operands": "uniform [0,1)" if uniform else "randn", "n": n, "burst_ms": round(best, 4),
             "burst_tflops": round(flop / best / 1e9, 1), "sustained_ms": round(sustained, 4),
             "sustained_tflops": round(flop / sustained / 1e9, 1), "how": "torch.matmul (cuBLAS), builder-measured"}
 
@@ -43,3 +45,5 @@ def run(dtype, tf32):
 if __name__ == "__main__":
     print(json.dumps(run(torch.float32, True)), flush=True)
     print(json.dumps(run(torch.bfloat16, False)), flush=True)
+    print(json.dumps(run(torch.float32, True, uniform=True)), flush=True)
+    print(json.dumps(run(torch.bfloat16, False, uniform=True)), flush=True)
