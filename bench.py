@@ -287,8 +287,8 @@ def gemm_probe(be, peaks, reps=10):
                     rec["frac"] = tf / peaks["bf16"]
                     rec["peak"] = peaks["bf16"]
                 else:                                        # cuBLAS TF32 8192^3 on this pool, builder-measured
-                    rec["frac"] = tf / 733.9                 # (tools/tf32_peak_probe.py, profiles/r2_cublas_peaks.jsonl)
-                    rec["peak"] = 733.9
+                    rec["frac"] = tf / 742.2                 # (tools/tf32_peak_probe.py, profiles/r2_cublas_peaks.jsonl)
+                    rec["peak"] = 742.2
                     rec["peak_source"] = "builder-measured cuBLAS tf32 burst (MEASURED_PEAKS.json has no tf32 entry)"
                 out["gemm2_tc_kernel (CTA pair) %s %dx%dx%d" % (mode, m, n, k)] = rec
                 del keep
