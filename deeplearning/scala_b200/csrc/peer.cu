@@ -7,8 +7,9 @@
 //
 //   phase 1  every CTA copies its chunks of this rank's gradients into this rank's staging area (peer visible)
 //            and raises one flag per peer (st.release.sys into the peer's flag array);
-//   phase 2  while the flags travel, the CTA applies the updates that need no exchange -- segments whose gradient was
-//            already reduced (the large bucket that NCCL moved under the backward pass), i.e. a multi-tensor SGD;
+//   phase 2  the updates that need no exchange -- segments whose gradient was already reduced (the large bucket that NCCL
+//            moved under the backward pass), i.e. a multi-tensor SGD -- run on kPeerGrid CTAs of their own in the same
+//            launch (on the exchange CTAs themselves when the launch has nothing to exchange);
 //   phase 3  it waits for the same CTA of every peer (ld.acquire.sys on its own flag array);
 //   phase 4  it reads the chunk from every rank's staging area (remote ranks over NVLink, 16-byte loads, all in
 //            flight together), adds them in rank order 0..W-1 -- the same order on every rank, so replicas stay
