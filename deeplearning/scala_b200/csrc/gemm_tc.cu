@@ -116,13 +116,15 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 
 // UMMA shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout): start address, leading / stride byte
 // offsets in 16-byte units, version 1 (Blackwell), layout type 2 = SWIZZLE_128B.
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte chunks XORed with the row of an 8-row atom), 1 = SWIZZLE_128B_BASE32B (32-byte chunks XORed
+// with the row of a 4-row atom: the form tcgen05 reads MN-major 32-bit operands in; TMA: CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout << 61;
   return d;
 }
 
@@ -290,7 +292,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
   constexpr int BLOCK_K = 128 / ELEM;       // one 128-byte swizzle row of K per stage
   constexpr int UMMA_K = 32 / ELEM;         // K per tcgen05.mma
   constexpr int MN_ATOM = 128 / ELEM;       // rows covered by one 128-byte line of an MN-major operand
-  static_assert(!(TF32 && (A_MN || B_MN)), "TF32 operands are K-major only (MN-major fp32 needs the 32B-atom swizzle)");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -438,8 +439,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
           const uint32_t b_addr = a_addr + A_STAGE_BYTES;
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
-            const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
+            // MN-major tf32: 4-row atoms of 512 B (SBO), 32-byte-chunk swizzle; everything else: 8-row atoms of 1024 B
+            const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, (TF32 && A_MN) ? 512 : 1024, (TF32 && A_MN) ? 1u : 2u);
+            const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, (TF32 && B_MN) ? 512 : 1024, (TF32 && B_MN) ? 1u : 2u);
             umma(d_tmem, ad, bd, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u, TF32);
           }
           umma_commit(empty_bar(stage));   // frees the smem slot once these MMAs have read it
@@ -619,7 +621,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
   constexpr int BLOCK_K = 128 / ELEM;
   constexpr int UMMA_K = 32 / ELEM;
   constexpr int MN_ATOM = 128 / ELEM;
-  static_assert(!(TF32 && (A_MN || B_MN)), "TF32 operands are K-major only");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -736,8 +737,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
           const uint32_t b_addr = a_addr + BM * 128;
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
-            const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
+            // MN-major tf32: 4-row atoms of 512 B (SBO), 32-byte-chunk swizzle; everything else: 8-row atoms of 1024 B
+            const uint64_t ad = smem_desc(a_addr + k * a_kstep, a_lbo, (TF32 && A_MN) ? 512 : 1024, (TF32 && A_MN) ? 1u : 2u);
+            const uint64_t bd = smem_desc(b_addr + k * b_kstep, b_lbo, (TF32 && B_MN) ? 512 : 1024, (TF32 && B_MN) ? 1u : 2u);
             umma_pair(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u, TF32);
           }
           umma_commit_pair(empty_bar(stage));        // frees the slot in BOTH CTAs once these MMAs have read it
@@ -917,7 +919,7 @@ static encode_tiled_fn get_encoder() {
 
 // 2-D row-major tensor [outer][inner] with a 128B-swizzled box.
 static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, const void *base, uint64_t inner, uint64_t outer,
-                    uint64_t pitch_elems, uint32_t box_inner, uint32_t box_outer) {
+                    uint64_t pitch_elems, uint32_t box_inner, uint32_t box_outer, bool atom32 = false) {
   encode_tiled_fn enc = get_encoder();
   DLS_CHECK(enc != nullptr, DLS_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t dims[2] = {inner, outer};
@@ -925,7 +927,8 @@ static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, co
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r) + " (inner " + std::to_string(inner) +
               ", outer " + std::to_string(outer) + ", pitch " + std::to_string(pitch_elems) + ")");
@@ -1092,7 +1095,6 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   using namespace tc;
   DLS_CHECK(kind == DLS_GEMM_BF16 || kind == DLS_GEMM_TF32, DLS_ERR_INVALID, "launch_gemm_tc: kind must be BF16 or TF32");
   const bool tf32 = kind == DLS_GEMM_TF32;
-  DLS_CHECK(!(tf32 && (a_mn || b_mn)), DLS_ERR_UNSUPPORTED, "launch_gemm_tc: TF32 operands must be K-major");
   const int elem = tf32 ? 4 : 2;
   const int block_k = 128 / elem, mn_atom = 128 / elem;
   DLS_CHECK((lda * elem) % 16 == 0 && (ldb * elem) % 16 == 0 && ((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0,
@@ -1101,7 +1103,7 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   CUtensorMap ma, mb, mc;
   int rc;
   // K-major [rows][K]: box = BLOCK_K x tile rows.  MN-major [K][rows]: box = 128 bytes of rows x BLOCK_K.
-  rc = a_mn ? make_map(&ma, dt, elem, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, mn_atom, block_k)
+  rc = a_mn ? make_map(&ma, dt, elem, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, mn_atom, block_k, tf32)
             : make_map(&ma, dt, elem, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, block_k, BM);
   if (rc) return rc;
   // CTA-pair kernel (cta_group::2, 256 x 256 tiles) for contractions that fill the machine at least twice with such tiles;
@@ -1118,7 +1120,7 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
   const int num_kb_all = (K + block_k - 1) / block_k;
   const bool will_split = tiles256 * 2 <= tc::usable_sms(ctx) && num_kb_all >= 16 && N % 4 == 0;
   const int bn = (!pair_mode && !will_split && N > 128 && tiles256 * 2 <= ctx->sm_count) ? 128 : BN;
-  rc = b_mn ? make_map(&mb, dt, elem, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, mn_atom, block_k)
+  rc = b_mn ? make_map(&mb, dt, elem, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, mn_atom, block_k, tf32)
             : make_map(&mb, dt, elem, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, block_k, pair_mode ? BN2 / 2 : bn);
   if (rc) return rc;
   ConvGeom plain;
@@ -1158,13 +1160,19 @@ int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn,
     mc = ma;   // unused by the kernel in direct-store mode
   }
   if (!rc && pair_mode && sp.splits == 1) {
-    if (tf32) rc = launch_variant2<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    if (tf32 && !a_mn && !b_mn) rc = launch_variant2<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else if (tf32 && !a_mn && b_mn) rc = launch_variant2<true, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else if (tf32 && a_mn && !b_mn) rc = launch_variant2<true, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
+    else if (tf32) rc = launch_variant2<true, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
     else if (!a_mn && !b_mn) rc = launch_variant2<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
     else if (!a_mn && b_mn) rc = launch_variant2<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
     else if (a_mn && !b_mn) rc = launch_variant2<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
     else rc = launch_variant2<false, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct);
   } else if (!rc) {
-    if (tf32) rc = launch_variant<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    if (tf32 && !a_mn && !b_mn) rc = launch_variant<true, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else if (tf32 && !a_mn && b_mn) rc = launch_variant<true, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else if (tf32 && a_mn && !b_mn) rc = launch_variant<true, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
+    else if (tf32) rc = launch_variant<true, true, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
     else if (!a_mn && !b_mn) rc = launch_variant<false, false, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
     else if (!a_mn && b_mn) rc = launch_variant<false, false, true>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);
     else if (a_mn && !b_mn) rc = launch_variant<false, true, false>(ctx, st, ma, mb, mc, dst, M, N, K, ld_dst, kepi, direct, sp, plain);

@@ -144,7 +144,13 @@ int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long ro
   Block &sh = private_blk ? *private_blk : buf->shadow[slot];
   long long &tag_r = private_blk ? no_rows : buf->shadow_rows[slot];
   long long &tag_c = private_blk ? no_cols : buf->shadow_cols[slot];
-  const bool transposed = mode == DLS_GEMM_TF32 && contraction_is_row;
+  // TF32 operands stored MN-major are read in place through the 32-byte-atom swizzle (gemm_tc.cu); DLS_TF32_MN=0 goes back to
+  // the transposing staging pass that made them K-major
+  static const bool tf32_mn = [] {
+    const char *e = getenv("DLS_TF32_MN");
+    return !(e && atoi(e) == 0);
+  }();
+  const bool transposed = mode == DLS_GEMM_TF32 && contraction_is_row && !tf32_mn;
   const long long p = mode == DLS_GEMM_BF16 ? ((cols + 7) & ~7LL) : transposed ? ((rows + 3) & ~3LL) : ((cols + 3) & ~3LL);
   // slot 1 holds either the transposed or the re-pitched fp32 copy; the sign of shadow_rows tells which
   const long long tag_rows = transposed ? -rows : rows;
@@ -181,7 +187,7 @@ int stage_operand(dls_ctx *ctx, int stream, int mode, dls_buf *buf, long long ro
   }
   *ptr = sh.ptr;
   *pitch = p;
-  *mn_major = mode == DLS_GEMM_BF16 ? contraction_is_row : false;
+  *mn_major = (mode == DLS_GEMM_BF16 || tf32_mn) ? contraction_is_row : false;
   return DLS_OK;
 }
 
