@@ -823,7 +823,8 @@ int dls_conv3x3_backward_weights_bias(dls_ctx *ctx, dls_buf *x, dls_buf *dz, siz
     // a sampled delta is contracted over its own pixels only: staged compact (slot 4; backward-data keeps the zero-filled
     // full-size copy in slot 2), the activation read through TMA element strides
     ConvGeom probe;
-    const bool compact = dzs > 1 && dzs <= 8 && conv_tiling((int)h / dzs, (int)wd / dzs, 64, &probe) && probe.bw * dzs <= 256 &&
+    const bool compact = dzs > 1 && dzs <= 8 && conv_tiling((int)h / dzs, (int)wd / dzs, mode == DLS_GEMM_TF32 ? 32 : 64, &probe) &&
+                         probe.bw * dzs <= 256 &&
                          probe.bh * dzs <= 256;
     if (!rc && compact) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h / dzs, (int)wd / dzs, (int)cout, 1, 1, &da, &cdp, 4);
     else if (!rc) rc = staged_act(ctx, stream, mode, dz, (int)batch, (int)h, (int)wd, (int)cout, 1, dzs, &da, &cdp);

@@ -940,7 +940,7 @@ static int make_map(CUtensorMap *map, CUtensorMapDataType dt, int elem_bytes, co
 // rank-N row-major tensor (dims[0] innermost, strides in bytes for dims 1..rank-1) with a 128B-swizzled box; elements
 // outside the tensor read as zero.
 static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *base, int rank, const uint64_t *dims,
-                       const uint64_t *strides_bytes, const uint32_t *box, const uint32_t *elem_strides = nullptr) {
+                       const uint64_t *strides_bytes, const uint32_t *box, const uint32_t *elem_strides = nullptr, bool atom32 = false) {
   encode_tiled_fn enc = get_encoder();
   DLS_CHECK(enc != nullptr, DLS_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   cuuint64_t d[5], s[4];
@@ -952,7 +952,8 @@ static int make_map_nd(CUtensorMap *map, CUtensorMapDataType dt, const void *bas
     if (i + 1 < rank) s[i] = strides_bytes[i];
   }
   CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void *>(base), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     std::string t = "cuTensorMapEncodeTiled (rank " + std::to_string(rank) + ") failed with CUresult " + std::to_string((int)r) + ": dims";
     for (int i = 0; i < rank; ++i) t += " " + std::to_string(dims[i]) + "/" + std::to_string(box[i]);
@@ -1292,18 +1293,22 @@ __global__ void __launch_bounds__(256) conv_dw_reduce_kernel(const float *__rest
 
 bool conv_dw_tc_supported(int kind, int H, int W, int cin, int cout) {
   ConvGeom g;
-  return kind == DLS_GEMM_BF16 && conv_tiling(H, W, 64, &g) && cin >= 1 && cout >= 1 && cout <= tc::BN;
+  const int atom = kind == DLS_GEMM_TF32 ? 32 : 64;   // pixels per k block = channels per 128-byte operand row
+  return (kind == DLS_GEMM_BF16 || kind == DLS_GEMM_TF32) && conv_tiling(H, W, atom, &g) && cin >= 1 && cout >= 1 && cout <= tc::BN;
 }
 
 int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int cxp, const void *dz, int cdp, int batch, int H, int W,
                       int cin, int cout, float *dw, int dzs) {
   using namespace tc;
-  DLS_CHECK(conv_dw_tc_supported(kind, H, W, cin, cout) && cxp % 64 == 0 && cdp % 64 == 0, DLS_ERR_UNSUPPORTED,
+  const bool tf32 = kind == DLS_GEMM_TF32;
+  const int elem = tf32 ? 4 : 2, atom = 128 / elem;
+  const CUtensorMapDataType dt = tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  DLS_CHECK(conv_dw_tc_supported(kind, H, W, cin, cout) && cxp % atom == 0 && cdp % atom == 0, DLS_ERR_UNSUPPORTED,
             "launch_conv_dw_tc: shape not supported by the implicit-GEMM weight-gradient kernel");
   ConvGeom cg;
   // the k pixels: all of them, or (sampled delta) the H/dzs x W/dzs grid of delta-carrying ones
-  DLS_CHECK(conv_tiling(H / dzs, W / dzs, 64, &cg), DLS_ERR_UNSUPPORTED, "launch_conv_dw_tc: the sampled pixel grid does not tile");
-  cg.cblks = cxp / 64;
+  DLS_CHECK(conv_tiling(H / dzs, W / dzs, atom, &cg), DLS_ERR_UNSUPPORTED, "launch_conv_dw_tc: the sampled pixel grid does not tile");
+  cg.cblks = cxp / atom;
   cg.n_mma = (cout + 15) & ~15;
   cg.px_stride = dzs;
   const long long P = (long long)batch * (H / dzs) * (W / dzs);
@@ -1312,16 +1317,16 @@ int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int c
   CUtensorMap ma, mb, mc;
   {
     const uint64_t dims[4] = {(uint64_t)cxp, (uint64_t)W, (uint64_t)H, (uint64_t)batch};
-    const uint64_t str[3] = {(uint64_t)cxp * 2, (uint64_t)cxp * 2 * W, (uint64_t)cxp * 2 * W * H};
-    const uint32_t box[4] = {64, (uint32_t)(cg.bw * dzs), (uint32_t)(cg.bh * dzs), (uint32_t)cg.bb};
+    const uint64_t str[3] = {(uint64_t)cxp * elem, (uint64_t)cxp * elem * W, (uint64_t)cxp * elem * W * H};
+    const uint32_t box[4] = {(uint32_t)atom, (uint32_t)(cg.bw * dzs), (uint32_t)(cg.bh * dzs), (uint32_t)cg.bb};
     const uint32_t est[4] = {1, (uint32_t)dzs, (uint32_t)dzs, 1};
-    int rc = make_map_nd(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, act, 4, dims, str, box, est);
+    int rc = make_map_nd(&ma, dt, act, 4, dims, str, box, est, tf32);
     if (rc) return rc;
   }
-  int rc = make_map(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dz, (uint64_t)cdp, (uint64_t)P, (uint64_t)cdp, 64, 64);
+  int rc = make_map(&mb, dt, elem, dz, (uint64_t)cdp, (uint64_t)P, (uint64_t)cdp, atom, atom, tf32);
   if (rc) return rc;
   const int tiles = (M + BM - 1) / BM;
-  const int num_kb = (int)((P + 63) / 64);
+  const int num_kb = (int)((P + atom - 1) / atom);
   SplitPlan sp;
   int want = std::max(1, std::min(usable_sms(ctx) / tiles, num_kb / 8));
   sp.kb_per_split = (num_kb + want - 1) / want;
@@ -1335,7 +1340,8 @@ int launch_conv_dw_tc(dls_ctx *ctx, int stream, int kind, const void *act, int c
   float *part = (float *)scratch.ptr;
   rc = make_map(&mc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, part, (uint64_t)N, (uint64_t)sp.c_rows, (uint64_t)ldp, EPI_CHUNK, 32);
   cudaStream_t st = ctx->streams[stream];
-  if (!rc) rc = launch_variant<false, true, true, 2>(ctx, st, ma, mb, mc, part, M, N, (int)P, ldp, GemmEpilogue(), 0, sp, cg);
+  if (!rc && tf32) rc = launch_variant<true, true, true, 2>(ctx, st, ma, mb, mc, part, M, N, (int)P, ldp, GemmEpilogue(), 0, sp, cg);
+  else if (!rc) rc = launch_variant<false, true, true, 2>(ctx, st, ma, mb, mc, part, M, N, (int)P, ldp, GemmEpilogue(), 0, sp, cg);
   if (!rc) {
     const int total = 9 * cin * cout;
     conv_dw_reduce_kernel<<<std::min((total + 255) / 256, ctx->sm_count * 8), 256, 0, st>>>(part, dw, sp.splits, (size_t)m_pad * ldp, cxp,
