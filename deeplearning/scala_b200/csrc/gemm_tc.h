@@ -55,7 +55,7 @@ int launch_conv_tc(dls_ctx *ctx, int stream, int kind, const void *act, int batc
                    void *copy_down = nullptr, void *copy_up = nullptr, int copy_s = 1);
 
 // Weight gradient dw[9*cin, cout] fp32 (= [3,3,cin,cout]) = sum over pixels of act[p - tap][c] * dz[p][f]: contraction over the
-// pixels, both operands read MN-major from their staged NHWC copies (act [batch][H][W][cxp], dz [batch*H*W][cdp]; bf16 only,
+// pixels, both operands read MN-major from their staged NHWC copies (act [batch][H][W][cxp], dz [batch*H*W][cdp]; bf16: 64-element atoms, tf32: 32-element atoms through the 32-byte-atom swizzle;
 // channels padded to 64), A through tap-shifted 4-D boxes; split over the SMs along the pixels + one reduce launch.
 bool conv_dw_tc_supported(int kind, int H, int W, int cin, int cout);
 // dzs > 1: dz is the COMPACT sampled delta [batch * H/dzs * W/dzs][cdp]; only those pixels are contracted, and the activation
@@ -78,7 +78,7 @@ int launch_conv_pack_weights(dls_ctx *ctx, int stream, int mode, const float *w,
 //   kind  : DLS_GEMM_BF16 (operands are bf16 in HBM) or DLS_GEMM_TF32 (operands are fp32 in HBM, read as tf32)
 //   a_mn  : false -> A stored [M][K] (K contiguous, pitch lda elements); true -> stored [K][M] (M contiguous)
 //   b_mn  : false -> B stored [N][K] (K contiguous, pitch ldb);          true -> stored [K][N] (N contiguous)
-// Operand rows must start 16-byte aligned (pitch * element size % 16 == 0); TF32 operands must be K-major.
+// Operand rows must start 16-byte aligned (pitch * element size % 16 == 0); MN-major TF32 operands are read through the 32-byte-atom swizzle.
 int launch_gemm_tc(dls_ctx *ctx, int stream, int kind, const void *A, bool a_mn, long long lda, const void *B, bool b_mn,
                    long long ldb, float *C, long long ldc, int M, int N, int K, const GemmEpilogue &epi);
 
