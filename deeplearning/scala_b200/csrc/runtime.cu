@@ -299,6 +299,17 @@ int dls_ctx_sync(dls_ctx *ctx) {
   if (ctx->comm_stream) DLS_CUDA(cudaStreamSynchronize(ctx->comm_stream));
   if (ctx->copy_stream) DLS_CUDA(cudaStreamSynchronize(ctx->copy_stream));
   for (cudaStream_t s : ctx->streams) DLS_CUDA(cudaStreamSynchronize(s));
+  {
+    // Every exchange has finished: forget the joins still owed.  An event recorded by eager work must not be waited
+    // for inside a capture opened later (cudaErrorStreamCaptureIsolation).
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+    for (dls_buf *b : ctx->comm_pending)
+      if (b && b->comm_ready) {
+        cudaEventDestroy(b->comm_ready);
+        b->comm_ready = nullptr;
+      }
+    ctx->comm_pending.clear();
+  }
   return peer_check(ctx);
 }
 
