@@ -29,6 +29,7 @@ DLS_HASH_WANG, DLS_HASH_LCG = 0, 1
 DLS_GEMM_FP32, DLS_GEMM_TF32, DLS_GEMM_BF16 = 0, 1, 2
 DLS_OPT_MOMENTUM, DLS_OPT_ADAM = 0, 1
 DLS_CONV_FORWARD, DLS_CONV_BACKWARD_DATA, DLS_CONV_BACKWARD_WEIGHTS = 0, 1, 2
+DLS_SUM_STATIC_MAX_FLOATS = 1 << 28
 
 
 class CtxOpts(C.Structure):
@@ -128,6 +129,7 @@ _SIG = {
     "dls_graph_retain": (None, [_P]),
     "dls_graph_release": (None, [_P]),
     "dls_buf_copy": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "dls_sum_static": (C.c_int, [_P, _P, C.c_size_t, _P]),
 }
 EXPORTS = tuple(_SIG)
 for _name, (_res, _args) in _SIG.items():

@@ -151,6 +151,16 @@ int dls_sum(dls_ctx *ctx, dls_buf *in, size_t n_floats, dls_event *const *deps, 
  * TensorLayers.sumAs unrolls on the host (TL:124-162) */
 int dls_sum_axis(dls_ctx *ctx, dls_buf *in, size_t outer, size_t k, size_t inner, dls_event *const *deps, int n_deps,
                  dls_buf **out, dls_event **done);
+/* The full sum above for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * out[0] = sum of in[0 .. n_floats) into a buffer the caller already owns; the grid scratch lives in a file-scope
+ * __device__ array (8448 bytes per GPU that loads the library, held until exit), so a call makes no cudaMalloc,
+ * cudaFree, event or allocator call.  n_floats above DLS_SUM_STATIC_MAX_FLOATS is rejected with DLS_ERR_INVALID.
+ * Every call on a device shares that array: calls ordered on one stream are safe, calls that overlap on the GPU
+ * race.  The first call on a device resolves the array's address; make it before opening a capture.  Same lane
+ * arithmetic as the allocating entry, so on devices with at most 256 SMs the two results are bit-identical. */
+#define DLS_SUM_STATIC_MAX_FLOATS 268435456u      /* 2^28 floats = 1 GiB of input                            */
+int dls_sum_static(dls_ctx *ctx, dls_buf *in, size_t n_floats, dls_buf *out);
 
 /* ---- RNG: replaces the `random` / `random_normal` programs Tensors:398-443 and their launches Tensors:479-524 */
 int dls_random(dls_ctx *ctx, size_t n_floats, uint32_t seed, dls_buf **out, dls_event **done);
