@@ -48,6 +48,9 @@ int dls_graph_begin(dls_ctx *ctx) {
   DLS_CHECK(ctx->n_streams == 1, DLS_ERR_UNSUPPORTED, "dls_graph_begin: captured steps need a single-stream context");
   DLS_CHECK(ctx->capture_pool == 0, DLS_ERR_INVALID, "dls_graph_begin: a capture is already open on this context");
   DLS_CUDA(cudaSetDevice(ctx->device));
+  // exchanges issued eagerly rejoin the compute stream now: their events may not be waited for inside the recording
+  int rc = join_all_exchanges(ctx, 0);
+  if (rc) return rc;
   // relaxed mode: the allocator may call cudaMalloc for the arena while recording
   DLS_CUDA(cudaStreamBeginCapture(ctx->streams[0], cudaStreamCaptureModeRelaxed));
   ctx->capture_pool = ctx->next_pool++;

@@ -300,15 +300,22 @@ int dls_ctx_sync(dls_ctx *ctx) {
   if (ctx->copy_stream) DLS_CUDA(cudaStreamSynchronize(ctx->copy_stream));
   for (cudaStream_t s : ctx->streams) DLS_CUDA(cudaStreamSynchronize(s));
   {
-    // Every exchange has finished: forget the joins still owed.  An event recorded by eager work must not be waited
-    // for inside a capture opened later (cudaErrorStreamCaptureIsolation).
+    // Forget the joins owed to exchanges that have finished: an event recorded by eager work must not be waited for
+    // inside a capture opened later (cudaErrorStreamCaptureIsolation).  An exchange another thread issued after the
+    // synchronisation above is not complete yet and stays owed.
     std::lock_guard<std::recursive_mutex> lk(ctx->mu);
-    for (dls_buf *b : ctx->comm_pending)
-      if (b && b->comm_ready) {
+    size_t kept = 0;
+    for (dls_buf *b : ctx->comm_pending) {
+      if (!b || !b->comm_ready) continue;
+      if (cudaEventQuery(b->comm_ready) == cudaSuccess) {
         cudaEventDestroy(b->comm_ready);
         b->comm_ready = nullptr;
+      } else {
+        cudaGetLastError();   // cudaErrorNotReady is not an error here
+        ctx->comm_pending[kept++] = b;
       }
-    ctx->comm_pending.clear();
+    }
+    ctx->comm_pending.resize(kept);
   }
   return peer_check(ctx);
 }
